@@ -1,0 +1,301 @@
+#!/usr/bin/env python
+"""bench.py — scored cell x locus nonzeros / second per EM iteration (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C2]
+
+A step is ONE EM iteration (compute_new_excluded, cellector/src/main.rs:308-347: alpha/beta tables, per-cell
+scoring, IQR threshold, exclusion, per-locus column pass, -80 locus filter) over the synthetic workload, driven
+through the C ABI of libcellector_cuda.so.  N=1 runs BASELINE.json configs[1] (C2: 10k cells x 100k loci, 2 %
+foreign cells); N>1 is weak scaling: every rank holds a C2-sized cell shard (N x 10k cells), per-locus arrays are
+allreduced with NCCL and the threshold is global.  L2 is flushed between timed steps.  One JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from cellector_b200 import synth  # noqa: E402
+
+METRIC = "scored cell x locus nonzeros per second per EM iteration"
+UNIT = "nnz/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C2", choices=list(synth.CONFIGS))
+    ap.add_argument("--cpu-sample-cells", type=int, default=2500)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--flags", type=int, default=0, help="extra clx_create flags (e.g. 4 = v0 scoring kernel)")
+    return ap.parse_args()
+
+
+def workload_config(name, world):
+    base = synth.CONFIGS[name]
+    cfg = synth.SynthConfig(**{**base.__dict__})
+    cfg.n_cells = base.n_cells * world  # weak scaling: fixed cells per GPU
+    return cfg
+
+
+def config_dict(name, cfg, world, extra=None):
+    d = {"workload": f"{name}: synthetic vartrix ref/alt, {cfg.n_cells // world} cells x {cfg.n_loci} loci per GPU, "
+                     f"density {cfg.density}, {cfg.minority_frac:.0%} minority genotype, min_alt=min_ref=4",
+         "cells_per_gpu": cfg.n_cells // world, "loci": cfg.n_loci, "density": cfg.density, "seed": cfg.seed,
+         "l2": "flushed between timed steps (512 MiB overwrite)", "sharding": f"cells x{world}"}
+    if extra:
+        d.update(extra)
+    return d
+
+
+class ClockSampler:
+    """nvidia-smi clocks line of B200_PROFILING.md sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def pinned_copy(a):
+    import torch
+    t = torch.empty(a.shape, dtype=torch.int32, pin_memory=True)
+    v = t.numpy().view(np.uint32)
+    v[...] = a
+    return t, v
+
+
+def run_reference(args, rank, world):
+    """The reference's own CPU implementation of the path (C++ restatement in oracle/: the Rust binary cannot be
+    built here), single thread like the reference, on a bounded cell slice of the same workload."""
+    if rank != 0:
+        return
+    from tests.oracle import Oracle
+    cfg = workload_config(args.workload, 1)
+    data = synth.generate(cfg)
+    n_s = min(args.cpu_sample_cells, data.n_cells)
+    keep = data.cell < n_s
+    orc = Oracle()
+    _, nnz_used = orc.load_cell_data(data.locus[keep], data.cell[keep], data.ref[keep], data.alt[keep], data.n_loci, n_s)
+    times = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        st = orc.compute_new_excluded(5.0)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            times.append(dt)
+        if not st.any_change:
+            orc.reset()
+    ms = 1e3 * sum(times) / len(times)
+    value = nnz_used / (ms * 1e-3)
+    sample = f"one EM iteration per step over the first {n_s} cells x all {data.n_loci} loci of {args.workload} ({nnz_used} scored nonzeros)"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": config_dict(args.workload, cfg, 1),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample,
+                             "host_cores": os.cpu_count()},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference = oracle/ C++ restatement of cellector (Rust toolchain absent); the reference is single-threaded (rayon declared, never used), so cores=1"}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(args, data):
+    from tests.oracle import Oracle
+    n_s = min(args.cpu_sample_cells * 2, data.n_cells)
+    keep = data.cell < n_s
+    orc = Oracle()
+    _, nnz_used = orc.load_cell_data(data.locus[keep], data.cell[keep], data.ref[keep], data.alt[keep], data.n_loci, n_s)
+    ts = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        orc.compute_new_excluded(5.0)
+        ts.append(time.perf_counter() - t0)
+    orc.close()
+    t = min(ts[1:])
+    return {"value": nnz_used / t, "unit": UNIT, "cores": 1, "kind": "port", "host_cores": os.cpu_count(),
+            "sample": f"one EM iteration over the first {n_s} cells x all loci of {args.workload} ({nnz_used} scored nonzeros, {t:.2f} s, best of 2 after warm-up)"}
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return 0
+    import torch
+    import torch.distributed as dist
+    from cellector_b200 import Cellector, api
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    cfg = workload_config(args.workload, world)
+    data = synth.generate(cfg, shard=rank, n_shards=world)
+    pins = [pinned_copy(a) for a in (data.locus, data.cell, data.ref, data.alt)]
+    host = [p[1] for p in pins]
+
+    lib = api.load_library()
+    ctx = Cellector(local_rank, api.FLAG_PROFILE | args.flags, lib)
+    if world > 1:
+        uid = [Cellector.nccl_unique_id(lib) if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(rank, world, uid[0])
+    n_loci_used, nnz_used = ctx.load_cell_data(*host, data.n_loci, data.n_cells)
+    nnz_total = sum_over_ranks(float(nnz_used))
+
+    def step():
+        ctx.flush_l2()
+        st = ctx.compute_new_excluded(5.0)
+        if not st.any_change:
+            ctx.reset()
+        return st
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    ctx.reset()
+    ctx.reset_phase_ms()
+    launches0 = ctx.launch_count()
+    barrier()
+    dev_ms, wall0 = [], time.perf_counter()
+    with ClockSampler(local_rank) as clocks:
+        for _ in range(args.steps):
+            dev_ms.append(step().device_ms)
+        barrier()
+    wall_ms = 1e3 * (time.perf_counter() - wall0) / args.steps
+    launches = ctx.launch_count() - launches0 - args.steps  # minus the untimed L2 flush kernels
+    ms_per_step = max_over_ranks(sum(dev_ms) / len(dev_ms))
+    value = nnz_total / (ms_per_step * 1e-3)
+    phases = ctx.phase_ms()
+
+    # roofline of the dominant kernel (per-cell scoring), timed with CUDA events on the library's stream
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    sc_ms, sc_n = phases["score"]
+    score_bytes = ctx.score_bytes()
+    achieved = score_bytes / (sc_ms / max(sc_n, 1) * 1e-3) / 1e9 if sc_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "per-cell scoring", "algorithmic_bytes_per_launch": score_bytes,
+                "kernel_us": 1e3 * sc_ms / max(sc_n, 1),
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)"}
+
+    # end to end through the C ABI with HOST buffers: load (H2D of the COO + GPU CSR/CSC build), EM to convergence,
+    # posteriors, and every per-cell / per-locus result copied back — the whole job a user of the CLI runs.
+    e2e = None
+    if not args.no_e2e:
+        n_e2e, ts, iters = max(3, min(args.steps, 5)), [], 0
+        for i in range(n_e2e + 1):
+            barrier()
+            t0 = time.perf_counter()
+            ctx.load_cell_data(*host, data.n_loci, data.n_cells)
+            stats = ctx.run_em(5.0)
+            cv, lv, pv = ctx.cell_vectors(), ctx.locus_vectors(), ctx.calculate_posteriors()
+            barrier()
+            if i > 0:
+                ts.append(time.perf_counter() - t0)
+            iters = len(stats)
+        t = max_over_ranks(sum(ts) / len(ts))
+        d2h = sum(v.nbytes for v in cv.values()) + sum(v.nbytes for v in lv.values()) + sum(v.nbytes for v in pv.values())
+        e2e = {"value": nnz_total * iters / t, "unit": UNIT, "h2d_bytes_per_step": int(sum(h.nbytes for h in host)),
+               "d2h_bytes_per_step": int(d2h), "seconds_per_job": t, "em_iterations_per_job": iters,
+               "what": "clx_load_coo from pinned host COO + EM to convergence + posteriors + all result vectors to host; value = scored nonzeros x EM iterations / job seconds"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(args, data)
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": config_dict(args.workload, cfg, world, {"nnz_scored_total": int(nnz_total), "loci_used": int(n_loci_used)}),
+                "wall_ms_per_step_incl_l2_flush": wall_ms, "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches),
+                "roofline": roofline, "cpu_baseline": cpu,
+                "phase_us_per_step": {k: 1e3 * v[0] / args.steps for k, v in phases.items()}}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,309 @@
+// abi.cu — the extern "C" surface of include/cellector_cuda.h: context lifetime, error plumbing, profiling
+// scopes and the host<->device copies at the boundary.  No exception or panic crosses this file.
+#include <math.h>
+#include <string.h>
+
+#include <new>
+
+#include "ctx.h"
+#include "numerics.cuh"
+
+namespace clx {
+
+static thread_local std::string g_create_error;
+
+int fail(clx_ctx* c, int code, const std::string& msg) {
+    if (c) c->err = msg;
+    else g_create_error = msg;
+    return code;
+}
+
+static cudaEvent_t get_event(clx_ctx* c) {
+    if (!c->event_pool.empty()) {
+        cudaEvent_t e = c->event_pool.back();
+        c->event_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+void phase_begin(clx_ctx* c, int phase) {
+    if (!(c->flags & CLX_FLAG_PROFILE)) return;
+    PendingEvent p{phase, get_event(c), get_event(c)};
+    cudaEventRecord(p.a, c->stream);
+    c->pending.push_back(p);
+}
+void phase_end(clx_ctx* c, int phase) {
+    if (!(c->flags & CLX_FLAG_PROFILE)) return;
+    for (size_t i = c->pending.size(); i-- > 0;) {
+        if (c->pending[i].phase == phase) {
+            cudaEventRecord(c->pending[i].b, c->stream);
+            return;
+        }
+    }
+}
+void phase_resolve(clx_ctx* c) {
+    for (auto& p : c->pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+            c->phase_ms[p.phase] += ms;
+            c->phase_launches[p.phase] += 1;
+        }
+        c->event_pool.push_back(p.a);
+        c->event_pool.push_back(p.b);
+    }
+    c->pending.clear();
+    cudaGetLastError();
+}
+
+template <typename T>
+static int d2h(clx_ctx* c, T* host, const T* dev, size_t n) {
+    if (!host || n == 0) return CLX_OK;
+    CLX_CUDA(c, cudaMemcpyAsync(host, dev, n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+    return CLX_OK;
+}
+
+__global__ void k_bits_to_bytes(const uint32_t* __restrict__ bits, uint32_t n, uint8_t* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (bits[i >> 5] >> (i & 31)) & 1u;
+}
+__global__ void k_u64_to_u32(const unsigned long long* __restrict__ in, uint32_t n, uint32_t* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (uint32_t)in[i];
+}
+__global__ void k_flush(uint4* __restrict__ p, size_t n, uint32_t v) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        p[i] = make_uint4(v, v, v, v);
+}
+
+}  // namespace clx
+
+using namespace clx;
+
+extern "C" {
+
+int clx_create(clx_ctx** out, int device, unsigned flags) {
+    if (!out) return CLX_ERR_ARG;
+    *out = nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+        return fail(nullptr, CLX_ERR_CUDA, std::string("no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= n_dev) return fail(nullptr, CLX_ERR_ARG, "device index out of range");
+    clx_ctx* c = new (std::nothrow) clx_ctx();
+    if (!c) return fail(nullptr, CLX_ERR_ARG, "out of host memory");
+    c->device = device;
+    c->flags = flags;
+#define CLX_CREATE_CUDA(call)                                                                          \
+    do {                                                                                               \
+        cudaError_t e__ = (call);                                                                      \
+        if (e__ != cudaSuccess) {                                                                      \
+            fail(nullptr, CLX_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));          \
+            delete c;                                                                                  \
+            return CLX_ERR_CUDA;                                                                       \
+        }                                                                                              \
+    } while (0)
+    CLX_CREATE_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CLX_CREATE_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        delete c;
+        return fail(nullptr, CLX_ERR_CUDA, "built for sm_100a (B200) only; device is sm_" + std::to_string(prop.major * 10 + prop.minor));
+    }
+    c->sm_count = prop.multiProcessorCount;
+    CLX_CREATE_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CLX_CREATE_CUDA(cudaEventCreate(&c->ev_iter_a));
+    CLX_CREATE_CUDA(cudaEventCreate(&c->ev_iter_b));
+    CLX_CREATE_CUDA(c->d_stats.alloc(1));
+    CLX_CREATE_CUDA(cudaMallocHost((void**)&c->h_stats, sizeof(DeviceStats)));
+    memset(c->h_stats, 0, sizeof(DeviceStats));
+    // ln(i!) for i <= 170 exactly like statrs: ln of the f64 running product (glibc log, as the Rust binary uses)
+    double lnfact[171], f = 1.0;
+    lnfact[0] = log(1.0);
+    for (int i = 1; i <= 170; ++i) {
+        f = f * (double)i;
+        lnfact[i] = log(f);
+    }
+    for (int n = 0; n <= 3; ++n)
+        for (int a = 0; a <= n; ++a) c->lbc10[lbc_idx(a, n)] = lnfact[n] - lnfact[a] - lnfact[n - a];
+    CLX_CREATE_CUDA(c->lnfact.alloc(171));
+    CLX_CREATE_CUDA(cudaMemcpy(c->lnfact.p, lnfact, sizeof(lnfact), cudaMemcpyHostToDevice));
+#undef CLX_CREATE_CUDA
+    *out = c;
+    return CLX_OK;
+}
+
+void clx_destroy(clx_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    comm_destroy(c);
+    phase_resolve(c);
+    for (cudaEvent_t e : c->event_pool) cudaEventDestroy(e);
+    if (c->ev_iter_a) cudaEventDestroy(c->ev_iter_a);
+    if (c->ev_iter_b) cudaEventDestroy(c->ev_iter_b);
+    if (c->h_stats) cudaFreeHost(c->h_stats);
+    clx::DevBuf<uint8_t>* dummy = nullptr;
+    (void)dummy;
+#define R(x) c->x.release()
+    R(locus_ids); R(csr); R(row_ptr); R(csc); R(col_ptr); R(locus_tot); R(h_cell); R(h_locus); R(h_ref); R(h_alt);
+    R(h_row_ptr); R(hc_perm); R(hc_col_ptr); R(hv_ll); R(hv_e); R(coo_locus); R(coo_cell); R(coo_ref); R(coo_alt);
+    R(lnfact); R(excl_bits); R(excl_bits_new); R(loci_used); R(min_cnt); R(tab); R(ll); R(ell); R(norm); R(nloci);
+    R(norm_all); R(sel_keys); R(sel_hist); R(sel_state); R(loc_ll); R(loc_int); R(post); R(post_u8); R(d_stats);
+    R(flush_buf);
+#undef R
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char* clx_last_error(const clx_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int clx_nccl_unique_id(void* out128) { return out128 ? comm_unique_id(out128) : CLX_ERR_ARG; }
+
+int clx_comm_init(clx_ctx* c, int rank, int world, const void* id) {
+    if (!c) return CLX_ERR_ARG;
+    return comm_init(c, rank, world, id);
+}
+
+int clx_load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, const uint32_t* locus,
+                 const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt,
+                 uint32_t* n_loci_used, uint64_t* nnz_used) {
+    if (!c) return CLX_ERR_ARG;
+    cudaSetDevice(c->device);
+    CLX_TRY(load_coo(c, nnz0, n_loci0, n_cells, locus, cell, ref, alt, min_ref, min_alt));
+    if (n_loci_used) *n_loci_used = c->n_loci;
+    if (nnz_used) *nnz_used = c->nnz;
+    return CLX_OK;
+}
+
+int clx_get_locus_ids(clx_ctx* c, uint32_t* ids) {
+    if (!c || !c->loaded) return c ? fail(c, CLX_ERR_STATE, "not loaded") : CLX_ERR_ARG;
+    CLX_TRY(d2h(c, ids, c->locus_ids.p, c->n_loci));
+    CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return CLX_OK;
+}
+
+int clx_reset(clx_ctx* c) {
+    if (!c || !c->loaded) return c ? fail(c, CLX_ERR_STATE, "not loaded") : CLX_ERR_ARG;
+    return em_reset(c);
+}
+
+int clx_em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
+    if (!c) return CLX_ERR_ARG;
+    return em_iteration(c, iqr_multiple, out);
+}
+
+int clx_get_cell_vectors(clx_ctx* c, double* ll, double* expected_ll, uint32_t* n_loci, double* norm, uint8_t* excluded) {
+    if (!c || !c->loaded) return c ? fail(c, CLX_ERR_STATE, "not loaded") : CLX_ERR_ARG;
+    if (!c->have_iteration) return fail(c, CLX_ERR_STATE, "no iteration run yet");
+    const uint32_t N = c->n_cells;
+    CLX_TRY(d2h(c, ll, c->ll.p, N));
+    CLX_TRY(d2h(c, expected_ll, c->ell.p, N));
+    CLX_TRY(d2h(c, n_loci, c->nloci.p, N));
+    CLX_TRY(d2h(c, norm, c->norm.p, N));
+    if (excluded && N) {
+        k_bits_to_bytes<<<(N + 255) / 256, 256, 0, c->stream>>>(c->excl_bits.p, N, c->post_u8.p);
+        c->launches++;
+        CLX_TRY(d2h(c, excluded, c->post_u8.p, N));
+    }
+    CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return CLX_OK;
+}
+
+int clx_get_locus_vectors(clx_ctx* c, const clx_locus_arrays* o) {
+    if (!c || !o) return CLX_ERR_ARG;
+    if (!c->loaded || !c->have_iteration) return fail(c, CLX_ERR_STATE, "no iteration run yet");
+    const size_t L = c->n_loci;
+    CLX_TRY(d2h(c, o->ll_minority, c->loc_ll.p, L));
+    CLX_TRY(d2h(c, o->ll_majority, c->loc_ll.p + L, L));
+    clx::DevBuf<uint32_t> tmp;
+    if ((o->cells_minority || o->cells_majority) && L) {
+        CLX_CUDA(c, tmp.alloc(2 * L));
+        k_u64_to_u32<<<(unsigned)((2 * L + 255) / 256), 256, 0, c->stream>>>(c->loc_int.p, (uint32_t)(2 * L), tmp.p);
+        c->launches++;
+        CLX_TRY(d2h(c, o->cells_minority, tmp.p, L));
+        CLX_TRY(d2h(c, o->cells_majority, tmp.p + L, L));
+    }
+    CLX_TRY(d2h(c, (unsigned long long*)o->ref_minority, c->loc_int.p + 2 * L, L));
+    CLX_TRY(d2h(c, (unsigned long long*)o->alt_minority, c->loc_int.p + 3 * L, L));
+    CLX_TRY(d2h(c, (unsigned long long*)o->ref_majority, c->loc_int.p + 4 * L, L));
+    CLX_TRY(d2h(c, (unsigned long long*)o->alt_majority, c->loc_int.p + 5 * L, L));
+    CLX_TRY(d2h(c, o->loci_used, c->loci_used.p, L));
+    CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+    tmp.release();
+    return CLX_OK;
+}
+
+int clx_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used, double* posterior,
+                   double* doublet_posterior, double* ll_major, double* ll_minor, uint8_t* label, uint8_t* anomaly,
+                   uint8_t* qual) {
+    if (!c) return CLX_ERR_ARG;
+    CLX_TRY(em_posteriors(c, posterior_threshold, min_loci_used));
+    const size_t N = c->n_cells;
+    CLX_TRY(d2h(c, posterior, c->post.p, N));
+    CLX_TRY(d2h(c, doublet_posterior, c->post.p + N, N));
+    CLX_TRY(d2h(c, ll_minor, c->ll.p, N));
+    CLX_TRY(d2h(c, ll_major, c->ll.p + N, N));
+    CLX_TRY(d2h(c, label, c->post_u8.p, N));
+    CLX_TRY(d2h(c, anomaly, c->post_u8.p + N, N));
+    CLX_TRY(d2h(c, qual, c->post_u8.p + 2 * N, N));
+    CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return CLX_OK;
+}
+
+int clx_final_locus_counts(clx_ctx* c, uint64_t* minority_ref_alt, uint64_t* majority_ref_alt) {
+    if (!c || !minority_ref_alt || !majority_ref_alt) return CLX_ERR_ARG;
+    if (!c->loaded) return fail(c, CLX_ERR_STATE, "not loaded");
+    const size_t n = 2 * (size_t)c->n_loci0;
+    clx::DevBuf<unsigned long long> mn, mj;
+    CLX_CUDA(c, mn.alloc(n + 1));
+    CLX_CUDA(c, mj.alloc(n + 1));
+    int rc = em_final_locus_counts(c, mn.p, mj.p);
+    if (rc == CLX_OK) {
+        cudaMemcpy(minority_ref_alt, mn.p, n * 8, cudaMemcpyDeviceToHost);
+        cudaMemcpy(majority_ref_alt, mj.p, n * 8, cudaMemcpyDeviceToHost);
+    }
+    mn.release();
+    mj.release();
+    return rc;
+}
+
+int clx_get_phase_ms(clx_ctx* c, int phase, double* total_ms, uint64_t* launches) {
+    if (!c || phase < 0 || phase >= CLX_PHASE_COUNT) return CLX_ERR_ARG;
+    if (total_ms) *total_ms = c->phase_ms[phase];
+    if (launches) *launches = c->phase_launches[phase];
+    return CLX_OK;
+}
+int clx_reset_phase_ms(clx_ctx* c) {
+    if (!c) return CLX_ERR_ARG;
+    for (int i = 0; i < CLX_PHASE_COUNT; ++i) {
+        c->phase_ms[i] = 0;
+        c->phase_launches[i] = 0;
+    }
+    return CLX_OK;
+}
+void* clx_get_stream(clx_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int clx_score_bytes(clx_ctx* c, uint64_t* bytes) {
+    if (!c || !bytes || !c->loaded) return CLX_ERR_ARG;
+    *bytes = c->score_bytes;
+    return CLX_OK;
+}
+int clx_launch_count(clx_ctx* c, uint64_t* launches) {
+    if (!c || !launches) return CLX_ERR_ARG;
+    *launches = c->launches;
+    return CLX_OK;
+}
+int clx_flush_l2(clx_ctx* c) {
+    if (!c) return CLX_ERR_ARG;
+    const size_t bytes = 512ull << 20;  // 4x the 126 MB L2
+    if (!c->flush_buf.p) CLX_CUDA(c, c->flush_buf.alloc(bytes));
+    static uint32_t v = 0;
+    k_flush<<<c->sm_count * 8, 256, 0, c->stream>>>((uint4*)c->flush_buf.p, bytes / 16, ++v);
+    CLX_CUDA(c, cudaGetLastError());
+    return CLX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,167 @@
+// ctx.h — internal context of libcellector_cuda.so (one GPU, one stream, optionally one NCCL rank).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/cellector_cuda.h"
+
+namespace clx {
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        release();
+        n = count;
+        if (count == 0) return cudaSuccess;
+        return cudaMalloc((void**)&p, count * sizeof(T));
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    size_t bytes() const { return n * sizeof(T); }
+};
+
+// packed nonzero of the CSR (by cell) matrix: used-locus index + u16 counts (0xFFFF/0xFFFF = "see heavy list")
+struct __align__(8) RowEntry {
+    uint32_t locus;
+    uint16_t ref, alt;
+};
+// packed nonzero of the CSC (by locus) matrix
+struct __align__(8) ColEntry {
+    uint32_t cell;
+    uint16_t ref, alt;
+};
+
+struct DeviceStats {  // written by kernels, copied to pinned host memory once per iteration
+    double median, q1, q3, iqr, threshold;
+    unsigned long long n_new, n_rescued, n_excluded, n_loci_filtered, n_loci_in_use;
+    unsigned int nan_flag, pad;
+};
+
+struct NcclApi;  // comm.cu
+
+struct PendingEvent {
+    int phase;
+    cudaEvent_t a, b;
+};
+
+}  // namespace clx
+
+struct clx_ctx {
+    std::string err;
+    int device = 0;
+    unsigned flags = 0;
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    uint64_t launches = 0;
+    uint64_t score_bytes = 0;  // algorithmic bytes of one launch of the scoring kernel
+
+    // --- communicator (comm.cu)
+    int rank = 0, world = 1;
+    void* nccl_comm = nullptr;
+
+    // --- matrix (load.cu)
+    bool loaded = false;
+    uint32_t n_cells = 0;          // local cells
+    uint64_t n_cells_global = 0;   // over all ranks
+    uint64_t cell_offset = 0;      // global id of local cell 0
+    uint32_t n_loci0 = 0, n_loci = 0;
+    uint64_t nnz0 = 0, nnz = 0;
+    uint64_t n_heavy = 0;
+    clx::DevBuf<uint32_t> locus_ids;          // [n_loci] used -> original
+    clx::DevBuf<clx::RowEntry> csr;           // [nnz] rows = cells, file order inside a row
+    clx::DevBuf<uint64_t> row_ptr;            // [n_cells + 1]
+    clx::DevBuf<clx::ColEntry> csc;           // [nnz] columns = used loci, cells ascending inside a column
+    clx::DevBuf<uint64_t> col_ptr;            // [n_loci + 1]
+    clx::DevBuf<unsigned long long> locus_tot;  // [2 * n_loci] (ref, alt) totals over all ranks
+    // heavy entries (total > K_LIGHT or a count that does not fit u16), CSR order
+    clx::DevBuf<uint32_t> h_cell, h_locus, h_ref, h_alt;  // [n_heavy]
+    clx::DevBuf<uint32_t> h_row_ptr;                      // [n_cells + 1]
+    clx::DevBuf<uint32_t> hc_perm;                        // [n_heavy] CSC order -> index into the CSR-order lists
+    clx::DevBuf<uint32_t> hc_col_ptr;                     // [n_loci + 1]
+    clx::DevBuf<double> hv_ll, hv_e;                      // [3 * n_heavy] values of the current scoring pass
+    // retained COO for clx_final_locus_counts
+    clx::DevBuf<uint32_t> coo_locus, coo_cell, coo_ref, coo_alt;
+    clx::DevBuf<double> lnfact;  // [171]
+    double lbc10[10];
+
+    // --- EM state (em.cu)
+    uint32_t iteration = 0;
+    uint64_t n_excluded_global = 0;  // size of the current excluded set over all ranks
+    bool have_iteration = false;
+    clx::DevBuf<uint32_t> excl_bits, excl_bits_new;   // [(n_cells + 31) / 32]
+    clx::DevBuf<uint8_t> loci_used;                   // [n_loci]
+    clx::DevBuf<unsigned long long> min_cnt;          // [2 * n_loci] minority (ref, alt) over all stored entries
+    clx::DevBuf<double> tab;                          // [3][n_loci][16] memo tables (slot 0 = EM, 0..2 = posteriors)
+    clx::DevBuf<double> ll, ell, norm;                // [n_cells] (+ ll for 3 tables in the posterior pass)
+    clx::DevBuf<uint32_t> nloci;                      // [n_cells]
+    clx::DevBuf<double> norm_all;                     // [world * max_local] gathered normalized values (world > 1)
+    clx::DevBuf<uint64_t> sel_keys;                   // select scratch
+    clx::DevBuf<unsigned int> sel_hist;               // select scratch
+    clx::DevBuf<unsigned long long> sel_state;        // select scratch
+    // per-locus outputs of the column pass: packed for one allreduce each
+    clx::DevBuf<double> loc_ll;                       // [2 * n_loci] (minority, majority)
+    clx::DevBuf<unsigned long long> loc_int;          // [6 * n_loci] cells_min, cells_maj, ref_min, alt_min, ref_maj, alt_maj
+    clx::DevBuf<double> post;                         // [5 * n_cells] posterior pass outputs
+    clx::DevBuf<uint8_t> post_u8;                     // [3 * n_cells]
+    clx::DevBuf<clx::DeviceStats> d_stats;
+    clx::DeviceStats* h_stats = nullptr;              // pinned
+    clx::DevBuf<uint8_t> flush_buf;
+    uint32_t max_local_cells = 0;
+
+    // --- profiling
+    std::vector<clx::PendingEvent> pending;
+    std::vector<cudaEvent_t> event_pool;
+    double phase_ms[CLX_PHASE_COUNT] = {0};
+    uint64_t phase_launches[CLX_PHASE_COUNT] = {0};
+    cudaEvent_t ev_iter_a = nullptr, ev_iter_b = nullptr;
+};
+
+namespace clx {
+
+int fail(clx_ctx* c, int code, const std::string& msg);
+#define CLX_CUDA(ctx, call)                                                                              \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess)                                                                          \
+            return clx::fail(ctx, CLX_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));    \
+    } while (0)
+#define CLX_TRY(call)                 \
+    do {                              \
+        int rc__ = (call);            \
+        if (rc__ != CLX_OK) return rc__; \
+    } while (0)
+
+// profiling scopes (no-ops unless CLX_FLAG_PROFILE)
+void phase_begin(clx_ctx* c, int phase);
+void phase_end(clx_ctx* c, int phase);
+void phase_resolve(clx_ctx* c);  // after a stream sync
+
+// comm.cu — collectives on ctx->stream; no-ops when world == 1
+int comm_allreduce_u32(clx_ctx* c, unsigned int* buf, size_t n);
+int comm_allreduce_u64(clx_ctx* c, unsigned long long* buf, size_t n);
+int comm_allreduce_f64(clx_ctx* c, double* buf, size_t n);
+int comm_allgather_f64(clx_ctx* c, const double* send, double* recv, size_t n_per_rank);
+int comm_allgather_u64_host(clx_ctx* c, uint64_t v, std::vector<uint64_t>* out);
+void comm_destroy(clx_ctx* c);
+int comm_unique_id(void* out128);
+int comm_init(clx_ctx* c, int rank, int world, const void* id128);
+
+// load.cu
+int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, const uint32_t* locus,
+             const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt);
+// em.cu
+int em_alloc(clx_ctx* c);
+int em_reset(clx_ctx* c);
+int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out);
+int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used);
+int em_final_locus_counts(clx_ctx* c, unsigned long long* d_min, unsigned long long* d_maj);
+
+}  // namespace clx

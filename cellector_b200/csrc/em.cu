@@ -1,0 +1,348 @@
+// em.cu — host orchestration of one EM iteration (compute_new_excluded, cellector/src/main.rs:308-347), the
+// posterior pass (calculate_posteriors, main.rs:228-280) and the final per-locus counts (load_data.rs:109-132).
+// Everything runs on ctx->stream; one stream synchronisation per iteration (to read ~100 bytes of scalars).
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "ctx.h"
+#include "em_kernels.cuh"
+#include "numerics.cuh"
+#include "select_kernels.cuh"
+
+namespace clx {
+namespace {
+
+constexpr int TPB = 256;
+
+int pick_group(double avg_len) {
+    // lanes per row/column: each lane should see >= ~8 two-entry loads
+    int g = 4;
+    while (g < 32 && avg_len > 16.0 * g) g <<= 1;
+    return g;
+}
+
+Lbc10 make_lbc(const clx_ctx* c) {
+    Lbc10 l;
+    for (int i = 0; i < 10; ++i) l.v[i] = c->lbc10[i];
+    return l;
+}
+
+template <int NT, bool WITH_E>
+void launch_score_rows(clx_ctx* c, int G, const uint8_t* used) {
+    const uint32_t n = c->n_cells;
+    if (n == 0) return;
+#define CLX_SCORE(GG)                                                                                                  \
+    k_score_rows<GG, NT, WITH_E><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                 \
+        c->csr.p, c->row_ptr.p, n, c->tab.p, c->n_loci, used, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p,                   \
+        (uint32_t)c->n_heavy, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag)
+    switch (G) {
+        case 4: CLX_SCORE(4); break;
+        case 8: CLX_SCORE(8); break;
+        case 16: CLX_SCORE(16); break;
+        default: CLX_SCORE(32); break;
+    }
+#undef CLX_SCORE
+    c->launches++;
+}
+
+void launch_columns(clx_ctx* c, int G) {
+    const uint32_t n = c->n_loci;
+    if (n == 0) return;
+#define CLX_COLS(GG)                                                                                                   \
+    k_columns<GG><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                                \
+        c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits_new.p, c->hc_col_ptr.p, c->hc_perm.p,        \
+        c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hv_ll.p, c->loc_ll.p, c->loc_int.p)
+    switch (G) {
+        case 4: CLX_COLS(4); break;
+        case 8: CLX_COLS(8); break;
+        case 16: CLX_COLS(16); break;
+        default: CLX_COLS(32); break;
+    }
+#undef CLX_COLS
+    c->launches++;
+}
+
+// ranks + interpolation weights of statrs' Data::{median, quantile} for n values
+void quantile_plan(uint64_t n, double tau, unsigned long long* ra, unsigned long long* rb, double* frac, int* mode) {
+    *ra = *rb = 0;
+    *frac = 0.0;
+    *mode = 1;
+    if (n == 0) return;
+    const double h = ((double)n + 1.0 / 3.0) * tau + 1.0 / 3.0;
+    const long long hf = (long long)h;
+    if (hf <= 0) { *mode = 1; return; }
+    if (hf >= (long long)n) { *mode = 2; *ra = *rb = n - 1; return; }
+    *mode = 0;
+    *ra = (unsigned long long)hf - 1;
+    *rb = (unsigned long long)hf < n - 1 ? (unsigned long long)hf : n - 1;
+    *frac = h - (double)hf;
+}
+
+SelectPlan make_plan(uint64_t n) {
+    SelectPlan p;
+    memset(&p, 0, sizeof(p));
+    p.n = n;
+    if (n) {
+        const uint64_t k = n / 2;
+        p.median_even = (n % 2 == 0) ? 1 : 0;
+        p.rank[0] = p.median_even ? k - 1 : k;
+        p.rank[1] = k;
+    }
+    quantile_plan(n, 0.25, &p.rank[2], &p.rank[3], &p.frac_q1, &p.q1_mode);
+    quantile_plan(n, 0.75, &p.rank[4], &p.rank[5], &p.frac_q3, &p.q3_mode);
+    return p;
+}
+
+// exact order statistics of `vals[0, n_vals)` (pads = +inf beyond the n real values) -> d_stats
+int run_select(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t n_real, double iqr_multiple) {
+    const SelectPlan plan = make_plan(n_real);
+    cudaStream_t s = c->stream;
+    if (n_vals <= SELECT_SMALL_MAX) {
+        uint32_t p2 = 2;
+        while (p2 < n_vals) p2 <<= 1;
+        k_select_small<<<1, 1024, (size_t)p2 * 8, s>>>(vals, (uint32_t)n_vals, p2, plan, iqr_multiple, c->d_stats.p);
+        c->launches++;
+        return CLX_OK;
+    }
+    unsigned long long* keys = (unsigned long long*)c->sel_keys.p;
+    SelectState init;
+    for (int t = 0; t < SELECT_TARGETS; ++t) {
+        init.prefix[t] = 0;
+        init.rank[t] = plan.rank[t];
+    }
+    SelectState* d_state = (SelectState*)c->sel_state.p;
+    unsigned int* hist = c->sel_hist.p;
+    unsigned int* ticket = hist + 8 * SELECT_TARGETS * 256;
+    CLX_CUDA(c, cudaMemcpyAsync(d_state, &init, sizeof(init), cudaMemcpyHostToDevice, s));
+    CLX_CUDA(c, cudaMemsetAsync(hist, 0, c->sel_hist.bytes(), s));
+    const unsigned grid = (unsigned)std::min<uint64_t>((n_vals + 512 * 8 - 1) / (512 * 8), (uint64_t)c->sm_count * 2);
+    k_select_keys<<<grid, 512, 0, s>>>(vals, n_vals, keys);
+    for (int pass = 0; pass < 8; ++pass)
+        k_select_pass<<<grid, 512, 0, s>>>(keys, n_vals, pass, d_state, hist, ticket, plan, iqr_multiple, c->d_stats.p);
+    c->launches += 9;
+    return CLX_OK;
+}
+
+}  // namespace
+
+int em_alloc(clx_ctx* c) {
+    const size_t N = c->n_cells, L = c->n_loci;
+    const size_t words = (N + 31) / 32 + 1;
+    CLX_CUDA(c, c->excl_bits.alloc(words));
+    CLX_CUDA(c, c->excl_bits_new.alloc(words));
+    CLX_CUDA(c, c->loci_used.alloc(L + 1));
+    CLX_CUDA(c, c->tab.alloc(3 * L * TAB_STRIDE + TAB_STRIDE));
+    CLX_CUDA(c, c->ll.alloc(3 * N + 1));
+    CLX_CUDA(c, c->ell.alloc(N + 1));
+    const size_t norm_n = std::max<size_t>(N, c->max_local_cells) + 1;
+    CLX_CUDA(c, c->norm.alloc(norm_n));
+    CLX_CUDA(c, c->nloci.alloc(N + 1));
+    CLX_CUDA(c, c->loc_ll.alloc(2 * L + 1));
+    CLX_CUDA(c, c->loc_int.alloc(8 * L + 1));
+    CLX_CUDA(c, c->post.alloc(2 * N + 1));
+    CLX_CUDA(c, c->post_u8.alloc(3 * N + 1));
+    const size_t n_sel = c->world > 1 ? (size_t)c->world * c->max_local_cells : N;
+    if (c->world > 1) CLX_CUDA(c, c->norm_all.alloc(n_sel + 1));
+    if (n_sel > SELECT_SMALL_MAX) CLX_CUDA(c, c->sel_keys.alloc(n_sel));
+    CLX_CUDA(c, c->sel_hist.alloc(8 * SELECT_TARGETS * 256 + 8));
+    CLX_CUDA(c, c->sel_state.alloc(sizeof(SelectState) / 8 + 1));
+    // pads of the gather buffer: +inf sorts after every real value
+    {
+        std::vector<double> inf(norm_n, INFINITY);
+        CLX_CUDA(c, cudaMemcpyAsync(c->norm.p, inf.data(), norm_n * 8, cudaMemcpyHostToDevice, c->stream));
+        CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    CLX_CUDA(c, cudaFuncSetAttribute(k_select_small, cudaFuncAttributeMaxDynamicSharedMemorySize, SELECT_SMALL_MAX * 8));
+    // roofline accounting of the v0 scoring kernel: packed entries + row pointers + outputs + table
+    c->score_bytes = 8ull * c->nnz + 8ull * (N + 1) + 20ull * N + 128ull * L;
+    return em_reset(c);
+}
+
+int em_reset(clx_ctx* c) {
+    cudaStream_t s = c->stream;
+    CLX_CUDA(c, cudaMemsetAsync(c->excl_bits.p, 0, c->excl_bits.bytes(), s));
+    CLX_CUDA(c, cudaMemsetAsync(c->excl_bits_new.p, 0, c->excl_bits_new.bytes(), s));
+    CLX_CUDA(c, cudaMemsetAsync(c->loci_used.p, 1, c->loci_used.bytes(), s));
+    CLX_CUDA(c, cudaMemsetAsync(c->loc_int.p, 0, c->loc_int.bytes(), s));
+    CLX_CUDA(c, cudaMemsetAsync(c->loc_ll.p, 0, c->loc_ll.bytes(), s));
+    CLX_CUDA(c, cudaStreamSynchronize(s));
+    c->iteration = 0;
+    c->have_iteration = false;
+    c->n_excluded_global = 0;
+    return CLX_OK;
+}
+
+int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
+    if (!c->loaded) return fail(c, CLX_ERR_STATE, "clx_em_iteration before clx_load_coo");
+    cudaStream_t s = c->stream;
+    const uint32_t N = c->n_cells, L = c->n_loci;
+    const int with_e = (c->flags & CLX_FLAG_NO_EXPECTED) ? 0 : 1;
+    CLX_CUDA(c, cudaEventRecord(c->ev_iter_a, s));
+    CLX_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, sizeof(DeviceStats), s));
+
+    // 1. alpha/beta + memo tables from the CURRENT excluded set (main.rs:309)
+    phase_begin(c, CLX_PHASE_TABLES);
+    if (L) {
+        k_tables<0><<<(L + 127) / 128, 128, 0, s>>>(c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L,
+                                                   L, make_lbc(c), 0.0, 0.0, with_e, c->tab.p);
+        c->launches++;
+    }
+    phase_end(c, CLX_PHASE_TABLES);
+
+    // 2. heavy entries, then the per-cell scoring pass (main.rs:312)
+    phase_begin(c, CLX_PHASE_HEAVY);
+    if (c->n_heavy) {
+        k_heavy<1><<<(unsigned)((c->n_heavy + 127) / 128), 128, 0, s>>>(c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy,
+                                                                      c->tab.p, L, c->loci_used.p, c->lnfact.p, with_e,
+                                                                      c->hv_ll.p, c->hv_e.p);
+        c->launches++;
+    }
+    phase_end(c, CLX_PHASE_HEAVY);
+    phase_begin(c, CLX_PHASE_SCORE);
+    {
+        const int G = pick_group(N ? (double)c->nnz / N : 0.0);
+        if (with_e) launch_score_rows<1, true>(c, G, c->loci_used.p);
+        else launch_score_rows<1, false>(c, G, c->loci_used.p);
+    }
+    phase_end(c, CLX_PHASE_SCORE);
+
+    // 3. threshold from exact order statistics of the normalized log likelihoods (main.rs:313-329)
+    const double* sel_vals = c->norm.p;
+    uint64_t n_vals = N;
+    if (c->world > 1) {
+        phase_begin(c, CLX_PHASE_COMM);
+        CLX_TRY(comm_allgather_f64(c, c->norm.p, c->norm_all.p, c->max_local_cells));
+        phase_end(c, CLX_PHASE_COMM);
+        sel_vals = c->norm_all.p;
+        n_vals = (uint64_t)c->world * c->max_local_cells;
+    }
+    phase_begin(c, CLX_PHASE_SELECT);
+    CLX_TRY(run_select(c, sel_vals, n_vals, c->n_cells_global, iqr_multiple));
+    // 4. new excluded set + change counts (main.rs:330-335)
+    if (N) {
+        k_exclude<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->norm.p, N, c->excl_bits.p, c->excl_bits_new.p, c->d_stats.p);
+        c->launches++;
+    }
+    phase_end(c, CLX_PHASE_SELECT);
+    if (c->world > 1) {
+        phase_begin(c, CLX_PHASE_COMM);
+        CLX_TRY(comm_allreduce_u64(c, &c->d_stats.p->n_new, 3));
+        phase_end(c, CLX_PHASE_COMM);
+    }
+
+    // 5. per-locus contributions split by the NEW set (main.rs:343) + minority allele counts for the next alpha/beta
+    phase_begin(c, CLX_PHASE_COLUMN);
+    launch_columns(c, pick_group(L ? (double)c->nnz / L : 0.0));
+    phase_end(c, CLX_PHASE_COLUMN);
+    if (c->world > 1) {
+        phase_begin(c, CLX_PHASE_COMM);
+        CLX_TRY(comm_allreduce_f64(c, c->loc_ll.p, 2 * (size_t)L));
+        CLX_TRY(comm_allreduce_u64(c, c->loc_int.p, 8 * (size_t)L));
+        phase_end(c, CLX_PHASE_COMM);
+    }
+    // 6. the -80 locus filter (main.rs:444-451)
+    phase_begin(c, CLX_PHASE_COLUMN);
+    if (L) {
+        k_locus_filter<<<(L + TPB - 1) / TPB, TPB, 0, s>>>(c->loc_ll.p, c->loc_int.p, L, c->loci_used.p, c->d_stats.p);
+        c->launches++;
+    }
+    phase_end(c, CLX_PHASE_COLUMN);
+
+    CLX_CUDA(c, cudaMemcpyAsync(c->h_stats, c->d_stats.p, sizeof(DeviceStats), cudaMemcpyDeviceToHost, s));
+    CLX_CUDA(c, cudaEventRecord(c->ev_iter_b, s));
+    CLX_CUDA(c, cudaStreamSynchronize(s));
+    CLX_CUDA(c, cudaGetLastError());
+    phase_resolve(c);
+    std::swap(c->excl_bits.p, c->excl_bits_new.p);
+    const DeviceStats& st = *c->h_stats;
+    if (st.nan_flag) return fail(c, CLX_ERR_NAN, "NaN normalized log likelihood (the reference panics in argsort, main.rs:504)");
+    c->n_excluded_global = st.n_excluded;
+    if (out) {
+        memset(out, 0, sizeof(*out));
+        out->any_change = (st.n_new > 0 || st.n_rescued > 0) ? 1 : 0;
+        out->iteration = c->iteration;
+        out->n_new_excluded = st.n_new;
+        out->n_rescued = st.n_rescued;
+        out->n_excluded = st.n_excluded;
+        out->median = st.median;
+        out->q1 = st.q1;
+        out->q3 = st.q3;
+        out->iqr = st.iqr;
+        out->threshold = st.threshold;
+        out->n_loci_filtered = st.n_loci_filtered;
+        out->n_loci_in_use = st.n_loci_in_use;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, c->ev_iter_a, c->ev_iter_b);
+        out->device_ms = ms;
+    }
+    c->iteration++;
+    c->have_iteration = true;
+    return CLX_OK;
+}
+
+int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used) {
+    if (!c->loaded) return fail(c, CLX_ERR_STATE, "clx_posteriors before clx_load_coo");
+    cudaStream_t s = c->stream;
+    const uint32_t N = c->n_cells, L = c->n_loci;
+    // main.rs:240, 250, 259-265 — scalars on the host in the reference's expression order
+    const double n_cells = (double)c->n_cells_global;
+    double mf = ((double)c->n_excluded_global + 1.0) / (n_cells + 1.0);
+    const double mf_unclamped = mf;
+    mf = fmax(mf, 0.01);
+    PosteriorParams pp;
+    pp.log_prior_doublet = log(n_cells / 1000.0 / 100.0 * fmax(mf, 0.1));
+    pp.log_prior_minority = log(mf);
+    pp.log_prior_majority = log(1.0 - mf);
+    pp.posterior_threshold = posterior_threshold;
+    pp.min_loci_used = min_loci_used;
+
+    phase_begin(c, CLX_PHASE_TABLES);
+    if (L) {
+        k_tables<1><<<(unsigned)((3ull * L + 127) / 128), 128, 0, s>>>(c->locus_tot.p, c->loc_int.p + 6 * (size_t)L,
+                                                                     c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), mf_unclamped,
+                                                                     mf, 0, c->tab.p);
+        c->launches++;
+    }
+    phase_end(c, CLX_PHASE_TABLES);
+    phase_begin(c, CLX_PHASE_HEAVY);
+    if (c->n_heavy) {
+        k_heavy<3><<<(unsigned)((c->n_heavy + 127) / 128), 128, 0, s>>>(c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy,
+                                                                      c->tab.p, L, nullptr, c->lnfact.p, 0, c->hv_ll.p, c->hv_e.p);
+        c->launches++;
+    }
+    phase_end(c, CLX_PHASE_HEAVY);
+    // get_loci_used_for_posterior_calc pushes true on both branches (main.rs:301-303): every locus is scored
+    phase_begin(c, CLX_PHASE_SCORE);
+    launch_score_rows<3, false>(c, pick_group(N ? (double)c->nnz / N : 0.0), nullptr);
+    phase_end(c, CLX_PHASE_SCORE);
+    if (N) {
+        k_posterior<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->ll.p, N, c->row_ptr.p, c->excl_bits.p, pp, c->post.p, c->post_u8.p);
+        c->launches++;
+    }
+    CLX_CUDA(c, cudaStreamSynchronize(s));
+    CLX_CUDA(c, cudaGetLastError());
+    phase_resolve(c);
+    // the EM memo table in slot 0 is stale now; the next clx_em_iteration rebuilds it anyway
+    return CLX_OK;
+}
+
+int em_final_locus_counts(clx_ctx* c, unsigned long long* d_min, unsigned long long* d_maj) {
+    if (!c->coo_locus.p && c->nnz0) return fail(c, CLX_ERR_STATE, "clx_final_locus_counts needs CLX_FLAG_KEEP_COO at clx_create");
+    cudaStream_t s = c->stream;
+    CLX_CUDA(c, cudaMemsetAsync(d_min, 0, 2 * (size_t)c->n_loci0 * 8, s));
+    CLX_CUDA(c, cudaMemsetAsync(d_maj, 0, 2 * (size_t)c->n_loci0 * 8, s));
+    if (c->nnz0) {
+        const unsigned grid = (unsigned)std::min<uint64_t>((c->nnz0 + TPB - 1) / TPB, (uint64_t)c->sm_count * 16);
+        k_final_counts<<<grid, TPB, 0, s>>>(c->coo_locus.p, c->coo_cell.p, c->coo_ref.p, c->coo_alt.p, c->nnz0, c->excl_bits.p,
+                                            d_min, d_maj);
+        c->launches++;
+    }
+    CLX_TRY(comm_allreduce_u64(c, d_min, 2 * (size_t)c->n_loci0));
+    CLX_TRY(comm_allreduce_u64(c, d_maj, 2 * (size_t)c->n_loci0));
+    CLX_CUDA(c, cudaStreamSynchronize(s));
+    return CLX_OK;
+}
+
+}  // namespace clx

@@ -1,0 +1,366 @@
+// load.cu — device-side replacement of load_data::load_cell_data (cellector/src/load_data.rs:134-181):
+//   pass 1  get_loci_used (load_data.rs:254-280): per locus count the entries with ref>0 and with alt>0,
+//           keep loci with both counts >= min, renumber densely in increasing locus order  -> GPU histogram +
+//           exclusive scan + stream compaction of the nonzeros;
+//   pass 2  per-cell row lists in file order (load_data.rs:151-174) -> packed CSR (stable sort by cell) and,
+//           for the per-locus passes, packed CSC (stable sort by locus: cells ascending inside a column,
+//           the order get_locus_log_likelihoods (main.rs:392-407) visits them in);
+//           locus_counts[l] = [sum ref, sum alt] (load_data.rs:157-158) -> u64 atomics (integers: order-free).
+// Zero-total entries and duplicated coordinates are kept as separate entries, like the reference.
+// Entries whose total exceeds K_LIGHT (or whose counts do not fit u16) are additionally listed in the
+// "heavy" side lists with full 32-bit counts; the packed matrices only carry a marker for them.
+#include <cub/cub.cuh>
+
+#include "ctx.h"
+#include "numerics.cuh"
+
+namespace clx {
+namespace {
+
+constexpr int TPB = 256;
+inline unsigned grid_for(uint64_t n, int tpb = TPB, unsigned cap = 148u * 16u) {
+    uint64_t g = (n + tpb - 1) / tpb;
+    if (g < 1) g = 1;
+    return (unsigned)(g > cap ? cap : g);
+}
+
+__global__ void k_locus_hist(const uint32_t* __restrict__ locus, const uint32_t* __restrict__ cell,
+                             const uint32_t* __restrict__ ref, const uint32_t* __restrict__ alt, uint64_t nnz0,
+                             uint32_t n_loci0, uint32_t n_cells, unsigned int* __restrict__ cnt,
+                             unsigned int* __restrict__ err) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < nnz0; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t l = locus[i];
+        if (l >= n_loci0 || cell[i] >= n_cells) {
+            atomicOr(err, 1u);
+            continue;
+        }
+        if (ref[i] > 0) atomicAdd(&cnt[2 * (size_t)l], 1u);
+        if (alt[i] > 0) atomicAdd(&cnt[2 * (size_t)l + 1], 1u);
+    }
+}
+
+__global__ void k_locus_flags(const unsigned int* __restrict__ cnt, uint32_t n_loci0, uint32_t min_ref,
+                              uint32_t min_alt, uint32_t* __restrict__ flag) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < n_loci0) flag[l] = (cnt[2 * (size_t)l] >= min_ref && cnt[2 * (size_t)l + 1] >= min_alt) ? 1u : 0u;
+}
+
+__global__ void k_locus_ids(const uint32_t* __restrict__ flag, const uint32_t* __restrict__ used_idx,
+                            uint32_t n_loci0, uint32_t* __restrict__ locus_ids) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l < n_loci0 && flag[l]) locus_ids[used_idx[l]] = l;
+}
+
+struct KeepEntry {
+    const uint32_t* locus;
+    const uint32_t* flag;
+    __device__ bool operator()(uint32_t i) const { return flag[locus[i]] != 0; }
+};
+struct FlagAt {
+    const uint8_t* flag;
+    const uint32_t* idx;  // optional indirection
+    __device__ bool operator()(uint32_t i) const { return flag[idx ? idx[i] : i] != 0; }
+};
+struct ToU64 {
+    __device__ uint64_t operator()(uint32_t v) const { return (uint64_t)v; }
+};
+
+__global__ void k_cell_keys(const uint32_t* __restrict__ kept_idx, const uint32_t* __restrict__ cell, uint64_t nnz,
+                            uint32_t* __restrict__ keys, uint32_t* __restrict__ row_cnt) {
+    for (uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < nnz; k += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t c = cell[kept_idx[k]];
+        keys[k] = c;
+        atomicAdd(&row_cnt[c], 1u);
+    }
+}
+
+__global__ void k_pack_csr(const uint32_t* __restrict__ csr_src, const uint32_t* __restrict__ locus,
+                           const uint32_t* __restrict__ ref, const uint32_t* __restrict__ alt,
+                           const uint32_t* __restrict__ used_idx, uint64_t nnz, RowEntry* __restrict__ csr,
+                           uint32_t* __restrict__ keys2, uint32_t* __restrict__ vals2, uint8_t* __restrict__ heavy,
+                           uint32_t* __restrict__ col_cnt, unsigned long long* __restrict__ locus_tot) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < nnz; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t src = csr_src[i];
+        const uint32_t l = used_idx[locus[src]];
+        const uint32_t r = ref[src], a = alt[src];
+        const bool hv = ((uint64_t)r + (uint64_t)a > (uint64_t)K_LIGHT);
+        RowEntry e;
+        e.locus = l;
+        e.ref = (uint16_t)(r > 0xFFFFu ? 0xFFFFu : r);
+        e.alt = (uint16_t)(a > 0xFFFFu ? 0xFFFFu : a);
+        csr[i] = e;
+        keys2[i] = l;
+        vals2[i] = (uint32_t)i;
+        heavy[i] = hv ? 1 : 0;
+        atomicAdd(&col_cnt[l], 1u);
+        if (r) atomicAdd(&locus_tot[2 * (size_t)l], (unsigned long long)r);
+        if (a) atomicAdd(&locus_tot[2 * (size_t)l + 1], (unsigned long long)a);
+    }
+}
+
+__global__ void k_pack_csc(const uint32_t* __restrict__ csc_src, const uint32_t* __restrict__ csr_src,
+                           const uint32_t* __restrict__ cell, const RowEntry* __restrict__ csr, uint64_t nnz,
+                           ColEntry* __restrict__ csc) {
+    for (uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; j < nnz; j += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t p = csc_src[j];
+        const RowEntry e = csr[p];
+        ColEntry o;
+        o.cell = cell[csr_src[p]];
+        o.ref = e.ref;
+        o.alt = e.alt;
+        csc[j] = o;
+    }
+}
+
+__global__ void k_heavy_gather(const uint32_t* __restrict__ hpos, uint64_t n_heavy, const uint32_t* __restrict__ csr_src,
+                               const RowEntry* __restrict__ csr, const uint32_t* __restrict__ cell,
+                               const uint32_t* __restrict__ ref, const uint32_t* __restrict__ alt,
+                               uint32_t* __restrict__ h_cell, uint32_t* __restrict__ h_locus,
+                               uint32_t* __restrict__ h_ref, uint32_t* __restrict__ h_alt) {
+    const uint64_t h = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (h >= n_heavy) return;
+    const uint32_t p = hpos[h];
+    const uint32_t src = csr_src[p];
+    h_cell[h] = cell[src];
+    h_locus[h] = csr[p].locus;
+    h_ref[h] = ref[src];
+    h_alt[h] = alt[src];
+}
+
+__device__ __forceinline__ uint32_t lower_bound_u32(const uint32_t* __restrict__ a, uint32_t n, uint64_t v) {
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if ((uint64_t)a[mid] < v) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+// out[i] = number of (sorted) positions < ptr[i], for i in [0, n]
+__global__ void k_segment_ptr(const uint32_t* __restrict__ pos, uint32_t n_pos, const uint64_t* __restrict__ ptr,
+                              uint32_t n, uint32_t* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i <= n) out[i] = lower_bound_u32(pos, n_pos, ptr[i]);
+}
+__global__ void k_heavy_perm(const uint32_t* __restrict__ hcpos, const uint32_t* __restrict__ csc_src,
+                             const uint32_t* __restrict__ hpos, uint32_t n_heavy, uint32_t* __restrict__ perm) {
+    const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h < n_heavy) perm[h] = lower_bound_u32(hpos, n_heavy, (uint64_t)csc_src[hcpos[h]]);
+}
+
+int bits_for(uint64_t n) {
+    int b = 1;
+    while (b < 32 && (1ull << b) < n) ++b;
+    return b;
+}
+
+}  // namespace
+
+int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, const uint32_t* locus,
+             const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt) {
+    cudaStream_t s = c->stream;
+    c->loaded = false;
+    if (nnz0 >= 0xFFFFFFFFull) return fail(c, CLX_ERR_ARG, "more than 2^32-1 nonzeros per GPU: shard the cells over more ranks");
+    if (nnz0 > 0 && (!locus || !cell || !ref || !alt)) return fail(c, CLX_ERR_ARG, "null COO array");
+    c->n_cells = n_cells;
+    c->n_loci0 = n_loci0;
+    c->nnz0 = nnz0;
+
+    // ---- shard bookkeeping (cells are sharded across ranks; loci are global)
+    {
+        std::vector<uint64_t> all;
+        CLX_TRY(comm_allgather_u64_host(c, (uint64_t)n_cells, &all));
+        c->n_cells_global = 0;
+        c->cell_offset = 0;
+        uint64_t mx = 0;
+        for (int r = 0; r < c->world; ++r) {
+            if (r < c->rank) c->cell_offset += all[r];
+            c->n_cells_global += all[r];
+            mx = all[r] > mx ? all[r] : mx;
+        }
+        c->max_local_cells = (uint32_t)mx;
+    }
+
+    // ---- COO to device
+    DevBuf<uint32_t>&d_locus = c->coo_locus, &d_cell = c->coo_cell, &d_ref = c->coo_ref, &d_alt = c->coo_alt;
+    CLX_CUDA(c, d_locus.alloc(nnz0));
+    CLX_CUDA(c, d_cell.alloc(nnz0));
+    CLX_CUDA(c, d_ref.alloc(nnz0));
+    CLX_CUDA(c, d_alt.alloc(nnz0));
+    if (nnz0) {
+        CLX_CUDA(c, cudaMemcpyAsync(d_locus.p, locus, nnz0 * 4, cudaMemcpyHostToDevice, s));
+        CLX_CUDA(c, cudaMemcpyAsync(d_cell.p, cell, nnz0 * 4, cudaMemcpyHostToDevice, s));
+        CLX_CUDA(c, cudaMemcpyAsync(d_ref.p, ref, nnz0 * 4, cudaMemcpyHostToDevice, s));
+        CLX_CUDA(c, cudaMemcpyAsync(d_alt.p, alt, nnz0 * 4, cudaMemcpyHostToDevice, s));
+    }
+
+    // ---- pass 1: locus filter
+    DevBuf<unsigned int> cnt, err;
+    DevBuf<uint32_t> flag, used_idx;
+    CLX_CUDA(c, cnt.alloc(2 * (size_t)n_loci0 + 2));
+    CLX_CUDA(c, err.alloc(1));
+    CLX_CUDA(c, flag.alloc((size_t)n_loci0 + 1));
+    CLX_CUDA(c, used_idx.alloc((size_t)n_loci0 + 1));
+    CLX_CUDA(c, cudaMemsetAsync(cnt.p, 0, cnt.bytes(), s));
+    CLX_CUDA(c, cudaMemsetAsync(err.p, 0, 4, s));
+    CLX_CUDA(c, cudaMemsetAsync(flag.p, 0, flag.bytes(), s));
+    if (nnz0) {
+        k_locus_hist<<<grid_for(nnz0), TPB, 0, s>>>(d_locus.p, d_cell.p, d_ref.p, d_alt.p, nnz0, n_loci0, n_cells, cnt.p, err.p);
+        c->launches++;
+    }
+    CLX_TRY(comm_allreduce_u32(c, cnt.p, 2 * (size_t)n_loci0));
+    if (n_loci0) {
+        k_locus_flags<<<(n_loci0 + TPB - 1) / TPB, TPB, 0, s>>>(cnt.p, n_loci0, min_ref, min_alt, flag.p);
+        c->launches++;
+    }
+    DevBuf<uint8_t> tmp;
+    size_t tmp_bytes = 0;
+    // exclusive scan over n_loci0 + 1 flags (last one is 0) so that used_idx[n_loci0] = n_loci
+    CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flag.p, used_idx.p, (int)(n_loci0 + 1), s));
+    CLX_CUDA(c, tmp.alloc(tmp_bytes));
+    CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, flag.p, used_idx.p, (int)(n_loci0 + 1), s));
+    c->launches += 2;
+    uint32_t n_loci = 0;
+    unsigned int h_err = 0;
+    CLX_CUDA(c, cudaMemcpyAsync(&n_loci, used_idx.p + n_loci0, 4, cudaMemcpyDeviceToHost, s));
+    CLX_CUDA(c, cudaMemcpyAsync(&h_err, err.p, 4, cudaMemcpyDeviceToHost, s));
+    CLX_CUDA(c, cudaStreamSynchronize(s));
+    if (h_err) return fail(c, CLX_ERR_ARG, "COO coordinate out of range (locus >= n_loci0 or cell >= n_cells)");
+    c->n_loci = n_loci;
+    CLX_CUDA(c, c->locus_ids.alloc(n_loci));
+    if (n_loci0) {
+        k_locus_ids<<<(n_loci0 + TPB - 1) / TPB, TPB, 0, s>>>(flag.p, used_idx.p, n_loci0, c->locus_ids.p);
+        c->launches++;
+    }
+
+    // ---- compaction of the kept nonzeros (file order preserved)
+    DevBuf<uint32_t> kept_idx, n_sel;
+    CLX_CUDA(c, kept_idx.alloc(nnz0));
+    CLX_CUDA(c, n_sel.alloc(1));
+    uint32_t nnz = 0;
+    if (nnz0) {
+        cub::CountingInputIterator<uint32_t> counting(0);
+        KeepEntry keep{d_locus.p, flag.p};
+        CLX_CUDA(c, cub::DeviceSelect::If(nullptr, tmp_bytes, counting, kept_idx.p, n_sel.p, (int)nnz0, keep, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, kept_idx.p, n_sel.p, (int)nnz0, keep, s));
+        c->launches += 2;
+        CLX_CUDA(c, cudaMemcpyAsync(&nnz, n_sel.p, 4, cudaMemcpyDeviceToHost, s));
+        CLX_CUDA(c, cudaStreamSynchronize(s));
+    }
+    c->nnz = nnz;
+
+    // ---- CSR: stable sort by cell
+    DevBuf<uint32_t> keys, keys_sorted, csr_src, row_cnt;
+    CLX_CUDA(c, keys.alloc(nnz));
+    CLX_CUDA(c, keys_sorted.alloc(nnz));
+    CLX_CUDA(c, csr_src.alloc(nnz));
+    CLX_CUDA(c, row_cnt.alloc((size_t)n_cells + 1));
+    CLX_CUDA(c, cudaMemsetAsync(row_cnt.p, 0, row_cnt.bytes(), s));
+    CLX_CUDA(c, c->row_ptr.alloc((size_t)n_cells + 1));
+    if (nnz) {
+        k_cell_keys<<<grid_for(nnz), TPB, 0, s>>>(kept_idx.p, d_cell.p, nnz, keys.p, row_cnt.p);
+        c->launches++;
+        const int eb = bits_for(n_cells);
+        CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys_sorted.p, kept_idx.p, csr_src.p, (int)nnz, 0, eb, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.p, keys_sorted.p, kept_idx.p, csr_src.p, (int)nnz, 0, eb, s));
+        c->launches += 4;
+    }
+    {
+        cub::TransformInputIterator<uint64_t, ToU64, const uint32_t*> it(row_cnt.p, ToU64());
+        CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, it, c->row_ptr.p, (int)(n_cells + 1), s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, it, c->row_ptr.p, (int)(n_cells + 1), s));
+        c->launches += 2;
+    }
+
+    // ---- pack CSR, locus totals, CSC keys
+    DevBuf<uint8_t> heavy;
+    DevBuf<uint32_t> col_cnt, vals2, csc_src;
+    CLX_CUDA(c, c->csr.alloc(nnz));
+    CLX_CUDA(c, heavy.alloc(nnz));
+    CLX_CUDA(c, col_cnt.alloc((size_t)n_loci + 1));
+    CLX_CUDA(c, vals2.alloc(nnz));
+    CLX_CUDA(c, csc_src.alloc(nnz));
+    CLX_CUDA(c, c->locus_tot.alloc(2 * (size_t)n_loci + 2));
+    CLX_CUDA(c, cudaMemsetAsync(col_cnt.p, 0, col_cnt.bytes(), s));
+    CLX_CUDA(c, cudaMemsetAsync(c->locus_tot.p, 0, c->locus_tot.bytes(), s));
+    CLX_CUDA(c, c->col_ptr.alloc((size_t)n_loci + 1));
+    CLX_CUDA(c, c->csc.alloc(nnz));
+    if (nnz) {
+        // keys / keys_sorted are reused as the locus keys of the second sort
+        k_pack_csr<<<grid_for(nnz), TPB, 0, s>>>(csr_src.p, d_locus.p, d_ref.p, d_alt.p, used_idx.p, nnz, c->csr.p, keys.p,
+                                                 vals2.p, heavy.p, col_cnt.p, c->locus_tot.p);
+        c->launches++;
+        const int eb = bits_for(n_loci);
+        CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys_sorted.p, vals2.p, csc_src.p, (int)nnz, 0, eb, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.p, keys_sorted.p, vals2.p, csc_src.p, (int)nnz, 0, eb, s));
+        c->launches += 4;
+        k_pack_csc<<<grid_for(nnz), TPB, 0, s>>>(csc_src.p, csr_src.p, d_cell.p, c->csr.p, nnz, c->csc.p);
+        c->launches++;
+    }
+    {
+        cub::TransformInputIterator<uint64_t, ToU64, const uint32_t*> it(col_cnt.p, ToU64());
+        CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, it, c->col_ptr.p, (int)(n_loci + 1), s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, it, c->col_ptr.p, (int)(n_loci + 1), s));
+        c->launches += 2;
+    }
+    CLX_TRY(comm_allreduce_u64(c, c->locus_tot.p, 2 * (size_t)n_loci));
+
+    // ---- heavy side lists
+    DevBuf<uint32_t> hpos, hcpos;
+    CLX_CUDA(c, hpos.alloc(nnz));
+    uint32_t n_heavy = 0;
+    if (nnz) {
+        cub::CountingInputIterator<uint32_t> counting(0);
+        FlagAt f1{heavy.p, nullptr};
+        CLX_CUDA(c, cub::DeviceSelect::If(nullptr, tmp_bytes, counting, hpos.p, n_sel.p, (int)nnz, f1, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, hpos.p, n_sel.p, (int)nnz, f1, s));
+        c->launches += 2;
+        CLX_CUDA(c, cudaMemcpyAsync(&n_heavy, n_sel.p, 4, cudaMemcpyDeviceToHost, s));
+        CLX_CUDA(c, cudaStreamSynchronize(s));
+    }
+    c->n_heavy = n_heavy;
+    CLX_CUDA(c, c->h_cell.alloc(n_heavy));
+    CLX_CUDA(c, c->h_locus.alloc(n_heavy));
+    CLX_CUDA(c, c->h_ref.alloc(n_heavy));
+    CLX_CUDA(c, c->h_alt.alloc(n_heavy));
+    CLX_CUDA(c, c->hc_perm.alloc(n_heavy));
+    CLX_CUDA(c, c->h_row_ptr.alloc((size_t)n_cells + 1));
+    CLX_CUDA(c, c->hc_col_ptr.alloc((size_t)n_loci + 1));
+    CLX_CUDA(c, c->hv_ll.alloc(3 * (size_t)n_heavy));
+    CLX_CUDA(c, c->hv_e.alloc(n_heavy));
+    CLX_CUDA(c, hcpos.alloc(n_heavy));
+    if (n_heavy) {
+        k_heavy_gather<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hpos.p, n_heavy, csr_src.p, c->csr.p, d_cell.p, d_ref.p,
+                                                               d_alt.p, c->h_cell.p, c->h_locus.p, c->h_ref.p, c->h_alt.p);
+        cub::CountingInputIterator<uint32_t> counting(0);
+        FlagAt f2{heavy.p, csc_src.p};
+        CLX_CUDA(c, cub::DeviceSelect::If(nullptr, tmp_bytes, counting, hcpos.p, n_sel.p, (int)nnz, f2, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, hcpos.p, n_sel.p, (int)nnz, f2, s));
+        k_heavy_perm<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, csc_src.p, hpos.p, n_heavy, c->hc_perm.p);
+        c->launches += 4;
+    }
+    k_segment_ptr<<<(n_cells + 1 + TPB - 1) / TPB, TPB, 0, s>>>(hpos.p, n_heavy, c->row_ptr.p, n_cells, c->h_row_ptr.p);
+    k_segment_ptr<<<(n_loci + 1 + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, n_heavy, c->col_ptr.p, n_loci, c->hc_col_ptr.p);
+    c->launches += 2;
+    CLX_CUDA(c, cudaStreamSynchronize(s));
+    CLX_CUDA(c, cudaGetLastError());
+
+    if (!(c->flags & CLX_FLAG_KEEP_COO)) {
+        d_locus.release();
+        d_cell.release();
+        d_ref.release();
+        d_alt.release();
+    }
+    CLX_TRY(em_alloc(c));
+    c->loaded = true;
+    return CLX_OK;
+}
+
+}  // namespace clx

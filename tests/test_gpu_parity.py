@@ -1,0 +1,132 @@
+"""GPU parity tests proper: every call goes through the C ABI of libcellector_cuda.so and is checked against
+the CPU oracle on the same seeded input (sizes the oracle finishes in seconds)."""
+import numpy as np
+import pytest
+
+from cellector_b200 import synth
+from tests.parity import assert_equal, run_parity
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def libs(oracle_lib):
+    from cellector_b200 import api
+    return api.load_library(), oracle_lib
+
+
+def _pair(libs, flags=0):
+    from cellector_b200 import Cellector
+    from tests.oracle import Oracle
+    return Cellector(0, flags, libs[0]), Oracle(libs[1])
+
+
+CASES = {
+    "small": synth.SynthConfig(n_cells=600, n_loci=3000, density=0.03, minority_frac=0.08, seed=3),
+    "c1_slice": synth.SynthConfig(n_cells=2000, n_loci=8000, density=0.02, minority_frac=0.05, seed=1),
+    "deep": synth.SynthConfig(n_cells=800, n_loci=2500, density=0.04, minority_frac=0.1, seed=5, deep_frac=0.05, deep_mean=60.0),
+    "skewed": synth.SynthConfig(n_cells=3000, n_loci=6000, density=0.01, minority_frac=0.05, seed=7, row_sigma=2.0),
+    "doublets": synth.SynthConfig(n_cells=1500, n_loci=5000, density=0.03, minority_frac=0.1, seed=9, doublet_frac=0.05),
+    "big_select": synth.SynthConfig(n_cells=40000, n_loci=1500, density=0.004, minority_frac=0.05, seed=11),
+}
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_parity_synthetic(libs, name):
+    gpu, orc = _pair(libs)
+    with gpu, orc:
+        n_it = run_parity(gpu, orc, synth.generate(CASES[name]))
+        assert n_it >= 1
+
+
+def test_parity_min_filters_and_iqr(libs):
+    gpu, orc = _pair(libs)
+    with gpu, orc:
+        run_parity(gpu, orc, synth.generate(CASES["small"]), min_ref=2, min_alt=7, iqr=2.0, min_loci_used=10,
+                   posterior_threshold=0.9)
+
+
+def _edge_matrix():
+    """Hand-built matrix with the reference's corner cases: a locus failing min_alt, zero-total
+    entries, a duplicated coordinate, a cell with no used loci, counts > 100 and > 65535, unsorted file order."""
+    rng = np.random.default_rng(0)
+    n_cells, n_loci = 64, 40
+    rows = []
+    for l in range(n_loci - 4):
+        for c in rng.choice(n_cells - 2, size=20, replace=False):
+            t = 1 + rng.poisson(0.7)
+            a = rng.binomial(t, 0.5 if l % 3 else 0.95)
+            rows.append((l, int(c), t - a, a))
+    rows += [(n_loci - 4, c, 1, 0) for c in range(10)]          # never any alt -> filtered
+    rows += [(n_loci - 3, c, 0, 0) for c in range(12)]          # zero-total only -> filtered (no cell has ref>0)
+    rows += [(0, 5, 0, 0), (1, 5, 0, 0)]                         # zero-total entries on used loci are kept
+    rows += [(2, 7, 1, 1), (2, 7, 1, 1)]                         # duplicated coordinate kept twice
+    rows += [(3, 9, 150, 70), (4, 9, 70000, 3), (5, 10, 2, 66000)]  # > 100 (ln_binomial switch) and > u16
+    rows += [(n_loci - 4, n_cells - 1, 3, 0)]                    # last cell only touches a filtered locus
+    rng.shuffle(rows)                                            # file order is NOT sorted
+    arr = np.array(rows, dtype=np.uint32)
+    return synth.SynthData(n_cells=n_cells, n_loci=n_loci, locus=arr[:, 0].copy(), cell=arr[:, 1].copy(),
+                           ref=arr[:, 2].copy(), alt=arr[:, 3].copy(), is_minority=np.zeros(n_cells, bool))
+
+
+def test_parity_edge_cases(libs):
+    gpu, orc = _pair(libs)
+    with gpu, orc:
+        run_parity(gpu, orc, _edge_matrix(), min_ref=4, min_alt=4, min_loci_used=5)
+
+
+def test_empty_and_all_filtered(libs):
+    gpu, orc = _pair(libs)
+    with gpu, orc:
+        d = _edge_matrix()
+        # thresholds nobody meets: zero loci used, every cell has norm 0.0, nobody is excluded
+        run_parity(gpu, orc, d, min_ref=1000, min_alt=1000)
+    gpu, orc = _pair(libs)
+    with gpu, orc:
+        e = synth.SynthData(n_cells=5, n_loci=7, locus=np.zeros(0, np.uint32), cell=np.zeros(0, np.uint32),
+                            ref=np.zeros(0, np.uint32), alt=np.zeros(0, np.uint32), is_minority=np.zeros(5, bool))
+        run_parity(gpu, orc, e)
+
+
+def test_out_of_range_coordinate_is_an_error(libs):
+    gpu, _ = _pair(libs)
+    with gpu:
+        with pytest.raises(RuntimeError, match="out of range"):
+            gpu.load_cell_data([0, 9], [0, 0], [1, 1], [1, 1], n_loci0=5, n_cells=3)
+
+
+def test_final_locus_counts_and_reset(libs):
+    from cellector_b200 import api
+    gpu, orc = _pair(libs, flags=8)  # CLX_FLAG_KEEP_COO
+    with gpu, orc:
+        d = synth.generate(CASES["small"])
+        run_parity(gpu, orc, d)
+        gm, gj = gpu.final_locus_counts()
+        om, oj = orc.final_locus_counts()
+        assert_equal(gm, om, "final minority counts")
+        assert_equal(gj, oj, "final majority counts")
+        # reset + rerun reproduces the first iteration bit for bit (deterministic reductions)
+        first = None
+        for _ in range(2):
+            gpu.reset()
+            gpu.compute_new_excluded()
+            cv = gpu.cell_vectors()
+            if first is None:
+                first = cv
+            else:
+                for k in cv:
+                    assert np.array_equal(cv[k], first[k]), k
+
+
+def test_determinism_bitwise(libs):
+    gpu, _ = _pair(libs)
+    d = synth.generate(CASES["c1_slice"])
+    outs = []
+    with gpu:
+        for _ in range(2):
+            gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+            gpu.run_em()
+            outs.append((gpu.cell_vectors(), gpu.locus_vectors(), gpu.calculate_posteriors()))
+    for a, b in zip(outs[0], outs[1]):
+        for k in a:
+            assert np.array_equal(a[k], b[k]), k
