@@ -19,6 +19,8 @@ LIB_PATH = os.path.join(_HERE, "libcellector_cuda.so")
 FLAG_PROFILE = 1
 FLAG_NO_EXPECTED = 2
 FLAG_KERNEL_V0 = 4
+FLAG_KEEP_COO = 8
+FLAG_NO_GRAPH = 16
 
 PHASES = ("tables", "score", "heavy", "select", "column", "comm")
 LABELS = ("0", "1", "doublet", "unassigned")

@@ -32,14 +32,21 @@ static cudaEvent_t get_event(clx_ctx* c) {
 void phase_begin(clx_ctx* c, int phase) {
     if (!(c->flags & CLX_FLAG_PROFILE)) return;
     PendingEvent p{phase, get_event(c), get_event(c)};
-    cudaEventRecord(p.a, c->stream);
-    c->pending.push_back(p);
+    if (c->capturing) {  // inside a stream capture only "external" records become timing nodes of the graph
+        cudaEventRecordWithFlags(p.a, c->stream, cudaEventRecordExternal);
+        c->graph_events.push_back(p);
+    } else {
+        cudaEventRecord(p.a, c->stream);
+        c->pending.push_back(p);
+    }
 }
 void phase_end(clx_ctx* c, int phase) {
     if (!(c->flags & CLX_FLAG_PROFILE)) return;
-    for (size_t i = c->pending.size(); i-- > 0;) {
-        if (c->pending[i].phase == phase) {
-            cudaEventRecord(c->pending[i].b, c->stream);
+    std::vector<PendingEvent>& v = c->capturing ? c->graph_events : c->pending;
+    for (size_t i = v.size(); i-- > 0;) {
+        if (v[i].phase == phase) {
+            if (c->capturing) cudaEventRecordWithFlags(v[i].b, c->stream, cudaEventRecordExternal);
+            else cudaEventRecord(v[i].b, c->stream);
             return;
         }
     }
@@ -55,6 +62,16 @@ void phase_resolve(clx_ctx* c) {
         c->event_pool.push_back(p.b);
     }
     c->pending.clear();
+    if (c->graph_events_fresh) {  // the graph's event nodes fired once since the last resolve
+        for (auto& p : c->graph_events) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+                c->phase_ms[p.phase] += ms;
+                c->phase_launches[p.phase] += 1;
+            }
+        }
+        c->graph_events_fresh = false;
+    }
     cudaGetLastError();
 }
 
@@ -119,6 +136,9 @@ int clx_create(clx_ctx** out, int device, unsigned flags) {
     CLX_CREATE_CUDA(c->d_stats.alloc(1));
     CLX_CREATE_CUDA(cudaMallocHost((void**)&c->h_stats, sizeof(DeviceStats)));
     memset(c->h_stats, 0, sizeof(DeviceStats));
+    CLX_CREATE_CUDA(c->d_params.alloc(1));
+    CLX_CREATE_CUDA(cudaMallocHost((void**)&c->h_params, sizeof(IterParams)));
+    c->h_params->iqr_multiple = 0.0;
     // ln(i!) for i <= 170 exactly like statrs: ln of the f64 running product (glibc log, as the Rust binary uses)
     double lnfact[171], f = 1.0;
     lnfact[0] = log(1.0);
@@ -141,6 +161,8 @@ void clx_destroy(clx_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     comm_destroy(c);
     phase_resolve(c);
+    em_drop_graph(c);
+    if (c->h_params) cudaFreeHost(c->h_params);
     for (cudaEvent_t e : c->event_pool) cudaEventDestroy(e);
     if (c->ev_iter_a) cudaEventDestroy(c->ev_iter_a);
     if (c->ev_iter_b) cudaEventDestroy(c->ev_iter_b);
@@ -149,8 +171,8 @@ void clx_destroy(clx_ctx* c) {
     (void)dummy;
 #define R(x) c->x.release()
     R(locus_ids); R(csr); R(row_ptr); R(csc); R(col_ptr); R(locus_tot); R(h_cell); R(h_locus); R(h_ref); R(h_alt);
-    R(h_row_ptr); R(hc_perm); R(hc_col_ptr); R(hv_ll); R(hv_e); R(coo_locus); R(coo_cell); R(coo_ref); R(coo_alt);
-    R(lnfact); R(excl_bits); R(excl_bits_new); R(loci_used); R(min_cnt); R(tab); R(ll); R(ell); R(norm); R(nloci);
+    R(h_row_ptr); R(hc_perm); R(hc_col_ptr); R(hv_ll); R(hv_e); R(giant_idx); R(coo_locus); R(coo_cell); R(coo_ref); R(coo_alt);
+    R(lnfact); R(excl_bits); R(d_params); R(loci_used); R(min_cnt); R(tab); R(ll); R(ell); R(norm); R(nloci);
     R(norm_all); R(sel_keys); R(sel_hist); R(sel_state); R(loc_ll); R(loc_int); R(post); R(post_u8); R(d_stats);
     R(flush_buf);
 #undef R

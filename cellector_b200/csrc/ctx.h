@@ -45,7 +45,10 @@ struct DeviceStats {  // written by kernels, copied to pinned host memory once p
     unsigned int nan_flag, pad;
 };
 
-struct NcclApi;  // comm.cu
+// Scalars that may change between iterations live in device memory so that a captured CUDA graph stays valid.
+struct IterParams {
+    double iqr_multiple;
+};
 
 struct PendingEvent {
     int phase;
@@ -86,6 +89,8 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> h_row_ptr;                      // [n_cells + 1]
     clx::DevBuf<uint32_t> hc_perm;                        // [n_heavy] CSC order -> index into the CSR-order lists
     clx::DevBuf<uint32_t> hc_col_ptr;                     // [n_loci + 1]
+    clx::DevBuf<uint32_t> giant_idx;                      // [n_giant] heavy entries with total > HEAVY_GIANT_TOTAL
+    uint32_t n_giant = 0;
     clx::DevBuf<double> hv_ll, hv_e;                      // [3 * n_heavy] values of the current scoring pass
     // retained COO for clx_final_locus_counts
     clx::DevBuf<uint32_t> coo_locus, coo_cell, coo_ref, coo_alt;
@@ -96,7 +101,7 @@ struct clx_ctx {
     uint32_t iteration = 0;
     uint64_t n_excluded_global = 0;  // size of the current excluded set over all ranks
     bool have_iteration = false;
-    clx::DevBuf<uint32_t> excl_bits, excl_bits_new;   // [(n_cells + 31) / 32]
+    clx::DevBuf<uint32_t> excl_bits;                  // [(n_cells + 31) / 32] current excluded set, updated in place
     clx::DevBuf<uint8_t> loci_used;                   // [n_loci]
     clx::DevBuf<unsigned long long> min_cnt;          // [2 * n_loci] minority (ref, alt) over all stored entries
     clx::DevBuf<double> tab;                          // [3][n_loci][16] memo tables (slot 0 = EM, 0..2 = posteriors)
@@ -112,6 +117,13 @@ struct clx_ctx {
     clx::DevBuf<double> post;                         // [5 * n_cells] posterior pass outputs
     clx::DevBuf<uint8_t> post_u8;                     // [3 * n_cells]
     clx::DevBuf<clx::DeviceStats> d_stats;
+    clx::DevBuf<clx::IterParams> d_params;
+    clx::IterParams* h_params = nullptr;              // pinned; copied to d_params at the head of every iteration
+    int score_G = 32, col_G = 8;                      // lanes per CSR row / CSC column (picked at load)
+    void* iter_graph_exec = nullptr;                  // cudaGraphExec_t of one EM iteration (world == 1)
+    uint64_t graph_launches = 0;                      // kernels inside that graph
+    bool capturing = false, graph_events_fresh = false;
+    std::vector<clx::PendingEvent> graph_events;      // phase events recorded by graph nodes (CLX_FLAG_PROFILE)
     clx::DeviceStats* h_stats = nullptr;              // pinned
     clx::DevBuf<uint8_t> flush_buf;
     uint32_t max_local_cells = 0;
@@ -160,6 +172,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
 // em.cu
 int em_alloc(clx_ctx* c);
 int em_reset(clx_ctx* c);
+void em_drop_graph(clx_ctx* c);
 int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out);
 int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used);
 int em_final_locus_counts(clx_ctx* c, unsigned long long* d_min, unsigned long long* d_maj);

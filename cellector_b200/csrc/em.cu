@@ -4,6 +4,8 @@
 #include <math.h>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "ctx.h"
@@ -17,9 +19,10 @@ namespace {
 constexpr int TPB = 256;
 
 int pick_group(double avg_len) {
-    // lanes per row/column: each lane should see >= ~8 two-entry loads
+    // lanes per row/column: every lane should have about one unrolled batch (SCORE_UNROLL 128-bit loads of two
+    // entries) of work, so that all of a row's loads are in flight at once
     int g = 4;
-    while (g < 32 && avg_len > 16.0 * g) g <<= 1;
+    while (g < 32 && avg_len > 2.0 * SCORE_UNROLL * g) g <<= 1;
     return g;
 }
 
@@ -29,14 +32,19 @@ Lbc10 make_lbc(const clx_ctx* c) {
     return l;
 }
 
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
 template <int NT, bool WITH_E>
-void launch_score_rows(clx_ctx* c, int G, const uint8_t* used) {
+void launch_score_rows(clx_ctx* c, int G) {
     const uint32_t n = c->n_cells;
     if (n == 0) return;
 #define CLX_SCORE(GG)                                                                                                  \
     k_score_rows<GG, NT, WITH_E><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                 \
-        c->csr.p, c->row_ptr.p, n, c->tab.p, c->n_loci, used, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p,                   \
-        (uint32_t)c->n_heavy, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag)
+        c->csr.p, c->row_ptr.p, n, c->tab.p, c->n_loci, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p, (uint32_t)c->n_heavy,   \
+        c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag)
     switch (G) {
         case 4: CLX_SCORE(4); break;
         case 8: CLX_SCORE(8); break;
@@ -47,13 +55,14 @@ void launch_score_rows(clx_ctx* c, int G, const uint8_t* used) {
     c->launches++;
 }
 
+template <bool FUSE>
 void launch_columns(clx_ctx* c, int G) {
     const uint32_t n = c->n_loci;
     if (n == 0) return;
 #define CLX_COLS(GG)                                                                                                   \
-    k_columns<GG><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                                \
-        c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits_new.p, c->hc_col_ptr.p, c->hc_perm.p,        \
-        c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hv_ll.p, c->loc_ll.p, c->loc_int.p)
+    k_columns<GG, FUSE><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                          \
+        c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_perm.p,            \
+        c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hv_ll.p, c->loc_ll.p, c->loc_int.p, c->d_stats.p)
     switch (G) {
         case 4: CLX_COLS(4); break;
         case 8: CLX_COLS(8); break;
@@ -95,33 +104,36 @@ SelectPlan make_plan(uint64_t n) {
     return p;
 }
 
-// exact order statistics of `vals[0, n_vals)` (pads = +inf beyond the n real values) -> d_stats
-int run_select(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t n_real, double iqr_multiple) {
+// exact order statistics of `vals[0, n_vals)` (pads = +inf beyond the n real values) -> d_stats, then the new
+// excluded set of this rank's cells (main.rs:330-335), in place in excl_bits
+int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t n_real) {
     const SelectPlan plan = make_plan(n_real);
     cudaStream_t s = c->stream;
+    const uint32_t N = c->n_cells;
     if (n_vals <= SELECT_SMALL_MAX) {
-        uint32_t p2 = 2;
-        while (p2 < n_vals) p2 <<= 1;
-        k_select_small<<<1, 1024, (size_t)p2 * 8, s>>>(vals, (uint32_t)n_vals, p2, plan, iqr_multiple, c->d_stats.p);
+        k_select_small<<<1, SELECT_SMALL_THREADS, 0, s>>>(vals, (uint32_t)n_vals, plan, c->d_params.p,
+                                                                         c->d_stats.p, c->norm.p, N, c->excl_bits.p);
         c->launches++;
+        if (vals != c->norm.p && N) {  // sharded: the selected values are the gathered ones, exclude separately
+            k_exclude<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->norm.p, N, c->excl_bits.p, c->d_stats.p);
+            c->launches++;
+        }
         return CLX_OK;
     }
     unsigned long long* keys = (unsigned long long*)c->sel_keys.p;
-    SelectState init;
-    for (int t = 0; t < SELECT_TARGETS; ++t) {
-        init.prefix[t] = 0;
-        init.rank[t] = plan.rank[t];
-    }
     SelectState* d_state = (SelectState*)c->sel_state.p;
     unsigned int* hist = c->sel_hist.p;
     unsigned int* ticket = hist + 8 * SELECT_TARGETS * 256;
-    CLX_CUDA(c, cudaMemcpyAsync(d_state, &init, sizeof(init), cudaMemcpyHostToDevice, s));
     CLX_CUDA(c, cudaMemsetAsync(hist, 0, c->sel_hist.bytes(), s));
     const unsigned grid = (unsigned)std::min<uint64_t>((n_vals + 512 * 8 - 1) / (512 * 8), (uint64_t)c->sm_count * 2);
-    k_select_keys<<<grid, 512, 0, s>>>(vals, n_vals, keys);
+    k_select_keys<<<grid, 512, 0, s>>>(vals, n_vals, keys, plan, d_state);
     for (int pass = 0; pass < 8; ++pass)
-        k_select_pass<<<grid, 512, 0, s>>>(keys, n_vals, pass, d_state, hist, ticket, plan, iqr_multiple, c->d_stats.p);
+        k_select_pass<<<grid, 512, 0, s>>>(keys, n_vals, pass, d_state, hist, ticket, plan, c->d_params.p, c->d_stats.p);
     c->launches += 9;
+    if (N) {
+        k_exclude<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->norm.p, N, c->excl_bits.p, c->d_stats.p);
+        c->launches++;
+    }
     return CLX_OK;
 }
 
@@ -130,8 +142,8 @@ int run_select(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t n_real,
 int em_alloc(clx_ctx* c) {
     const size_t N = c->n_cells, L = c->n_loci;
     const size_t words = (N + 31) / 32 + 1;
+    em_drop_graph(c);
     CLX_CUDA(c, c->excl_bits.alloc(words));
-    CLX_CUDA(c, c->excl_bits_new.alloc(words));
     CLX_CUDA(c, c->loci_used.alloc(L + 1));
     CLX_CUDA(c, c->tab.alloc(3 * L * TAB_STRIDE + TAB_STRIDE));
     CLX_CUDA(c, c->ll.alloc(3 * N + 1));
@@ -154,8 +166,9 @@ int em_alloc(clx_ctx* c) {
         CLX_CUDA(c, cudaMemcpyAsync(c->norm.p, inf.data(), norm_n * 8, cudaMemcpyHostToDevice, c->stream));
         CLX_CUDA(c, cudaStreamSynchronize(c->stream));
     }
-    CLX_CUDA(c, cudaFuncSetAttribute(k_select_small, cudaFuncAttributeMaxDynamicSharedMemorySize, SELECT_SMALL_MAX * 8));
-    // roofline accounting of the v0 scoring kernel: packed entries + row pointers + outputs + table
+    c->score_G = env_int("CLX_SCORE_G", pick_group(N ? (double)c->nnz / N : 0.0));
+    c->col_G = env_int("CLX_COL_G", pick_group(L ? (double)c->nnz / L : 0.0));
+    // roofline accounting of the gather scoring kernel: packed entries + row pointers + outputs + table
     c->score_bytes = 8ull * c->nnz + 8ull * (N + 1) + 20ull * N + 128ull * L;
     return em_reset(c);
 }
@@ -163,7 +176,6 @@ int em_alloc(clx_ctx* c) {
 int em_reset(clx_ctx* c) {
     cudaStream_t s = c->stream;
     CLX_CUDA(c, cudaMemsetAsync(c->excl_bits.p, 0, c->excl_bits.bytes(), s));
-    CLX_CUDA(c, cudaMemsetAsync(c->excl_bits_new.p, 0, c->excl_bits_new.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->loci_used.p, 1, c->loci_used.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->loc_int.p, 0, c->loc_int.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->loc_ll.p, 0, c->loc_ll.bytes(), s));
@@ -174,41 +186,57 @@ int em_reset(clx_ctx* c) {
     return CLX_OK;
 }
 
-int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
-    if (!c->loaded) return fail(c, CLX_ERR_STATE, "clx_em_iteration before clx_load_coo");
+void em_drop_graph(clx_ctx* c) {
+    if (c->iter_graph_exec) cudaGraphExecDestroy((cudaGraphExec_t)c->iter_graph_exec);
+    c->iter_graph_exec = nullptr;
+    for (auto& p : c->graph_events) {
+        c->event_pool.push_back(p.a);
+        c->event_pool.push_back(p.b);
+    }
+    c->graph_events.clear();
+}
+
+namespace {
+
+// Every kernel of one compute_new_excluded pass, in stream order (also the body of the captured CUDA graph).
+int enqueue_iteration(clx_ctx* c) {
     cudaStream_t s = c->stream;
     const uint32_t N = c->n_cells, L = c->n_loci;
     const int with_e = (c->flags & CLX_FLAG_NO_EXPECTED) ? 0 : 1;
-    CLX_CUDA(c, cudaEventRecord(c->ev_iter_a, s));
-    CLX_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, sizeof(DeviceStats), s));
+    CLX_CUDA(c, cudaMemcpyAsync(c->d_params.p, c->h_params, sizeof(IterParams), cudaMemcpyHostToDevice, s));
 
-    // 1. alpha/beta + memo tables from the CURRENT excluded set (main.rs:309)
+    // 1. alpha/beta + memo tables from the CURRENT excluded set (main.rs:309); also clears d_stats
     phase_begin(c, CLX_PHASE_TABLES);
     if (L) {
-        k_tables<0><<<(L + 127) / 128, 128, 0, s>>>(c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L,
-                                                   L, make_lbc(c), 0.0, 0.0, with_e, c->tab.p);
+        k_tables<0><<<(L + TAB_LPB - 1) / TAB_LPB, TPB, 0, s>>>(
+            c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), 0.0, 0.0, with_e,
+            c->loci_used.p, c->tab.p, c->d_stats.p);
         c->launches++;
+    } else {
+        CLX_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, sizeof(DeviceStats), s));
     }
     phase_end(c, CLX_PHASE_TABLES);
 
     // 2. heavy entries, then the per-cell scoring pass (main.rs:312)
     phase_begin(c, CLX_PHASE_HEAVY);
     if (c->n_heavy) {
-        k_heavy<1><<<(unsigned)((c->n_heavy + 127) / 128), 128, 0, s>>>(c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy,
-                                                                      c->tab.p, L, c->loci_used.p, c->lnfact.p, with_e,
-                                                                      c->hv_ll.p, c->hv_e.p);
+        k_heavy_em<<<(unsigned)((c->n_heavy + HEAVY_HB - 1) / HEAVY_HB), TPB, 0, s>>>(
+            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, c->tab.p, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
         c->launches++;
+        if (c->n_giant) {
+            k_heavy_giant<<<c->n_giant, TPB, 0, s>>>(c->giant_idx.p, c->n_giant, c->h_locus.p, c->h_ref.p, c->h_alt.p, c->tab.p,
+                                                     c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+            c->launches++;
+        }
     }
     phase_end(c, CLX_PHASE_HEAVY);
     phase_begin(c, CLX_PHASE_SCORE);
-    {
-        const int G = pick_group(N ? (double)c->nnz / N : 0.0);
-        if (with_e) launch_score_rows<1, true>(c, G, c->loci_used.p);
-        else launch_score_rows<1, false>(c, G, c->loci_used.p);
-    }
+    if (with_e) launch_score_rows<1, true>(c, c->score_G);
+    else launch_score_rows<1, false>(c, c->score_G);
     phase_end(c, CLX_PHASE_SCORE);
 
     // 3. threshold from exact order statistics of the normalized log likelihoods (main.rs:313-329)
+    //    + new excluded set and change counts (main.rs:330-335)
     const double* sel_vals = c->norm.p;
     uint64_t n_vals = N;
     if (c->world > 1) {
@@ -219,12 +247,7 @@ int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
         n_vals = (uint64_t)c->world * c->max_local_cells;
     }
     phase_begin(c, CLX_PHASE_SELECT);
-    CLX_TRY(run_select(c, sel_vals, n_vals, c->n_cells_global, iqr_multiple));
-    // 4. new excluded set + change counts (main.rs:330-335)
-    if (N) {
-        k_exclude<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->norm.p, N, c->excl_bits.p, c->excl_bits_new.p, c->d_stats.p);
-        c->launches++;
-    }
+    CLX_TRY(run_select_exclude(c, sel_vals, n_vals, c->n_cells_global));
     phase_end(c, CLX_PHASE_SELECT);
     if (c->world > 1) {
         phase_begin(c, CLX_PHASE_COMM);
@@ -232,30 +255,70 @@ int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
         phase_end(c, CLX_PHASE_COMM);
     }
 
-    // 5. per-locus contributions split by the NEW set (main.rs:343) + minority allele counts for the next alpha/beta
+    // 4. per-locus contributions split by the NEW set (main.rs:343) + minority allele counts for the next
+    //    alpha/beta + the -80 locus filter (main.rs:444-451; after the allreduce when cells are sharded)
     phase_begin(c, CLX_PHASE_COLUMN);
-    launch_columns(c, pick_group(L ? (double)c->nnz / L : 0.0));
+    if (c->world > 1) launch_columns<false>(c, c->col_G);
+    else launch_columns<true>(c, c->col_G);
     phase_end(c, CLX_PHASE_COLUMN);
     if (c->world > 1) {
         phase_begin(c, CLX_PHASE_COMM);
         CLX_TRY(comm_allreduce_f64(c, c->loc_ll.p, 2 * (size_t)L));
         CLX_TRY(comm_allreduce_u64(c, c->loc_int.p, 8 * (size_t)L));
         phase_end(c, CLX_PHASE_COMM);
+        phase_begin(c, CLX_PHASE_COLUMN);
+        if (L) {
+            k_locus_filter<<<(L + TPB - 1) / TPB, TPB, 0, s>>>(c->loc_ll.p, c->loc_int.p, L, c->loci_used.p, c->d_stats.p);
+            c->launches++;
+        }
+        phase_end(c, CLX_PHASE_COLUMN);
     }
-    // 6. the -80 locus filter (main.rs:444-451)
-    phase_begin(c, CLX_PHASE_COLUMN);
-    if (L) {
-        k_locus_filter<<<(L + TPB - 1) / TPB, TPB, 0, s>>>(c->loc_ll.p, c->loc_int.p, L, c->loci_used.p, c->d_stats.p);
-        c->launches++;
-    }
-    phase_end(c, CLX_PHASE_COLUMN);
-
     CLX_CUDA(c, cudaMemcpyAsync(c->h_stats, c->d_stats.p, sizeof(DeviceStats), cudaMemcpyDeviceToHost, s));
+    return CLX_OK;
+}
+
+}  // namespace
+
+int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
+    if (!c->loaded) return fail(c, CLX_ERR_STATE, "clx_em_iteration before clx_load_coo");
+    cudaStream_t s = c->stream;
+    c->h_params->iqr_multiple = iqr_multiple;
+    // One-GPU contexts replay the iteration as a CUDA graph (a dozen launches, ~40 us of work at 10x scale:
+    // launch gaps matter).  Sharded contexts enqueue directly: NCCL calls sit between the kernels.
+    const bool use_graph = c->world == 1 && !(c->flags & CLX_FLAG_NO_GRAPH);
+    if (use_graph && !c->iter_graph_exec) {
+        cudaGraph_t graph = nullptr;
+        const uint64_t launches0 = c->launches;
+        CLX_CUDA(c, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+        c->capturing = true;
+        const int rc = enqueue_iteration(c);
+        c->capturing = false;
+        const cudaError_t e = cudaStreamEndCapture(s, &graph);
+        c->graph_launches = c->launches - launches0;
+        c->launches = launches0;
+        if (rc != CLX_OK) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc;
+        }
+        CLX_CUDA(c, e);
+        cudaGraphExec_t exec = nullptr;
+        const cudaError_t e2 = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        CLX_CUDA(c, e2);
+        c->iter_graph_exec = exec;
+    }
+    CLX_CUDA(c, cudaEventRecord(c->ev_iter_a, s));
+    if (use_graph) {
+        CLX_CUDA(c, cudaGraphLaunch((cudaGraphExec_t)c->iter_graph_exec, s));
+        c->launches += c->graph_launches;
+        c->graph_events_fresh = true;
+    } else {
+        CLX_TRY(enqueue_iteration(c));
+    }
     CLX_CUDA(c, cudaEventRecord(c->ev_iter_b, s));
     CLX_CUDA(c, cudaStreamSynchronize(s));
     CLX_CUDA(c, cudaGetLastError());
     phase_resolve(c);
-    std::swap(c->excl_bits.p, c->excl_bits_new.p);
     const DeviceStats& st = *c->h_stats;
     if (st.nan_flag) return fail(c, CLX_ERR_NAN, "NaN normalized log likelihood (the reference panics in argsort, main.rs:504)");
     c->n_excluded_global = st.n_excluded;
@@ -300,22 +363,22 @@ int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used
 
     phase_begin(c, CLX_PHASE_TABLES);
     if (L) {
-        k_tables<1><<<(unsigned)((3ull * L + 127) / 128), 128, 0, s>>>(c->locus_tot.p, c->loc_int.p + 6 * (size_t)L,
-                                                                     c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), mf_unclamped,
-                                                                     mf, 0, c->tab.p);
+        k_tables<1><<<3 * ((L + TAB_LPB - 1) / TAB_LPB), TPB, 0, s>>>(
+            c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), mf_unclamped, mf, 0,
+            nullptr, c->tab.p, nullptr);
         c->launches++;
     }
     phase_end(c, CLX_PHASE_TABLES);
     phase_begin(c, CLX_PHASE_HEAVY);
     if (c->n_heavy) {
-        k_heavy<3><<<(unsigned)((c->n_heavy + 127) / 128), 128, 0, s>>>(c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy,
-                                                                      c->tab.p, L, nullptr, c->lnfact.p, 0, c->hv_ll.p, c->hv_e.p);
+        k_heavy_post<<<(unsigned)((3 * c->n_heavy + TPB - 1) / TPB), TPB, 0, s>>>(
+            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, c->tab.p, L, c->lnfact.p, c->hv_ll.p);
         c->launches++;
     }
     phase_end(c, CLX_PHASE_HEAVY);
     // get_loci_used_for_posterior_calc pushes true on both branches (main.rs:301-303): every locus is scored
     phase_begin(c, CLX_PHASE_SCORE);
-    launch_score_rows<3, false>(c, pick_group(N ? (double)c->nnz / N : 0.0), nullptr);
+    launch_score_rows<3, false>(c, c->score_G);
     phase_end(c, CLX_PHASE_SCORE);
     if (N) {
         k_posterior<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->ll.p, N, c->row_ptr.p, c->excl_bits.p, pp, c->post.p, c->post_u8.p);
@@ -346,3 +409,4 @@ int em_final_locus_counts(clx_ctx* c, unsigned long long* d_min, unsigned long l
 }
 
 }  // namespace clx
+

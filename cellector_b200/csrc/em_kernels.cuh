@@ -17,82 +17,371 @@ struct Lbc10 {
     double v[10];
 };
 
+__device__ __forceinline__ double shfl_f64(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+__device__ __forceinline__ double quiet_nan() { return __longlong_as_double(0x7ff8000000000000ll); }
+
+// The table build is fp64-issue bound (a Lanczos ln_gamma is ~320 instructions), so the ln_gamma evaluations of
+// a CTA's TAB_LPB loci are laid out as one flat task list with every lane busy, results go to shared memory,
+// and a second phase combines them in the reference's expression order (stats.rs:41-53), so every value is
+// bit-identical to a one-thread evaluation.  Tasks of one locus:
+//   0..3   ln_gamma(i + alpha)          4..7   ln_gamma(i + beta)
+//   MODE 0 (alpha, beta integer-valued: (a + alpha) + (r + beta) is the same double for every a)
+//     8..10  ln_gamma((0 + alpha) + (n + beta)), n = 1..3        11  ln_gamma(alpha + beta)
+//   MODE 1 (alpha, beta scaled by the minority fraction: keep every (a | n) argument as the reference forms it)
+//     8..16  ln_gamma((a + alpha) + (r + beta)) for the nine (a | n) pairs        17  ln_gamma(alpha + beta)
+// A locus switched off by the -80 rule gets NaN in every T/E slot (slot 3 = 0.0 / NaN is the "used" marker
+// zero-total and heavy entries read): the scorer then needs no separate loci_used gather.  Block 0 also
+// clears the per-iteration DeviceStats.
+constexpr int TAB_LPB = 64;  // loci per CTA
 template <int MODE>
-__global__ void __launch_bounds__(128) k_tables(const unsigned long long* __restrict__ tot,
+__global__ void __launch_bounds__(256) k_tables(const unsigned long long* __restrict__ tot,
                                                 const unsigned long long* __restrict__ raw_min_ref,
                                                 const unsigned long long* __restrict__ raw_min_alt, uint32_t n_loci,
                                                 Lbc10 lbc, double mf, double mf_clamped, int with_expected,
-                                                double* __restrict__ tab) {
-    const uint64_t idx = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-    const uint32_t n_tab = MODE == 0 ? 1u : 3u;
-    if (idx >= (uint64_t)n_loci * n_tab) return;
-    const uint32_t t = (uint32_t)(idx / n_loci), l = (uint32_t)(idx % n_loci);
-    const double maj_a = (double)tot[2 * (size_t)l + 1] + 1.0 - (double)raw_min_alt[l];
-    const double maj_b = (double)tot[2 * (size_t)l] + 1.0 - (double)raw_min_ref[l];
-    double alpha = maj_a, beta = maj_b;
-    if (MODE == 1) {
-        // init_alpha_betas(locus_counts, included): totals + 1 - majority counts = minority counts + 1 (exact integers)
-        const double min_a = (double)raw_min_alt[l] + 1.0;
-        const double min_b = (double)raw_min_ref[l] + 1.0;
-        if (t == 0) {
-            alpha = min_a;
-            beta = min_b;
-        } else if (t == 1) {  // main.rs:250-254
-            alpha = (maj_a - 1.0) * mf_clamped + 1.0;
-            beta = (maj_b - 1.0) * mf_clamped + 1.0;
-        } else {  // main.rs:244-248, un-clamped fraction
-            alpha = (maj_a - 1.0) * mf + (min_a - 1.0) + 1.0;
-            beta = (maj_b - 1.0) * mf + (min_b - 1.0) + 1.0;
+                                                const uint8_t* __restrict__ used, double* __restrict__ tab,
+                                                DeviceStats* __restrict__ st_clear) {
+    static_assert(K_LIGHT == 3, "task layout below is for K_LIGHT == 3");
+    constexpr int NTASK = MODE == 0 ? 12 : 18;
+    constexpr int TDEN = NTASK - 1;  // task index of ln_gamma(alpha + beta)
+    __shared__ double s_ab[TAB_LPB][2];
+    __shared__ unsigned char s_on[TAB_LPB];
+    __shared__ double s_g[TAB_LPB][NTASK];
+    __shared__ double s_rec[TAB_LPB][TAB_STRIDE];
+    __shared__ double s_lbc[10];
+    if (st_clear != nullptr && blockIdx.x == 0 && threadIdx.x < sizeof(DeviceStats) / 8)
+        reinterpret_cast<unsigned long long*>(st_clear)[threadIdx.x] = 0ull;
+    const uint32_t blocks_per_tab = (n_loci + TAB_LPB - 1) / TAB_LPB;
+    const uint32_t t = blockIdx.x / blocks_per_tab;
+    const uint32_t l0 = (blockIdx.x % blocks_per_tab) * TAB_LPB;
+    const int tid = threadIdx.x;
+    if (tid < 10) s_lbc[tid] = lbc.v[tid];
+    if (tid < TAB_LPB) {
+        const uint32_t l = l0 + tid;
+        double alpha = 1.0, beta = 1.0;
+        bool on = false;
+        if (l < n_loci) {
+            const double maj_a = (double)tot[2 * (size_t)l + 1] + 1.0 - (double)raw_min_alt[l];
+            const double maj_b = (double)tot[2 * (size_t)l] + 1.0 - (double)raw_min_ref[l];
+            alpha = maj_a;
+            beta = maj_b;
+            if (MODE == 1) {
+                // init_alpha_betas(locus_counts, included): totals + 1 - majority counts = minority counts + 1
+                const double min_a = (double)raw_min_alt[l] + 1.0;
+                const double min_b = (double)raw_min_ref[l] + 1.0;
+                if (t == 0) {
+                    alpha = min_a;
+                    beta = min_b;
+                } else if (t == 1) {  // main.rs:250-254
+                    alpha = (maj_a - 1.0) * mf_clamped + 1.0;
+                    beta = (maj_b - 1.0) * mf_clamped + 1.0;
+                } else {  // main.rs:244-248, un-clamped fraction
+                    alpha = (maj_a - 1.0) * mf + (min_a - 1.0) + 1.0;
+                    beta = (maj_b - 1.0) * mf + (min_b - 1.0) + 1.0;
+                }
+            }
+            on = used == nullptr || used[l] != 0;
+        }
+        s_ab[tid][0] = alpha;
+        s_ab[tid][1] = beta;
+        s_on[tid] = on ? 1 : 0;
+    }
+    __syncthreads();
+    // phase 1: flat ln_gamma task list
+    for (int task = tid; task < TAB_LPB * NTASK; task += blockDim.x) {
+        const int ll = task / NTASK, j = task % NTASK;
+        if (!s_on[ll]) continue;
+        const double alpha = s_ab[ll][0], beta = s_ab[ll][1];
+        double x;
+        if (j < 4) x = (double)j + alpha;
+        else if (j < 8) x = (double)(j - 4) + beta;
+        else if (j == TDEN) x = alpha + beta;
+        else if (MODE == 0) x = (0.0 + alpha) + ((double)(j - 7) + beta);
+        else {
+            const int p = j - 8;
+            const int pn = p < 2 ? 1 : (p < 5 ? 2 : 3);
+            const int pa = p < 2 ? p : (p < 5 ? p - 2 : p - 5);
+            x = ((double)pa + alpha) + ((double)(pn - pa) + beta);
+        }
+        s_g[ll][j] = ln_gamma(x);
+    }
+    __syncthreads();
+    // phase 2a: T(a | n) = lbc + (lga[a] + lgb[r] - lgab) - den for the nine pairs; record tail
+    for (int task = tid; task < TAB_LPB * 16; task += blockDim.x) {
+        const int ll = task >> 4, slot = task & 15;
+        const bool on = s_on[ll] != 0;
+        const double* g = s_g[ll];
+        double out = quiet_nan();
+        if (slot == TAB_ALPHA) out = s_ab[ll][0];
+        else if (slot == TAB_BETA) out = s_ab[ll][1];
+        else if (on) {
+            // log_beta_calc(alpha, beta): ln_gamma(0 + alpha), ln_gamma(0 + beta) share their argument bits with tasks 0 / 4
+            const double den = g[0] + g[4] - g[TDEN];
+            if (slot == TAB_DEN) out = den;
+            else if (slot == 3) out = 0.0;
+            else if (slot < 12) {
+                const int pn = (slot >> 2) + 1, pa = slot & 3;
+                if (pa <= pn) {
+                    const int third = MODE == 0 ? 7 + pn : 8 + (pn == 1 ? 0 : (pn == 2 ? 2 : 5)) + pa;
+                    const double num = g[pa] + g[4 + (pn - pa)] - g[third];
+                    out = s_lbc[lbc_idx(pa, pn)] + num - den;
+                }
+            }
+        }
+        s_rec[ll][slot] = out;
+    }
+    __syncthreads();
+    // phase 2b: expected_log_likelihood (stats.rs:17-22), one thread per (locus, n), left-to-right chain
+    if (tid < TAB_LPB * K_LIGHT) {
+        const int ll = tid / K_LIGHT, n = tid % K_LIGHT + 1;
+        if (s_on[ll]) {
+            double e = 0.0;
+            if (with_expected) {
+                e = 2.0 * s_rec[ll][tab_idx_T(0, n)];
+                for (int k = 1; k <= n; ++k) e = logsumexp2(e, 2.0 * s_rec[ll][tab_idx_T(k, n)]);
+            }
+            s_rec[ll][tab_idx_E(n)] = e;
         }
     }
-    double out[TAB_STRIDE];
-    build_locus_table(alpha, beta, lbc.v, with_expected != 0, out);
-    double4* dst = reinterpret_cast<double4*>(tab + ((size_t)t * n_loci + l) * TAB_STRIDE);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) dst[i] = make_double4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+    __syncthreads();
+    // coalesced store of the CTA's records (slots 2, 7, 12 were written by phase 2b after 2a left NaN there)
+    const uint32_t n_here = n_loci - l0 < (uint32_t)TAB_LPB ? n_loci - l0 : (uint32_t)TAB_LPB;
+    double* dst = tab + ((size_t)t * n_loci + l0) * TAB_STRIDE;
+    for (uint32_t i = tid; i < n_here * TAB_STRIDE; i += blockDim.x) dst[i] = (&s_rec[0][0])[i];
 }
 
 // ------------------------------------------------------------------------------------------------
 // Heavy entries (total > K_LIGHT): direct evaluation with the same expressions (stats.rs:41-53, 8-22).
-template <int NT>
-__global__ void __launch_bounds__(128) k_heavy(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
-                                               const uint32_t* __restrict__ h_alt, uint32_t n_heavy,
-                                               const double* __restrict__ tab, uint32_t n_loci,
-                                               const uint8_t* __restrict__ used, const double* __restrict__ lnfact,
-                                               int with_expected, double* __restrict__ hv_ll, double* __restrict__ hv_e) {
-    const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
-    if (h >= n_heavy) return;
-    const uint32_t l = h_locus[h];
-    const bool on = used == nullptr || used[l] != 0;
-    const uint64_t a = h_alt[h], r = h_ref[h], n = a + r;
-    const double lbc = on ? ln_binomial(n, a, lnfact) : 0.0;
-#pragma unroll
-    for (int t = 0; t < NT; ++t) {
-        double v = 0.0;
-        const double* rec = tab + ((size_t)t * n_loci + l) * TAB_STRIDE;
-        if (on) v = log_beta_binomial_pmf_den((double)a, (double)r, rec[TAB_ALPHA], rec[TAB_BETA], lbc, rec[TAB_DEN]);
-        hv_ll[(size_t)t * n_heavy + h] = v;
+//
+// EM pass (k_heavy_em): a CTA takes HEAVY_HB consecutive entries.  An entry of total n needs
+//   ln_gamma(k + alpha), k = 0..n     ln_gamma(j + beta), j = 0..n     ln_gamma((a + alpha) + (r + beta))
+// (alpha, beta are integer-valued in the EM pass, so the third argument is the same double for every split k of n,
+// and pmf(k = alt) is the entry's own log_pmf).  These 2(n+1)+1 evaluations form a flat task list over the CTA —
+// all lanes busy — with results in shared memory; then ll_k = ln C(n,k) + (lga[k] + lgb[n-k] - lgab) - den, and the
+// expected-log-likelihood chain runs left to right per entry like stats.rs:17-22 (entries with n > HEAVY_CHAIN_MAX
+// use a warp-wide max/sum logsumexp instead: same value to ~1e-16 relative, diagnostic column only).
+// Entries with n > HEAVY_GIANT are left to k_heavy_giant (one CTA each).
+constexpr int HEAVY_HB = 64;
+constexpr int HEAVY_CAP = 2560;        // ln_gamma results per round (20 KB) + as many pmf slots
+constexpr uint32_t HEAVY_GIANT = HEAVY_GIANT_TOTAL;  // 2(n+1)+1 <= HEAVY_CAP
+static_assert(2 * (HEAVY_GIANT_TOTAL + 1) + 1 <= HEAVY_CAP, "a non-giant entry must fit one round");
+constexpr uint32_t HEAVY_CHAIN_MAX = 32;
+
+__device__ __forceinline__ double heavy_ll_k(uint64_t n, uint64_t k, const double* __restrict__ lga,
+                                             const double* __restrict__ lgb, double lgab, double den,
+                                             const double* __restrict__ lnfact) {
+    const double num = lga[k] + lgb[n - k] - lgab;
+    return ln_binomial(n, k, lnfact) + num - den;
+}
+
+__global__ void __launch_bounds__(256) k_heavy_em(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
+                                                  const uint32_t* __restrict__ h_alt, uint32_t n_heavy,
+                                                  const double* __restrict__ tab, const double* __restrict__ lnfact,
+                                                  int with_expected, double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+    __shared__ double s_g[HEAVY_CAP];
+    __shared__ double s_ll[HEAVY_CAP];  // pmf k of the entry whose tasks start at g0 sits at s_ll[g0 + k]
+    __shared__ double s_alpha[HEAVY_HB], s_beta[HEAVY_HB], s_den[HEAVY_HB];
+    __shared__ uint32_t s_n[HEAVY_HB], s_a[HEAVY_HB], s_off[HEAVY_HB + 1];
+    __shared__ int s_range[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t h0 = blockIdx.x * HEAVY_HB;
+    const uint32_t n_here = n_heavy - h0 < (uint32_t)HEAVY_HB ? n_heavy - h0 : (uint32_t)HEAVY_HB;
+    if (tid < HEAVY_HB) {
+        uint32_t ntask = 0, n = 0, a = 0;
+        double alpha = 1.0, beta = 1.0, den = 0.0;
+        if ((uint32_t)tid < n_here) {
+            const uint32_t h = h0 + tid;
+            const double* rec = tab + (size_t)h_locus[h] * TAB_STRIDE;
+            a = h_alt[h];
+            const uint64_t nn = (uint64_t)a + h_ref[h];
+            alpha = rec[TAB_ALPHA];
+            beta = rec[TAB_BETA];
+            den = rec[TAB_DEN];
+            const bool on = den == den;  // NaN den marks a locus that is switched off: contributes nothing
+            if (!on) {
+                hv_ll[h] = 0.0;
+                hv_e[h] = 0.0;
+            } else if (nn <= HEAVY_GIANT) {
+                n = (uint32_t)nn;
+                ntask = with_expected ? 2 * (n + 1) + 1 : 3;
+            }
+        }
+        s_alpha[tid] = alpha; s_beta[tid] = beta; s_den[tid] = den;
+        s_n[tid] = n; s_a[tid] = a;
+        s_off[tid + 1] = ntask;
     }
-    if (NT == 1) {
-        double e = 0.0;
-        if (on && with_expected) e = expected_ll_direct(n, tab[(size_t)l * TAB_STRIDE + TAB_ALPHA],
-                                                        tab[(size_t)l * TAB_STRIDE + TAB_BETA],
-                                                        tab[(size_t)l * TAB_STRIDE + TAB_DEN], lnfact);
-        hv_e[h] = e;
+    if (tid == 0) s_off[0] = 0;
+    __syncthreads();
+    if (tid == 0) {
+        for (int i = 0; i < HEAVY_HB; ++i) s_off[i + 1] += s_off[i];
+        s_range[0] = 0;
+    }
+    __syncthreads();
+    for (;;) {
+        const int e0 = s_range[0];
+        if (e0 >= (int)n_here) break;
+        __syncthreads();
+        if (tid == 0) {  // as many consecutive entries as fit in the result buffer
+            int e1 = e0 + 1;
+            while (e1 < (int)n_here && s_off[e1 + 1] - s_off[e0] <= (uint32_t)HEAVY_CAP) ++e1;
+            s_range[1] = e1;
+        }
+        __syncthreads();
+        const int e1 = s_range[1];
+        const uint32_t base = s_off[e0], total = s_off[e1] - base;
+        // phase 1: flat ln_gamma tasks
+        for (uint32_t task = tid; task < total; task += blockDim.x) {
+            int lo = e0, hi = e1 - 1;  // entry e with s_off[e] <= base + task < s_off[e + 1]
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (s_off[mid] <= base + task) lo = mid;
+                else hi = mid - 1;
+            }
+            const uint32_t j = base + task - s_off[lo], n = s_n[lo], a = s_a[lo];
+            const double alpha = s_alpha[lo], beta = s_beta[lo];
+            double x;
+            if (with_expected) {
+                if (j <= n) x = (double)j + alpha;
+                else if (j <= 2 * n + 1) x = (double)(j - n - 1) + beta;
+                else x = ((double)a + alpha) + ((double)(n - a) + beta);
+            } else {
+                x = j == 0 ? (double)a + alpha : (j == 1 ? (double)(n - a) + beta : ((double)a + alpha) + ((double)(n - a) + beta));
+            }
+            s_g[task] = ln_gamma(x);
+        }
+        __syncthreads();
+        if (with_expected) {
+            // phase 2a: ll_k for every (entry, k)
+            for (uint32_t task = tid; task < total; task += blockDim.x) {
+                int lo = e0, hi = e1 - 1;
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (s_off[mid] <= base + task) lo = mid;
+                    else hi = mid - 1;
+                }
+                const uint32_t j = base + task - s_off[lo], n = s_n[lo];
+                if (j > n) continue;
+                const uint32_t g0 = s_off[lo] - base;
+                s_ll[g0 + j] = heavy_ll_k(n, j, s_g + g0, s_g + g0 + n + 1, s_g[g0 + 2 * n + 2], s_den[lo], lnfact);
+            }
+            __syncthreads();
+            // phase 2b: per entry, own log_pmf = ll_{alt}; chain over k
+            for (int e = e0 + tid; e < e1; e += blockDim.x) {
+                const uint32_t n = s_n[e];
+                if (s_off[e + 1] == s_off[e]) continue;  // switched off or giant
+                const uint32_t p0 = s_off[e] - base;
+                hv_ll[h0 + e] = s_ll[p0 + s_a[e]];
+                if (n <= HEAVY_CHAIN_MAX) {
+                    double ex = 2.0 * s_ll[p0];
+                    for (uint32_t k = 1; k <= n; ++k) ex = logsumexp2(ex, 2.0 * s_ll[p0 + k]);
+                    hv_e[h0 + e] = ex;
+                }
+            }
+            // deep entries: one warp each, max / sum form of the same logsumexp
+            for (int e = e0 + warp; e < e1; e += (int)(blockDim.x >> 5)) {
+                const uint32_t n = s_n[e];
+                if (s_off[e + 1] == s_off[e] || n <= HEAVY_CHAIN_MAX) continue;
+                const uint32_t p0 = s_off[e] - base;
+                double m = -INFINITY;
+                for (uint32_t k = lane; k <= n; k += 32) m = fmax(m, 2.0 * s_ll[p0 + k]);
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, off));
+                double sum = 0.0;
+                for (uint32_t k = lane; k <= n; k += 32) sum += exp(2.0 * s_ll[p0 + k] - m);
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+                if (lane == 0) hv_e[h0 + e] = m + log(sum);
+            }
+        } else {
+            for (int e = e0 + tid; e < e1; e += blockDim.x) {
+                if (s_off[e + 1] == s_off[e]) continue;
+                const uint32_t g0 = s_off[e] - base, n = s_n[e], a = s_a[e];
+                const double num = s_g[g0] + s_g[g0 + 1] - s_g[g0 + 2];
+                hv_ll[h0 + e] = ln_binomial(n, a, lnfact) + num - s_den[e];
+                hv_e[h0 + e] = 0.0;
+            }
+        }
+        __syncthreads();
+        if (tid == 0) s_range[0] = e1;
+        __syncthreads();
     }
 }
 
+// One CTA per giant entry (total > HEAVY_GIANT): streaming max / sum logsumexp over k = 0..n in fixed chunks.
+__global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict__ giant_idx, uint32_t n_giant,
+                                                     const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
+                                                     const uint32_t* __restrict__ h_alt, const double* __restrict__ tab,
+                                                     const double* __restrict__ lnfact, int with_expected,
+                                                     double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+    __shared__ double s_m[8], s_s[8];
+    const uint32_t h = giant_idx[blockIdx.x];
+    const double* rec = tab + (size_t)h_locus[h] * TAB_STRIDE;
+    const double alpha = rec[TAB_ALPHA], beta = rec[TAB_BETA], den = rec[TAB_DEN];
+    if (!(den == den)) return;  // switched off: k_heavy_em wrote the zeros
+    const uint64_t a = h_alt[h], r = h_ref[h], n = a + r;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) hv_ll[h] = log_beta_binomial_pmf_den((double)a, (double)r, alpha, beta, ln_binomial(n, a, lnfact), den);
+    if (!with_expected) {
+        if (tid == 0) hv_e[h] = 0.0;
+        return;
+    }
+    double m = -INFINITY, sum = 0.0;  // running max and sum of exp(2 ll_k - m)
+    for (uint64_t k = tid; k <= n; k += blockDim.x) {
+        const double v = 2.0 * log_beta_binomial_pmf_den((double)k, (double)(n - k), alpha, beta, ln_binomial(n, k, lnfact), den);
+        if (v > m) {
+            sum = sum * exp(m - v) + 1.0;
+            m = v;
+        } else {
+            sum += exp(v - m);
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const double m2 = __shfl_xor_sync(0xffffffffu, m, off), s2 = __shfl_xor_sync(0xffffffffu, sum, off);
+        const double mm = fmax(m, m2);
+        sum = (m == -INFINITY ? 0.0 : sum * exp(m - mm)) + (m2 == -INFINITY ? 0.0 : s2 * exp(m2 - mm));
+        m = mm;
+    }
+    if (lane == 0) { s_m[warp] = m; s_s[warp] = sum; }
+    __syncthreads();
+    if (tid == 0) {
+        double M = s_m[0], S = s_s[0];
+        for (int w = 1; w < 8; ++w) {
+            const double mm = fmax(M, s_m[w]);
+            S = (M == -INFINITY ? 0.0 : S * exp(M - mm)) + (s_m[w] == -INFINITY ? 0.0 : s_s[w] * exp(s_m[w] - mm));
+            M = mm;
+        }
+        hv_e[h] = M + log(S);
+    }
+}
+
+// Posterior pass (three tables, no expected-log-likelihood): one thread per (entry, table).
+__global__ void __launch_bounds__(256) k_heavy_post(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
+                                                    const uint32_t* __restrict__ h_alt, uint32_t n_heavy,
+                                                    const double* __restrict__ tab, uint32_t n_loci,
+                                                    const double* __restrict__ lnfact, double* __restrict__ hv_ll) {
+    const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (i >= 3ull * n_heavy) return;
+    const uint32_t t = (uint32_t)(i / n_heavy), h = (uint32_t)(i % n_heavy);
+    const double* rec = tab + ((size_t)t * n_loci + h_locus[h]) * TAB_STRIDE;
+    const uint64_t a = h_alt[h], r = h_ref[h];
+    hv_ll[(size_t)t * n_heavy + h] =
+        log_beta_binomial_pmf_den((double)a, (double)r, rec[TAB_ALPHA], rec[TAB_BETA], ln_binomial(a + r, a, lnfact), rec[TAB_DEN]);
+}
+
 // ------------------------------------------------------------------------------------------------
-// v0 scoring kernel (get_cell_log_likelihoods, main.rs:541-591): G lanes per CSR row, 128-bit loads of two
-// packed entries, memo-table gathers served by L2, xor-shuffle tree, heavy values appended in row order.
+// Gather scoring kernel (get_cell_log_likelihoods, main.rs:541-591) for matrices whose memo table stays in L2:
+// G lanes per CSR row, U independent 128-bit loads of two packed entries per lane in flight, one memo-table
+// sector per entry (NaN = locus switched off), xor-shuffle tree, heavy values appended in row order.
+constexpr int SCORE_UNROLL = 4;
 template <int G, int NT, bool WITH_E>
 __global__ void __launch_bounds__(256) k_score_rows(const RowEntry* __restrict__ csr, const uint64_t* __restrict__ row_ptr,
                                                     uint32_t n_cells, const double* __restrict__ tab, uint32_t n_loci,
-                                                    const uint8_t* __restrict__ used, const uint32_t* __restrict__ h_row_ptr,
+                                                    const uint32_t* __restrict__ h_row_ptr,
                                                     const double* __restrict__ hv_ll, const double* __restrict__ hv_e,
                                                     uint32_t n_heavy, double* __restrict__ ll, double* __restrict__ ell,
                                                     uint32_t* __restrict__ nloci, double* __restrict__ norm,
                                                     unsigned int* __restrict__ nan_flag) {
+    constexpr int U = SCORE_UNROLL;
     const uint32_t gid = (blockIdx.x * blockDim.x + threadIdx.x) / G;
     const uint32_t g = threadIdx.x % G;
     const bool live = gid < n_cells;
@@ -103,23 +392,43 @@ __global__ void __launch_bounds__(256) k_score_rows(const RowEntry* __restrict__
     for (int t = 0; t < NT; ++t) acc[t] = 0.0;
     double acc_e = 0.0;
     uint32_t cnt = 0;
-    for (uint64_t i = (begin & ~1ull) + 2ull * g; i < end; i += 2ull * G) {
-        const uint4 q = __ldg(reinterpret_cast<const uint4*>(csr + i));
-        const uint32_t loc[2] = {q.x, q.z};
-        const uint32_t cnts[2] = {q.y, q.w};
+    const size_t tstride = (size_t)n_loci * TAB_STRIDE;
+    for (uint64_t i0 = (begin & ~1ull) + 2ull * g; i0 < end; i0 += 2ull * G * U) {
+        uint4 q[U];
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const uint64_t idx = i + k;
-            if (idx < begin || idx >= end) continue;
-            const uint32_t l = loc[k];
-            if (used != nullptr && used[l] == 0) continue;
-            ++cnt;
-            const uint32_t r = cnts[k] & 0xFFFFu, a = cnts[k] >> 16, n = r + a;
-            if (n == 0 || n > (uint32_t)K_LIGHT) continue;  // exact zero / heavy list
-            const double* rec = tab + (size_t)l * TAB_STRIDE;
+        for (int u = 0; u < U; ++u) {
+            const uint64_t i = i0 + 2ull * G * u;
+            q[u] = i < end ? __ldg(reinterpret_cast<const uint4*>(csr + i)) : make_uint4(0u, 0u, 0u, 0u);
+        }
+        double v[U][2][NT], ev[U][2];
+        bool ok[U][2];
 #pragma unroll
-            for (int t = 0; t < NT; ++t) acc[t] += __ldg(rec + (size_t)t * n_loci * TAB_STRIDE + tab_idx_T((int)a, (int)n));
-            if (WITH_E) acc_e += __ldg(rec + tab_idx_E((int)n));
+        for (int u = 0; u < U; ++u) {
+            const uint32_t loc[2] = {q[u].x, q[u].z};
+            const uint32_t cnts[2] = {q[u].y, q[u].w};
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const uint64_t idx = i0 + 2ull * G * u + k;
+                ok[u][k] = idx >= begin && idx < end;
+                const uint32_t r = cnts[k] & 0xFFFFu, a = cnts[k] >> 16, n = r + a;
+                const bool light = (n - 1u) < (uint32_t)K_LIGHT;  // zero-total and heavy entries read the marker slot
+                const double* rec = tab + (size_t)(ok[u][k] ? loc[k] : 0u) * TAB_STRIDE;
+                const int st = light ? tab_idx_T((int)a, (int)n) : 3;
+#pragma unroll
+                for (int t = 0; t < NT; ++t) v[u][k][t] = ok[u][k] ? __ldg(rec + (size_t)t * tstride + st) : 0.0;
+                if (WITH_E) ev[u][k] = ok[u][k] ? __ldg(rec + (light ? 5 * (int)n - 3 : 3)) : 0.0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const bool used = ok[u][k] && (v[u][k][0] == v[u][k][0]);
+                cnt += used ? 1u : 0u;
+#pragma unroll
+                for (int t = 0; t < NT; ++t) acc[t] += used ? v[u][k][t] : 0.0;
+                if (WITH_E) acc_e += used ? ev[u][k] : 0.0;
+            }
         }
     }
 #pragma unroll
@@ -149,39 +458,43 @@ __global__ void __launch_bounds__(256) k_score_rows(const RowEntry* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------
-// Exclusion (main.rs:330-335): new set = {i : norm_i < threshold}; one warp writes one 32-bit word.
-__global__ void __launch_bounds__(256) k_exclude(const double* __restrict__ norm, uint32_t n_cells,
-                                                 const uint32_t* __restrict__ old_bits, uint32_t* __restrict__ new_bits,
-                                                 DeviceStats* __restrict__ st) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const double thr = st->threshold;
+// Exclusion (main.rs:330-335): new set = {i : norm_i < threshold}; one warp rewrites one 32-bit word in place.
+__device__ __forceinline__ void exclude_word(const double* __restrict__ norm, uint32_t n_cells, uint32_t i, double thr,
+                                             uint32_t* __restrict__ bits, DeviceStats* __restrict__ st) {
     const bool ex = i < n_cells && norm[i] < thr;
     const uint32_t word = __ballot_sync(0xffffffffu, ex);
     if ((threadIdx.x & 31) == 0 && i < n_cells) {
         const uint32_t w = i >> 5;
-        const uint32_t old = old_bits[w];
-        new_bits[w] = word;
+        const uint32_t old = bits[w];
+        bits[w] = word;
         const uint32_t nn = __popc(word & ~old), nr = __popc(old & ~word), ne = __popc(word);
         if (nn) atomicAdd(&st->n_new, (unsigned long long)nn);
         if (nr) atomicAdd(&st->n_rescued, (unsigned long long)nr);
         if (ne) atomicAdd(&st->n_excluded, (unsigned long long)ne);
     }
 }
+__global__ void __launch_bounds__(256) k_exclude(const double* __restrict__ norm, uint32_t n_cells,
+                                                 uint32_t* __restrict__ bits, DeviceStats* __restrict__ st) {
+    exclude_word(norm, n_cells, blockIdx.x * blockDim.x + threadIdx.x, st->threshold, bits, st);
+}
 
 // ------------------------------------------------------------------------------------------------
 // Column pass (get_locus_log_likelihoods, main.rs:368-420) fused with the allele counts of the excluded cells
-// that the next iteration's init_alpha_betas needs.  G lanes per CSC column, cells ascending, fixed xor tree
-// (no floating-point atomics); heavy entries are appended by lane 0 in column order.
+// that the next iteration's init_alpha_betas needs and, on one GPU, with the -80 locus filter (main.rs:431-451).
+// G lanes per CSC column, cells ascending, fixed xor tree (no floating-point atomics); the column's memo record
+// is one L1-resident line; heavy entries are appended by lane 0 in column order.
 // loc_ll  : [0,L) minority sum log_pmf, [L,2L) majority.
 // loc_int : 8 arrays of L: cells_min, cells_maj, ref_min, alt_min, ref_maj, alt_maj, raw_min_ref, raw_min_alt.
-template <int G>
+template <int G, bool FUSE_FILTER>
 __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ csc, const uint64_t* __restrict__ col_ptr,
                                                  uint32_t n_loci, const double* __restrict__ tab,
-                                                 const uint8_t* __restrict__ used, const uint32_t* __restrict__ excl_bits,
+                                                 uint8_t* __restrict__ used, const uint32_t* __restrict__ excl_bits,
                                                  const uint32_t* __restrict__ hc_col_ptr, const uint32_t* __restrict__ hc_perm,
                                                  const uint32_t* __restrict__ h_cell, const uint32_t* __restrict__ h_ref,
                                                  const uint32_t* __restrict__ h_alt, const double* __restrict__ hv_ll,
-                                                 double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int) {
+                                                 double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int,
+                                                 DeviceStats* __restrict__ st) {
+    constexpr int U = SCORE_UNROLL;
     const uint32_t gid = (blockIdx.x * blockDim.x + threadIdx.x) / G;
     const uint32_t g = threadIdx.x % G;
     const bool live = gid < n_loci;
@@ -190,22 +503,35 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
     const double* rec = tab + (size_t)l * TAB_STRIDE;
     double s_min = 0.0, s_maj = 0.0;
     uint32_t c_min = 0, c_maj = 0, r_min = 0, a_min = 0, r_maj = 0, a_maj = 0;
-    for (uint64_t i = (begin & ~1ull) + 2ull * g; i < end; i += 2ull * G) {
-        const uint4 q = __ldg(reinterpret_cast<const uint4*>(csc + i));
-        const uint32_t cel[2] = {q.x, q.z};
-        const uint32_t cnts[2] = {q.y, q.w};
+    for (uint64_t i0 = (begin & ~1ull) + 2ull * g; i0 < end; i0 += 2ull * G * U) {
+        uint4 q[U];
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const uint64_t idx = i + k;
-            if (idx < begin || idx >= end) continue;
-            const uint32_t c = cel[k];
-            const bool ex = (__ldg(excl_bits + (c >> 5)) >> (c & 31)) & 1u;
-            const uint32_t r = cnts[k] & 0xFFFFu, a = cnts[k] >> 16, n = r + a;
-            if (ex) ++c_min; else ++c_maj;
-            if (n == 0 || n > (uint32_t)K_LIGHT) continue;
-            const double v = __ldg(rec + tab_idx_T((int)a, (int)n));
-            if (ex) { s_min += v; r_min += r; a_min += a; }
-            else    { s_maj += v; r_maj += r; a_maj += a; }
+        for (int u = 0; u < U; ++u) {
+            const uint64_t i = i0 + 2ull * G * u;
+            q[u] = i < end ? __ldg(reinterpret_cast<const uint4*>(csc + i)) : make_uint4(0u, 0u, 0u, 0u);
+        }
+        uint32_t w[U][2];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            w[u][0] = __ldg(excl_bits + (q[u].x >> 5));
+            w[u][1] = __ldg(excl_bits + (q[u].z >> 5));
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t cel[2] = {q[u].x, q[u].z};
+            const uint32_t cnts[2] = {q[u].y, q[u].w};
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const uint64_t idx = i0 + 2ull * G * u + k;
+                if (idx < begin || idx >= end) continue;
+                const bool ex = (w[u][k] >> (cel[k] & 31)) & 1u;
+                const uint32_t r = cnts[k] & 0xFFFFu, a = cnts[k] >> 16, n = r + a;
+                if (ex) ++c_min; else ++c_maj;
+                if ((n - 1u) >= (uint32_t)K_LIGHT) continue;  // exact zero / heavy list
+                const double v = __ldg(rec + tab_idx_T((int)a, (int)n));  // this column's record: one hot L1 line
+                if (ex) { s_min += v; r_min += r; a_min += a; }
+                else    { s_maj += v; r_maj += r; a_maj += a; }
+            }
         }
     }
 #pragma unroll
@@ -219,6 +545,7 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
         r_maj += __shfl_xor_sync(0xffffffffu, r_maj, off);
         a_maj += __shfl_xor_sync(0xffffffffu, a_maj, off);
     }
+    bool filtered = false, in_use = false;
     if (live && g == 0) {
         unsigned long long R_min = r_min, A_min = a_min, R_maj = r_maj, A_maj = a_maj;
         const uint32_t hb = hc_col_ptr[l], he = hc_col_ptr[l + 1];
@@ -242,6 +569,22 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
         loc_int[5 * L + l] = on ? A_maj : 0;
         loc_int[6 * L + l] = R_min;  // init_alpha_betas subtracts every stored entry of an excluded cell (main.rs:603-608)
         loc_int[7 * L + l] = A_min;
+        if (FUSE_FILTER) {  // main.rs:431-451 on this locus
+            const double per_cell = (on && c_min != 0) ? s_min / (double)c_min : 0.0;
+            if (per_cell < -80.0) {
+                filtered = on;
+                used[l] = 0;
+            } else {
+                in_use = on;
+            }
+        }
+    }
+    if (FUSE_FILTER) {
+        const uint32_t f = __popc(__ballot_sync(0xffffffffu, filtered)), u = __popc(__ballot_sync(0xffffffffu, in_use));
+        if ((threadIdx.x & 31) == 0) {
+            if (f) atomicAdd(&st->n_loci_filtered, (unsigned long long)f);
+            if (u) atomicAdd(&st->n_loci_in_use, (unsigned long long)u);
+        }
     }
 }
 

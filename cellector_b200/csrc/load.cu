@@ -61,6 +61,12 @@ struct FlagAt {
     const uint32_t* idx;  // optional indirection
     __device__ bool operator()(uint32_t i) const { return flag[idx ? idx[i] : i] != 0; }
 };
+struct GiantAt {
+    const uint32_t* ref;
+    const uint32_t* alt;
+    uint64_t limit;
+    __device__ bool operator()(uint32_t h) const { return (uint64_t)ref[h] + (uint64_t)alt[h] > limit; }
+};
 struct ToU64 {
     __device__ uint64_t operator()(uint32_t v) const { return (uint64_t)v; }
 };
@@ -345,6 +351,21 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, hcpos.p, n_sel.p, (int)nnz, f2, s));
         k_heavy_perm<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, csc_src.p, hpos.p, n_heavy, c->hc_perm.p);
         c->launches += 4;
+    }
+    // entries too deep for the batched heavy kernel get a CTA each (em_kernels.cuh: k_heavy_giant)
+    c->n_giant = 0;
+    CLX_CUDA(c, c->giant_idx.alloc(n_heavy));
+    if (n_heavy) {
+        cub::CountingInputIterator<uint32_t> counting(0);
+        GiantAt gp{c->h_ref.p, c->h_alt.p, (uint64_t)HEAVY_GIANT_TOTAL};
+        CLX_CUDA(c, cub::DeviceSelect::If(nullptr, tmp_bytes, counting, c->giant_idx.p, n_sel.p, (int)n_heavy, gp, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, c->giant_idx.p, n_sel.p, (int)n_heavy, gp, s));
+        c->launches += 2;
+        uint32_t ng = 0;
+        CLX_CUDA(c, cudaMemcpyAsync(&ng, n_sel.p, 4, cudaMemcpyDeviceToHost, s));
+        CLX_CUDA(c, cudaStreamSynchronize(s));
+        c->n_giant = ng;
     }
     k_segment_ptr<<<(n_cells + 1 + TPB - 1) / TPB, TPB, 0, s>>>(hpos.p, n_heavy, c->row_ptr.p, n_cells, c->h_row_ptr.p);
     k_segment_ptr<<<(n_loci + 1 + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, n_heavy, c->col_ptr.p, n_loci, c->hc_col_ptr.p);

@@ -21,6 +21,8 @@ namespace clx {
 
 // Totals 1..K_LIGHT are memoised per locus; deeper entries go to the heavy list (direct Lanczos).
 constexpr int K_LIGHT = 3;
+// Heavy entries deeper than this are evaluated by one CTA each (k_heavy_giant) instead of the batched kernel.
+constexpr uint32_t HEAVY_GIANT_TOTAL = 1000;
 // One 128-byte record per locus, laid out so that everything an entry of total n needs sits in one
 // 32-byte sector:   [0..1] T(a=0..1 | n=1)  [2] E(1)  [3] -
 //                   [4..6] T(a=0..2 | n=2)  [7] E(2)
@@ -98,9 +100,12 @@ CLX_HD double log_beta_binomial_pmf_den(double alt, double ref, double alpha, do
     const double ln_numerator = log_beta_calc(alt + alpha, ref + beta);
     return ln_coefficient + ln_numerator - den;
 }
+// stats.rs:35-39: max + ln(exp(v1 - max) + exp(v2 - max)).  One of the two differences is exactly 0 and
+// exp(0) == 1 exactly, so the sum is 1 + exp(other difference) bit for bit: (v1 - mx) + (v2 - mx) adds an exact
+// zero to the other difference (and still propagates NaN), which saves one of the two exp evaluations.
 CLX_HD double logsumexp2(double v1, double v2) {
     const double mx = fmax(v1, v2);
-    const double sum = exp(v1 - mx) + exp(v2 - mx);
+    const double sum = 1.0 + exp((v1 - mx) + (v2 - mx));
     return mx + log(sum);
 }
 

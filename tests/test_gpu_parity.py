@@ -39,6 +39,32 @@ def test_parity_synthetic(libs, name):
         assert n_it >= 1
 
 
+@pytest.mark.parametrize("flags", [16, 1, 1 | 16, 2], ids=["no_graph", "profile_graph", "profile_no_graph", "no_expected"])
+def test_parity_flag_variants(libs, flags):
+    """CLX_FLAG_NO_GRAPH (plain launches), CLX_FLAG_PROFILE (phase events, also as graph nodes), CLX_FLAG_NO_EXPECTED."""
+    gpu, orc = _pair(libs, flags)
+    with gpu, orc:
+        d = synth.generate(CASES["deep"])
+        if flags & 2:
+            # expected_ll is not computed: compare everything else
+            gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+            orc.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+            for _ in range(20):
+                gs, os_ = gpu.compute_new_excluded(), orc.compute_new_excluded()
+                gc, oc = gpu.cell_vectors(), orc.cell_vectors()
+                assert_equal(gc["excluded"], oc["excluded"], "excluded")
+                assert_equal(gc["n_loci"], oc["n_loci"], "n_loci")
+                np.testing.assert_allclose(gc["ll"], oc["ll"], rtol=1e-9, atol=1e-12)
+                assert not gc["expected_ll"].any()
+                if not os_.any_change:
+                    break
+        else:
+            run_parity(gpu, orc, d)
+            if flags & 1:
+                ph = gpu.phase_ms()
+                assert ph["score"][1] >= 1 and ph["score"][0] > 0.0, ph
+
+
 def test_parity_min_filters_and_iqr(libs):
     gpu, orc = _pair(libs)
     with gpu, orc:
