@@ -218,8 +218,11 @@ def main():
     n_loci_used, nnz_used = ctx.load_cell_data(*host, data.n_loci, data.n_cells)
     nnz_total = sum_over_ranks(float(nnz_used))
 
+    no_flush = os.environ.get("CLX_BENCH_NO_FLUSH") == "1"  # diagnostics only: a reported number always flushes
+
     def step():
-        ctx.flush_l2()
+        if not no_flush:
+            ctx.flush_l2()
         st = ctx.compute_new_excluded(5.0)
         if not st.any_change:
             ctx.reset()

@@ -16,7 +16,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcellector_cuda.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
-CU_SOURCES = ["abi.cu", "load.cu", "em.cu", "comm.cu"]
+CU_SOURCES = ["abi.cu", "load.cu", "em.cu", "comm.cu", "tiled.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
     "-fmad=false",                      # Rust never contracts a*b+c; parity needs the same (numerics.cuh)
@@ -42,7 +42,7 @@ def _compile(cu):
     src = os.path.join(CSRC, cu)
     obj = os.path.join(OBJ, cu.replace(".cu", ".o"))
     if _newer([src] + _headers(), obj):
-        cmd = [NVCC, *NVCC_FLAGS, "-c", src, "-o", obj]
+        cmd = [NVCC, *NVCC_FLAGS, *os.environ.get("CLX_EXTRA_NVCC", "").split(), "-c", src, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log = os.path.join(OBJ, cu + ".log")
         with open(log, "w") as f:

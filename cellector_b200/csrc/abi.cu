@@ -171,7 +171,8 @@ void clx_destroy(clx_ctx* c) {
     (void)dummy;
 #define R(x) c->x.release()
     R(locus_ids); R(csr); R(row_ptr); R(csc); R(col_ptr); R(locus_tot); R(h_cell); R(h_locus); R(h_ref); R(h_alt);
-    R(h_row_ptr); R(hc_perm); R(hc_col_ptr); R(hv_ll); R(hv_e); R(giant_idx); R(coo_locus); R(coo_cell); R(coo_ref); R(coo_alt);
+    R(h_row_ptr); R(hc_perm); R(hc_col_ptr); R(hv_ll); R(hv_e); R(giant_idx); R(tl_stream); R(tl_pk_q); R(tl_pk_base); R(tl_items); R(tl_cb_item); R(tl_part); R(tab13);
+    R(n_used); R(row_len); R(coo_locus); R(coo_cell); R(coo_ref); R(coo_alt);
     R(lnfact); R(excl_bits); R(d_params); R(loci_used); R(min_cnt); R(tab); R(ll); R(ell); R(norm); R(nloci);
     R(norm_all); R(sel_keys); R(sel_hist); R(sel_state); R(loc_ll); R(loc_int); R(post); R(post_u8); R(d_stats);
     R(flush_buf);

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <string>
 #include <vector>
@@ -18,7 +19,11 @@ struct DevBuf {
         release();
         n = count;
         if (count == 0) return cudaSuccess;
-        return cudaMalloc((void**)&p, count * sizeof(T));
+        const cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+        // CLX_POISON=1 fills every fresh allocation with 0xAB: a read of memory nobody wrote shows up at once
+        static const bool poison = getenv("CLX_POISON") != nullptr;
+        if (e == cudaSuccess && poison) cudaMemset(p, 0xAB, count * sizeof(T));
+        return e;
     }
     void release() {
         if (p) cudaFree(p);
@@ -92,6 +97,19 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> giant_idx;                      // [n_giant] heavy entries with total > HEAVY_GIANT_TOTAL
     uint32_t n_giant = 0;
     clx::DevBuf<double> hv_ll, hv_e;                      // [3 * n_heavy] values of the current scoring pass
+    // --- tiled scoring layout (tiled.cu): light entries (total 1..3) packed to 4 bytes, ordered by
+    //     runs (one cell x one locus tile) inside packets; one work item = one cell block x a range of locus tiles
+    bool tiled_ready = false;
+    uint32_t tl_NB = 0, tl_Pc = 0, tl_nT = 0, tl_n_items = 0, tl_n_units = 0;
+    uint64_t tl_n_light = 0, tl_stream_len = 0;       // light entries; stream length incl. slice padding
+    clx::DevBuf<uint32_t> tl_stream;                  // [tl_stream_len] packets of runs (tiled.cu), 4-byte words
+    clx::DevBuf<uint32_t> tl_pk_q;                    // [n_packets + 1] packet starts, in quads (16 B)
+    clx::DevBuf<uint32_t> tl_pk_base;                 // [n_units + 1] first packet of every (cell block, tile) unit
+    clx::DevBuf<uint32_t> tl_items;                   // [n_items][4] cell block, first tile, end tile, -
+    clx::DevBuf<uint32_t> tl_cb_item;                 // [Pc + 1] first item of every cell block
+    clx::DevBuf<double> tl_part;                      // [n_items][NB][2] per-item partial (log_pmf, expected) sums
+    clx::DevBuf<double> tab13;                        // [3][nT * TILE_L][13] compact memo records for the tiled kernel
+    clx::DevBuf<uint32_t> n_used, row_len;            // [n_cells] loci_used_per_cell (main.rs:575) / stored row length
     // retained COO for clx_final_locus_counts
     clx::DevBuf<uint32_t> coo_locus, coo_cell, coo_ref, coo_alt;
     clx::DevBuf<double> lnfact;  // [171]
@@ -151,6 +169,18 @@ int fail(clx_ctx* c, int code, const std::string& msg);
         if (rc__ != CLX_OK) return rc__; \
     } while (0)
 
+// CLX_SYNC_DEBUG=1 (with CLX_FLAG_NO_GRAPH): synchronise after a launch and name the kernel that faulted
+#define CLX_DEBUG_SYNC(ctx, what)                                                                        \
+    do {                                                                                                 \
+        static const bool dbg__ = getenv("CLX_SYNC_DEBUG") != nullptr;                                   \
+        if (dbg__ && !(ctx)->capturing) {                                                                \
+            cudaError_t e__ = cudaStreamSynchronize((ctx)->stream);                                      \
+            if (e__ == cudaSuccess) e__ = cudaGetLastError();                                            \
+            if (e__ != cudaSuccess)                                                                      \
+                return clx::fail(ctx, CLX_ERR_CUDA, std::string("after ") + what + ": " + cudaGetErrorString(e__)); \
+        }                                                                                                \
+    } while (0)
+
 // profiling scopes (no-ops unless CLX_FLAG_PROFILE)
 void phase_begin(clx_ctx* c, int phase);
 void phase_end(clx_ctx* c, int phase);
@@ -169,6 +199,9 @@ int comm_init(clx_ctx* c, int rank, int world, const void* id128);
 // load.cu
 int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, const uint32_t* locus,
              const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt);
+// tiled.cu
+int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry);  // CSR-order cell id of every entry
+int score_tiled(clx_ctx* c, int table, bool with_e, bool em_outputs);
 // em.cu
 int em_alloc(clx_ctx* c);
 int em_reset(clx_ctx* c);

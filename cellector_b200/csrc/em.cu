@@ -32,6 +32,8 @@ Lbc10 make_lbc(const clx_ctx* c) {
     return l;
 }
 
+bool use_tiled(const clx_ctx* c) { return c->tiled_ready && !(c->flags & CLX_FLAG_KERNEL_V0); }
+
 int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
@@ -62,7 +64,7 @@ void launch_columns(clx_ctx* c, int G) {
 #define CLX_COLS(GG)                                                                                                   \
     k_columns<GG, FUSE><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                          \
         c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_perm.p,            \
-        c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hv_ll.p, c->loc_ll.p, c->loc_int.p, c->d_stats.p)
+        c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hv_ll.p, c->loc_ll.p, c->loc_int.p, c->n_used.p, c->d_stats.p)
     switch (G) {
         case 4: CLX_COLS(4); break;
         case 8: CLX_COLS(8); break;
@@ -170,6 +172,9 @@ int em_alloc(clx_ctx* c) {
     c->col_G = env_int("CLX_COL_G", pick_group(L ? (double)c->nnz / L : 0.0));
     // roofline accounting of the gather scoring kernel: packed entries + row pointers + outputs + table
     c->score_bytes = 8ull * c->nnz + 8ull * (N + 1) + 20ull * N + 128ull * L;
+    // tiled kernel: the packet stream (2-byte entries + 4-byte run headers) + one read of the 104-byte compact
+    // records + 16 B of sums per cell
+    if (use_tiled(c)) c->score_bytes = 4ull * c->tl_stream_len + 104ull * L + 16ull * N;
     return em_reset(c);
 }
 
@@ -179,6 +184,7 @@ int em_reset(clx_ctx* c) {
     CLX_CUDA(c, cudaMemsetAsync(c->loci_used.p, 1, c->loci_used.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->loc_int.p, 0, c->loc_int.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->loc_ll.p, 0, c->loc_ll.bytes(), s));
+    if (c->n_cells) CLX_CUDA(c, cudaMemcpyAsync(c->n_used.p, c->row_len.p, (size_t)c->n_cells * 4, cudaMemcpyDeviceToDevice, s));
     CLX_CUDA(c, cudaStreamSynchronize(s));
     c->iteration = 0;
     c->have_iteration = false;
@@ -210,12 +216,13 @@ int enqueue_iteration(clx_ctx* c) {
     if (L) {
         k_tables<0><<<(L + TAB_LPB - 1) / TAB_LPB, TPB, 0, s>>>(
             c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), 0.0, 0.0, with_e,
-            c->loci_used.p, c->tab.p, c->d_stats.p);
+            c->loci_used.p, c->tab.p, c->tiled_ready ? c->tab13.p : nullptr, c->tl_nT * TILE_L, c->d_stats.p);
         c->launches++;
     } else {
         CLX_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, sizeof(DeviceStats), s));
     }
     phase_end(c, CLX_PHASE_TABLES);
+    CLX_DEBUG_SYNC(c, "k_tables");
 
     // 2. heavy entries, then the per-cell scoring pass (main.rs:312)
     phase_begin(c, CLX_PHASE_HEAVY);
@@ -230,10 +237,16 @@ int enqueue_iteration(clx_ctx* c) {
         }
     }
     phase_end(c, CLX_PHASE_HEAVY);
+    CLX_DEBUG_SYNC(c, "k_heavy");
     phase_begin(c, CLX_PHASE_SCORE);
-    if (with_e) launch_score_rows<1, true>(c, c->score_G);
-    else launch_score_rows<1, false>(c, c->score_G);
+    if (use_tiled(c)) {
+        CLX_TRY(score_tiled(c, 0, with_e != 0, true));
+    } else {
+        if (with_e) launch_score_rows<1, true>(c, c->score_G);
+        else launch_score_rows<1, false>(c, c->score_G);
+    }
     phase_end(c, CLX_PHASE_SCORE);
+    CLX_DEBUG_SYNC(c, "score");
 
     // 3. threshold from exact order statistics of the normalized log likelihoods (main.rs:313-329)
     //    + new excluded set and change counts (main.rs:330-335)
@@ -249,6 +262,7 @@ int enqueue_iteration(clx_ctx* c) {
     phase_begin(c, CLX_PHASE_SELECT);
     CLX_TRY(run_select_exclude(c, sel_vals, n_vals, c->n_cells_global));
     phase_end(c, CLX_PHASE_SELECT);
+    CLX_DEBUG_SYNC(c, "select");
     if (c->world > 1) {
         phase_begin(c, CLX_PHASE_COMM);
         CLX_TRY(comm_allreduce_u64(c, &c->d_stats.p->n_new, 3));
@@ -261,6 +275,7 @@ int enqueue_iteration(clx_ctx* c) {
     if (c->world > 1) launch_columns<false>(c, c->col_G);
     else launch_columns<true>(c, c->col_G);
     phase_end(c, CLX_PHASE_COLUMN);
+    CLX_DEBUG_SYNC(c, "k_columns");
     if (c->world > 1) {
         phase_begin(c, CLX_PHASE_COMM);
         CLX_TRY(comm_allreduce_f64(c, c->loc_ll.p, 2 * (size_t)L));
@@ -268,7 +283,8 @@ int enqueue_iteration(clx_ctx* c) {
         phase_end(c, CLX_PHASE_COMM);
         phase_begin(c, CLX_PHASE_COLUMN);
         if (L) {
-            k_locus_filter<<<(L + TPB - 1) / TPB, TPB, 0, s>>>(c->loc_ll.p, c->loc_int.p, L, c->loci_used.p, c->d_stats.p);
+            k_locus_filter<<<(L + TPB - 1) / TPB, TPB, 0, s>>>(c->loc_ll.p, c->loc_int.p, L, c->loci_used.p, c->csc.p, c->col_ptr.p,
+                                                               c->n_used.p, c->d_stats.p);
             c->launches++;
         }
         phase_end(c, CLX_PHASE_COLUMN);
@@ -365,7 +381,7 @@ int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used
     if (L) {
         k_tables<1><<<3 * ((L + TAB_LPB - 1) / TAB_LPB), TPB, 0, s>>>(
             c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), mf_unclamped, mf, 0,
-            nullptr, c->tab.p, nullptr);
+            nullptr, c->tab.p, c->tiled_ready ? c->tab13.p : nullptr, c->tl_nT * TILE_L, nullptr);
         c->launches++;
     }
     phase_end(c, CLX_PHASE_TABLES);
@@ -378,7 +394,11 @@ int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used
     phase_end(c, CLX_PHASE_HEAVY);
     // get_loci_used_for_posterior_calc pushes true on both branches (main.rs:301-303): every locus is scored
     phase_begin(c, CLX_PHASE_SCORE);
-    launch_score_rows<3, false>(c, c->score_G);
+    if (use_tiled(c)) {
+        for (int t = 0; t < 3; ++t) CLX_TRY(score_tiled(c, t, false, false));
+    } else {
+        launch_score_rows<3, false>(c, c->score_G);
+    }
     phase_end(c, CLX_PHASE_SCORE);
     if (N) {
         k_posterior<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->ll.p, N, c->row_ptr.p, c->excl_bits.p, pp, c->post.p, c->post_u8.p);

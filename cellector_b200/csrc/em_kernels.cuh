@@ -39,6 +39,7 @@ __global__ void __launch_bounds__(256) k_tables(const unsigned long long* __rest
                                                 const unsigned long long* __restrict__ raw_min_alt, uint32_t n_loci,
                                                 Lbc10 lbc, double mf, double mf_clamped, int with_expected,
                                                 const uint8_t* __restrict__ used, double* __restrict__ tab,
+                                                double* __restrict__ tab13, uint32_t n_loci_pad,
                                                 DeviceStats* __restrict__ st_clear) {
     static_assert(K_LIGHT == 3, "task layout below is for K_LIGHT == 3");
     constexpr int NTASK = MODE == 0 ? 12 : 18;
@@ -147,6 +148,20 @@ __global__ void __launch_bounds__(256) k_tables(const unsigned long long* __rest
     const uint32_t n_here = n_loci - l0 < (uint32_t)TAB_LPB ? n_loci - l0 : (uint32_t)TAB_LPB;
     double* dst = tab + ((size_t)t * n_loci + l0) * TAB_STRIDE;
     for (uint32_t i = tid; i < n_here * TAB_STRIDE; i += blockDim.x) dst[i] = (&s_rec[0][0])[i];
+    // compact 13-double records for the tiled scoring kernel (numerics.cuh): zeros for a switched-off locus
+    if (tab13 != nullptr) {
+        double* d13 = tab13 + ((size_t)t * n_loci_pad + l0) * TAB13;
+        for (uint32_t i = tid; i < n_here * TAB13; i += blockDim.x) {
+            const uint32_t ll = i / TAB13, p = i % TAB13;
+            double v = 0.0;
+            if (s_on[ll] && p < 12) {
+                // p < 9: T slot p(a, n) = n(n+1)/2 - 1 + a;  9..11: E(n = p - 8)
+                const int n = p < 2 ? 1 : (p < 5 ? 2 : (p < 9 ? 3 : (int)p - 8));
+                v = p < 9 ? s_rec[ll][tab_idx_T((int)p - (n * (n + 1)) / 2 + 1, n)] : s_rec[ll][tab_idx_E(n)];
+            }
+            d13[i] = v;
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -493,7 +508,7 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
                                                  const uint32_t* __restrict__ h_cell, const uint32_t* __restrict__ h_ref,
                                                  const uint32_t* __restrict__ h_alt, const double* __restrict__ hv_ll,
                                                  double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int,
-                                                 DeviceStats* __restrict__ st) {
+                                                 uint32_t* __restrict__ n_used, DeviceStats* __restrict__ st) {
     constexpr int U = SCORE_UNROLL;
     const uint32_t gid = (blockIdx.x * blockDim.x + threadIdx.x) / G;
     const uint32_t g = threadIdx.x % G;
@@ -510,11 +525,15 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
             const uint64_t i = i0 + 2ull * G * u;
             q[u] = i < end ? __ldg(reinterpret_cast<const uint4*>(csc + i)) : make_uint4(0u, 0u, 0u, 0u);
         }
+        // excluded-bitmap words of the two cells; a slot outside [begin, end) may hold anything (the neighbouring
+        // column, or bytes past the end of the array): never turn it into an address
         uint32_t w[U][2];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            w[u][0] = __ldg(excl_bits + (q[u].x >> 5));
-            w[u][1] = __ldg(excl_bits + (q[u].z >> 5));
+            const uint64_t idx = i0 + 2ull * G * u;
+            const bool ok0 = idx >= begin && idx < end, ok1 = idx + 1 >= begin && idx + 1 < end;
+            w[u][0] = ok0 ? __ldg(excl_bits + (q[u].x >> 5)) : 0u;
+            w[u][1] = ok1 ? __ldg(excl_bits + (q[u].z >> 5)) : 0u;
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -580,6 +599,10 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
         }
     }
     if (FUSE_FILTER) {
+        // a locus switched off now stops counting toward loci_used_per_cell (main.rs:575) of the cells it covers
+        const bool grp_f = __shfl_sync(0xffffffffu, filtered ? 1 : 0, (int)((threadIdx.x & 31u) & ~(uint32_t)(G - 1))) != 0;
+        if (grp_f)
+            for (uint64_t i = begin + g; i < end; i += G) atomicSub(&n_used[csc[i].cell], 1u);
         const uint32_t f = __popc(__ballot_sync(0xffffffffu, filtered)), u = __popc(__ballot_sync(0xffffffffu, in_use));
         if ((threadIdx.x & 31) == 0) {
             if (f) atomicAdd(&st->n_loci_filtered, (unsigned long long)f);
@@ -591,7 +614,9 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
 // The -80 rule (main.rs:431-451): per-cell minority log likelihood of the locus below -80 switches it off.
 __global__ void __launch_bounds__(256) k_locus_filter(const double* __restrict__ loc_ll,
                                                       const unsigned long long* __restrict__ loc_int, uint32_t n_loci,
-                                                      uint8_t* __restrict__ used, DeviceStats* __restrict__ st) {
+                                                      uint8_t* __restrict__ used, const ColEntry* __restrict__ csc,
+                                                      const uint64_t* __restrict__ col_ptr, uint32_t* __restrict__ n_used,
+                                                      DeviceStats* __restrict__ st) {
     const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
     bool filtered = false, in_use = false;
     if (l < n_loci) {
@@ -601,6 +626,8 @@ __global__ void __launch_bounds__(256) k_locus_filter(const double* __restrict__
         if (per_cell < -80.0) {
             filtered = was;
             used[l] = 0;
+            if (was)  // rare: this rank's cells of the locus stop counting it (loci_used_per_cell, main.rs:575)
+                for (uint64_t i = col_ptr[l]; i < col_ptr[l + 1]; ++i) atomicSub(&n_used[csc[i].cell], 1u);
         } else {
             in_use = was;
         }

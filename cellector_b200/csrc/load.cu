@@ -284,7 +284,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     // ---- pack CSR, locus totals, CSC keys
     DevBuf<uint8_t> heavy;
     DevBuf<uint32_t> col_cnt, vals2, csc_src;
-    CLX_CUDA(c, c->csr.alloc(nnz));
+    CLX_CUDA(c, c->csr.alloc((size_t)nnz + 2));  // +2: the 128-bit loads of the gather kernels may touch one entry past the end
     CLX_CUDA(c, heavy.alloc(nnz));
     CLX_CUDA(c, col_cnt.alloc((size_t)n_loci + 1));
     CLX_CUDA(c, vals2.alloc(nnz));
@@ -293,12 +293,14 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     CLX_CUDA(c, cudaMemsetAsync(col_cnt.p, 0, col_cnt.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->locus_tot.p, 0, c->locus_tot.bytes(), s));
     CLX_CUDA(c, c->col_ptr.alloc((size_t)n_loci + 1));
-    CLX_CUDA(c, c->csc.alloc(nnz));
+    CLX_CUDA(c, c->csc.alloc((size_t)nnz + 2));
     if (nnz) {
         // keys / keys_sorted are reused as the locus keys of the second sort
         k_pack_csr<<<grid_for(nnz), TPB, 0, s>>>(csr_src.p, d_locus.p, d_ref.p, d_alt.p, used_idx.p, nnz, c->csr.p, keys.p,
                                                  vals2.p, heavy.p, col_cnt.p, c->locus_tot.p);
         c->launches++;
+        // tiled scoring layout: keys_sorted still holds the cell of every CSR entry here
+        CLX_TRY(build_tiled(c, keys_sorted.p));
         const int eb = bits_for(n_loci);
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys_sorted.p, vals2.p, csc_src.p, (int)nnz, 0, eb, s));
         CLX_CUDA(c, tmp.alloc(tmp_bytes));
@@ -307,6 +309,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         k_pack_csc<<<grid_for(nnz), TPB, 0, s>>>(csc_src.p, csr_src.p, d_cell.p, c->csr.p, nnz, c->csc.p);
         c->launches++;
     }
+    if (!nnz) CLX_TRY(build_tiled(c, nullptr));
     {
         cub::TransformInputIterator<uint64_t, ToU64, const uint32_t*> it(col_cnt.p, ToU64());
         CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, it, c->col_ptr.p, (int)(n_loci + 1), s));

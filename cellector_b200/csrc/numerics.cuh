@@ -35,6 +35,15 @@ CLX_HD int tab_idx_E(int n) { return n == 1 ? 2 : (n == 2 ? 7 : 12); }
 // index of ln C(n, a) in the 10-entry constant block for n <= 3
 CLX_HD int lbc_idx(int a, int n) { return (n * (n + 1)) / 2 + a; }
 
+// Compact record of the tiled scoring kernel: 13 doubles (odd stride: spreads shared-memory banks)
+//   [0..1] T(.|1)  [2..4] T(.|2)  [5..8] T(.|3)  [9..11] E(1..3)  [12] 0.0
+// slot p(a, n) = n(n+1)/2 - 1 + a; every slot of a switched-off locus is 0.0 (loci_used_per_cell is kept separately).
+constexpr int TAB13 = 13;
+constexpr int TILE_L = 512;   // loci per table tile (53,248 bytes in shared memory)
+constexpr int TL_WARPS = 32;  // warps per CTA of the tiled kernel; a cell belongs to warp (cell_local % TL_WARPS)
+CLX_HD int tab13_T(int a, int n) { return (n * (n + 1)) / 2 - 1 + a; }
+CLX_HD int tab13_E(int n) { return 8 + n; }
+
 struct Lanczos {
     // statrs GAMMA_DK / GAMMA_R / constants
     static constexpr double R = 10.900511;
