@@ -12,6 +12,11 @@ namespace clx {
 
 static thread_local std::string g_create_error;
 
+cudaStream_t& alloc_stream() {
+    static thread_local cudaStream_t s = nullptr;
+    return s;
+}
+
 int fail(clx_ctx* c, int code, const std::string& msg) {
     if (c) c->err = msg;
     else g_create_error = msg;
@@ -131,6 +136,13 @@ int clx_create(clx_ctx** out, int device, unsigned flags) {
     }
     c->sm_count = prop.multiProcessorCount;
     CLX_CREATE_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    alloc_stream() = c->stream;
+    {   // keep freed blocks in the device pool: scratch buffers of the next load come back without a driver call
+        cudaMemPool_t pool = nullptr;
+        CLX_CREATE_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        unsigned long long keep = ~0ull;
+        CLX_CREATE_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     CLX_CREATE_CUDA(cudaEventCreate(&c->ev_iter_a));
     CLX_CREATE_CUDA(cudaEventCreate(&c->ev_iter_b));
     CLX_CREATE_CUDA(c->d_stats.alloc(1));
@@ -149,7 +161,8 @@ int clx_create(clx_ctx** out, int device, unsigned flags) {
     for (int n = 0; n <= 3; ++n)
         for (int a = 0; a <= n; ++a) c->lbc10[lbc_idx(a, n)] = lnfact[n] - lnfact[a] - lnfact[n - a];
     CLX_CREATE_CUDA(c->lnfact.alloc(171));
-    CLX_CREATE_CUDA(cudaMemcpy(c->lnfact.p, lnfact, sizeof(lnfact), cudaMemcpyHostToDevice));
+    CLX_CREATE_CUDA(cudaMemcpyAsync(c->lnfact.p, lnfact, sizeof(lnfact), cudaMemcpyHostToDevice, c->stream));
+    CLX_CREATE_CUDA(cudaStreamSynchronize(c->stream));
 #undef CLX_CREATE_CUDA
     *out = c;
     return CLX_OK;
@@ -167,18 +180,13 @@ void clx_destroy(clx_ctx* c) {
     if (c->ev_iter_a) cudaEventDestroy(c->ev_iter_a);
     if (c->ev_iter_b) cudaEventDestroy(c->ev_iter_b);
     if (c->h_stats) cudaFreeHost(c->h_stats);
-    clx::DevBuf<uint8_t>* dummy = nullptr;
-    (void)dummy;
-#define R(x) c->x.release()
-    R(locus_ids); R(csr); R(row_ptr); R(csc); R(col_ptr); R(locus_tot); R(h_cell); R(h_locus); R(h_ref); R(h_alt);
-    R(h_row_ptr); R(hc_perm); R(hc_col_ptr); R(hv_ll); R(hv_e); R(giant_idx); R(tl_stream); R(tl_pk_q); R(tl_pk_base); R(tl_items); R(tl_cb_item); R(tl_part); R(tab13);
-    R(n_used); R(row_len); R(coo_locus); R(coo_cell); R(coo_ref); R(coo_alt);
-    R(lnfact); R(excl_bits); R(d_params); R(loci_used); R(min_cnt); R(tab); R(ll); R(ell); R(norm); R(nloci);
-    R(norm_all); R(sel_keys); R(sel_hist); R(sel_state); R(loc_ll); R(loc_int); R(post); R(post_u8); R(d_stats);
-    R(flush_buf);
-#undef R
-    if (c->stream) cudaStreamDestroy(c->stream);
-    delete c;
+    cudaStream_t s = c->stream;
+    alloc_stream() = s;
+    delete c;  // every DevBuf member frees itself on the stream
+    if (s) {
+        cudaStreamSynchronize(s);
+        cudaStreamDestroy(s);
+    }
 }
 
 const char* clx_last_error(const clx_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
@@ -187,6 +195,7 @@ int clx_nccl_unique_id(void* out128) { return out128 ? comm_unique_id(out128) : 
 
 int clx_comm_init(clx_ctx* c, int rank, int world, const void* id) {
     if (!c) return CLX_ERR_ARG;
+    alloc_stream() = c->stream;
     return comm_init(c, rank, world, id);
 }
 
@@ -195,6 +204,7 @@ int clx_load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, 
                  uint32_t* n_loci_used, uint64_t* nnz_used) {
     if (!c) return CLX_ERR_ARG;
     cudaSetDevice(c->device);
+    alloc_stream() = c->stream;
     CLX_TRY(load_coo(c, nnz0, n_loci0, n_cells, locus, cell, ref, alt, min_ref, min_alt));
     if (n_loci_used) *n_loci_used = c->n_loci;
     if (nnz_used) *nnz_used = c->nnz;
@@ -237,6 +247,7 @@ int clx_get_cell_vectors(clx_ctx* c, double* ll, double* expected_ll, uint32_t* 
 
 int clx_get_locus_vectors(clx_ctx* c, const clx_locus_arrays* o) {
     if (!c || !o) return CLX_ERR_ARG;
+    alloc_stream() = c->stream;
     if (!c->loaded || !c->have_iteration) return fail(c, CLX_ERR_STATE, "no iteration run yet");
     const size_t L = c->n_loci;
     CLX_TRY(d2h(c, o->ll_minority, c->loc_ll.p, L));
@@ -279,6 +290,7 @@ int clx_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_use
 int clx_final_locus_counts(clx_ctx* c, uint64_t* minority_ref_alt, uint64_t* majority_ref_alt) {
     if (!c || !minority_ref_alt || !majority_ref_alt) return CLX_ERR_ARG;
     if (!c->loaded) return fail(c, CLX_ERR_STATE, "not loaded");
+    alloc_stream() = c->stream;
     const size_t n = 2 * (size_t)c->n_loci0;
     clx::DevBuf<unsigned long long> mn, mj;
     CLX_CUDA(c, mn.alloc(n + 1));
@@ -322,6 +334,7 @@ int clx_launch_count(clx_ctx* c, uint64_t* launches) {
 int clx_flush_l2(clx_ctx* c) {
     if (!c) return CLX_ERR_ARG;
     const size_t bytes = 512ull << 20;  // 4x the 126 MB L2
+    alloc_stream() = c->stream;
     if (!c->flush_buf.p) CLX_CUDA(c, c->flush_buf.alloc(bytes));
     static uint32_t v = 0;
     k_flush<<<c->sm_count * 8, 256, 0, c->stream>>>((uint4*)c->flush_buf.p, bytes / 16, ++v);

@@ -11,25 +11,40 @@
 
 namespace clx {
 
+// Stream-ordered allocations (cudaMallocAsync on the context stream): the device pool keeps freed blocks
+// (release threshold = max, set in clx_create), so the dozens of scratch buffers of a load cost no driver
+// round trip after the first job.  The ABI entry points set the stream of the calling thread.
+cudaStream_t& alloc_stream();
+
 template <typename T>
 struct DevBuf {
     T* p = nullptr;
     size_t n = 0;
+    cudaStream_t st = nullptr;
     cudaError_t alloc(size_t count) {
         release();
         n = count;
         if (count == 0) return cudaSuccess;
-        const cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+        st = alloc_stream();
+        const cudaError_t e = cudaMallocAsync((void**)&p, count * sizeof(T), st);
         // CLX_POISON=1 fills every fresh allocation with 0xAB: a read of memory nobody wrote shows up at once
         static const bool poison = getenv("CLX_POISON") != nullptr;
-        if (e == cudaSuccess && poison) cudaMemset(p, 0xAB, count * sizeof(T));
+        if (e == cudaSuccess && poison) cudaMemsetAsync(p, 0xAB, count * sizeof(T), st);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            n = 0;
+        }
         return e;
     }
     void release() {
-        if (p) cudaFree(p);
+        if (p) cudaFreeAsync(p, st);
         p = nullptr;
         n = 0;
     }
+    ~DevBuf() { release(); }
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
     size_t bytes() const { return n * sizeof(T); }
 };
 
