@@ -253,11 +253,25 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     sc_ms, sc_n = phases["score"]
-    score_bytes = ctx.score_bytes()
-    achieved = score_bytes / (sc_ms / max(sc_n, 1) * 1e-3) / 1e9 if sc_ms > 0 else 0.0
+    # ALGORITHMIC bytes of one scoring pass, SURVEY.md §8(d): 8 B packed (locus, ref, alt) entry per scored nonzero
+    # + int64 row pointers + 20 B of per-cell outputs + one read of a 12-double per-locus table.  The tiled kernel
+    # actually streams a compacted re-encoding of the same entries (2-byte entries in padded groups): those bytes
+    # are reported beside it as `moved`.
+    n_local, L = data.n_cells, n_loci_used
+    algo_bytes = 8 * nnz_used + 8 * (n_local + 1) + 20 * n_local + 96 * L
+    moved_bytes = ctx.score_bytes()
+    k_s = sc_ms / max(sc_n, 1) * 1e-3
+    achieved = algo_bytes / k_s / 1e9 if sc_ms > 0 else 0.0
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "score_kernel_traffic.json"))).get("dram_bytes_per_launch")
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "per-cell scoring", "algorithmic_bytes_per_launch": score_bytes,
-                "kernel_us": 1e3 * sc_ms / max(sc_n, 1),
+                "traffic": traffic, "kernel": "per-cell scoring (k_score_tiled + k_score_finish)",
+                "algorithmic_bytes_per_launch": int(algo_bytes), "moved_bytes_per_launch": int(moved_bytes),
+                "achieved_moved": moved_bytes / k_s / 1e9 if sc_ms > 0 else 0.0,
+                "kernel_us": 1e6 * k_s,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)"}
 
     # end to end through the C ABI with HOST buffers: load (H2D of the COO + GPU CSR/CSC build), EM to convergence,

@@ -28,6 +28,8 @@ struct Api {
     int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
     std::string err;
     bool ok = false;
 };
@@ -50,6 +52,8 @@ Api& api() {
     CLX_SYM(AllReduce, "ncclAllReduce")
     CLX_SYM(AllGather, "ncclAllGather")
     CLX_SYM(GetErrorString, "ncclGetErrorString")
+    CLX_SYM(GroupStart, "ncclGroupStart")
+    CLX_SYM(GroupEnd, "ncclGroupEnd")
 #undef CLX_SYM
     a.ok = true;
     return a;
@@ -70,6 +74,18 @@ int allreduce(clx_ctx* c, void* buf, size_t n, int dtype) {
 }
 
 }  // namespace
+
+// Collectives issued between group_begin and group_end are fused by NCCL into one launch.
+int comm_group_begin(clx_ctx* c) {
+    if (c->world <= 1) return CLX_OK;
+    const int rc = api().GroupStart();
+    return rc == ncclSuccess ? CLX_OK : nccl_fail(c, "ncclGroupStart", rc);
+}
+int comm_group_end(clx_ctx* c) {
+    if (c->world <= 1) return CLX_OK;
+    const int rc = api().GroupEnd();
+    return rc == ncclSuccess ? CLX_OK : nccl_fail(c, "ncclGroupEnd", rc);
+}
 
 int comm_unique_id(void* out128) {
     Api& a = api();

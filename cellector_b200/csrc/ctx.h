@@ -205,6 +205,8 @@ void phase_resolve(clx_ctx* c);  // after a stream sync
 int comm_allreduce_u32(clx_ctx* c, unsigned int* buf, size_t n);
 int comm_allreduce_u64(clx_ctx* c, unsigned long long* buf, size_t n);
 int comm_allreduce_f64(clx_ctx* c, double* buf, size_t n);
+int comm_group_begin(clx_ctx* c);
+int comm_group_end(clx_ctx* c);
 int comm_allgather_f64(clx_ctx* c, const double* send, double* recv, size_t n_per_rank);
 int comm_allgather_u64_host(clx_ctx* c, uint64_t v, std::vector<uint64_t>* out);
 void comm_destroy(clx_ctx* c);

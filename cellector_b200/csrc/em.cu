@@ -112,14 +112,29 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
     const SelectPlan plan = make_plan(n_real);
     cudaStream_t s = c->stream;
     const uint32_t N = c->n_cells;
-    if (n_vals <= SELECT_SMALL_MAX) {
+    static const int mode = env_int("CLX_SELECT_MODE", 0);  // tests: 1 forces the cooperative kernel, 2 the multi-launch path
+    if (mode == 0 && n_vals <= SELECT_SMALL_MAX && vals == c->norm.p) {  // one GPU, small: one CTA, exclusion fused
         k_select_small<<<1, SELECT_SMALL_THREADS, 0, s>>>(vals, (uint32_t)n_vals, plan, c->d_params.p,
                                                                          c->d_stats.p, c->norm.p, N, c->excl_bits.p);
         c->launches++;
-        if (vals != c->norm.p && N) {  // sharded: the selected values are the gathered ones, exclude separately
-            k_exclude<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->norm.p, N, c->excl_bits.p, c->d_stats.p);
-            c->launches++;
-        }
+        return CLX_OK;
+    }
+    const uint64_t per_cta = (uint64_t)SELECT_SMALL_THREADS * SELECT_R;
+    if (mode != 2 && n_vals <= per_cta * (uint64_t)c->sm_count) {  // cooperative grid, keys in registers, one launch
+        CLX_CUDA(c, cudaMemsetAsync(c->sel_hist.p, 0, c->sel_hist.bytes(), s));
+        const unsigned grid = (unsigned)std::max<uint64_t>(1, (n_vals + per_cta - 1) / per_cta);
+        const double* norm_local = c->norm.p;
+        const IterParams* prm = c->d_params.p;
+        DeviceStats* st = c->d_stats.p;
+        unsigned int* scratch = c->sel_hist.p;
+        unsigned long long* glist = (unsigned long long*)c->sel_keys.p;
+        uint32_t* bits = c->excl_bits.p;
+        uint32_t n_local = N;
+        SelectPlan pl = plan;
+        void* args[] = {(void*)&vals, (void*)&n_vals, (void*)&pl, (void*)&prm, (void*)&st, (void*)&scratch,
+                        (void*)&glist, (void*)&norm_local, (void*)&n_local, (void*)&bits};
+        CLX_CUDA(c, cudaLaunchCooperativeKernel((const void*)k_select_coop, dim3(grid), dim3(SELECT_SMALL_THREADS), args, 0, s));
+        c->launches++;
         return CLX_OK;
     }
     unsigned long long* keys = (unsigned long long*)c->sel_keys.p;
@@ -159,8 +174,10 @@ int em_alloc(clx_ctx* c) {
     CLX_CUDA(c, c->post_u8.alloc(3 * N + 1));
     const size_t n_sel = c->world > 1 ? (size_t)c->world * c->max_local_cells : N;
     if (c->world > 1) CLX_CUDA(c, c->norm_all.alloc(n_sel + 1));
-    if (n_sel > SELECT_SMALL_MAX) CLX_CUDA(c, c->sel_keys.alloc(n_sel));
-    CLX_CUDA(c, c->sel_hist.alloc(8 * SELECT_TARGETS * 256 + 8));
+    const size_t n_cta_keys = (size_t)SELECT_SMALL_THREADS * SELECT_R * (size_t)c->sm_count;
+    (void)n_cta_keys;
+    CLX_CUDA(c, c->sel_keys.alloc(n_sel + 256));  // key array of the multi-launch path / survivor list
+    CLX_CUDA(c, c->sel_hist.alloc(SELECT_COOP_SCRATCH + 8 * SELECT_TARGETS * 256 + 8));
     CLX_CUDA(c, c->sel_state.alloc(sizeof(SelectState) / 8 + 1));
     // pads of the gather buffer: +inf sorts after every real value
     {
@@ -263,12 +280,6 @@ int enqueue_iteration(clx_ctx* c) {
     CLX_TRY(run_select_exclude(c, sel_vals, n_vals, c->n_cells_global));
     phase_end(c, CLX_PHASE_SELECT);
     CLX_DEBUG_SYNC(c, "select");
-    if (c->world > 1) {
-        phase_begin(c, CLX_PHASE_COMM);
-        CLX_TRY(comm_allreduce_u64(c, &c->d_stats.p->n_new, 3));
-        phase_end(c, CLX_PHASE_COMM);
-    }
-
     // 4. per-locus contributions split by the NEW set (main.rs:343) + minority allele counts for the next
     //    alpha/beta + the -80 locus filter (main.rs:444-451; after the allreduce when cells are sharded)
     phase_begin(c, CLX_PHASE_COLUMN);
@@ -278,8 +289,12 @@ int enqueue_iteration(clx_ctx* c) {
     CLX_DEBUG_SYNC(c, "k_columns");
     if (c->world > 1) {
         phase_begin(c, CLX_PHASE_COMM);
+        // one fused NCCL launch: per-locus sums and counts + the three change counters of the exclusion step
+        CLX_TRY(comm_group_begin(c));
+        CLX_TRY(comm_allreduce_u64(c, &c->d_stats.p->n_new, 3));
         CLX_TRY(comm_allreduce_f64(c, c->loc_ll.p, 2 * (size_t)L));
         CLX_TRY(comm_allreduce_u64(c, c->loc_int.p, 8 * (size_t)L));
+        CLX_TRY(comm_group_end(c));
         phase_end(c, CLX_PHASE_COMM);
         phase_begin(c, CLX_PHASE_COLUMN);
         if (L) {

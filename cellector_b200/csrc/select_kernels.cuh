@@ -8,6 +8,7 @@
 //   * larger N             : MSB-first radix select, 8 passes of 8 bits, all six ranks in flight at once,
 //                            one launch per pass (histogram + last-block digit pick).
 #pragma once
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
 #include "ctx.h"
@@ -270,6 +271,258 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_small(const dou
             const unsigned int old = __shfl_sync(0xffffffffu, old_word, j);
             if (lane == 0 && (uint32_t)j * SELECT_SMALL_THREADS + (uint32_t)(warp << 5) < n_cells_local) {
                 bits[i >> 5] = word;
+                nn += __popc(word & ~old);
+                nr += __popc(old & ~word);
+                ne += __popc(word);
+            }
+        }
+        if (lane == 0) {
+            if (nn) atomicAdd(&st->n_new, (unsigned long long)nn);
+            if (nr) atomicAdd(&st->n_rescued, (unsigned long long)nr);
+            if (ne) atomicAdd(&st->n_excluded, (unsigned long long)ne);
+        }
+    }
+}
+
+// ---- medium N (up to SELECT_SMALL_MAX keys per CTA x one CTA per SM): the same register-resident radix select,
+// spread over a cooperative grid.  Every CTA keeps its keys in registers; per pass the CTA histograms are added
+// into a global histogram (one region per pass, zeroed by the host), the grid synchronises, and every CTA picks
+// the digits redundantly from the global histogram — one launch for the whole select, ~one grid barrier per
+// pass.  Used when cells are sharded (the gathered values of all ranks are selected on every rank, so all ranks
+// get the identical threshold) and on one GPU beyond SELECT_SMALL_MAX cells.  The exclusion rule
+// (main.rs:330-335) for this rank's cells runs in the same launch.
+constexpr int SELECT_COOP_HIST = 8 * SELECT_TARGETS * 256;  // u32 words
+constexpr int SELECT_COOP_SCRATCH = SELECT_COOP_HIST + 8;   // + {or, nor} (2 x u64) + n_list + pad
+__global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
+    const double* __restrict__ vals, uint64_t n, SelectPlan plan, const IterParams* __restrict__ prm,
+    DeviceStats* __restrict__ st, unsigned int* __restrict__ scratch, unsigned long long* __restrict__ glist,
+    const double* __restrict__ norm_local, uint32_t n_cells_local, uint32_t* __restrict__ bits) {
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    __shared__ unsigned int sh[SELECT_TARGETS][256];
+    __shared__ unsigned long long spre[SELECT_TARGETS], srank[SELECT_TARGETS];
+    __shared__ int sgrp[SELECT_TARGETS];
+    __shared__ unsigned long long s_or[32], s_nor[32];
+    __shared__ unsigned int scnt[SELECT_TARGETS], s_total;
+    __shared__ int s_nlead, s_leadt[SELECT_TARGETS];
+    __shared__ unsigned long long s_leadpre[SELECT_TARGETS], s_result[SELECT_TARGETS];
+    __shared__ unsigned long long s_list[SELECT_RANK_CAP];
+    __shared__ double sthr;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long* g_or = reinterpret_cast<unsigned long long*>(scratch + SELECT_COOP_HIST);
+    unsigned int* g_nlist = scratch + SELECT_COOP_HIST + 4;
+    unsigned long long key[SELECT_R];
+    unsigned int valid = 0;
+    unsigned long long k_or = 0ull, k_nor = 0ull;
+#pragma unroll
+    for (int j = 0; j < SELECT_R; ++j) {
+        const uint64_t i = ((uint64_t)blockIdx.x * SELECT_R + j) * SELECT_SMALL_THREADS + tid;
+        key[j] = 0ull;
+        if (i < n) {
+            key[j] = f64_to_key(vals[i]);
+            valid |= 1u << j;
+            k_or |= key[j];
+            k_nor |= ~key[j];
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        k_or |= __shfl_xor_sync(0xffffffffu, k_or, off);
+        k_nor |= __shfl_xor_sync(0xffffffffu, k_nor, off);
+    }
+    if (lane == 0) { s_or[warp] = k_or; s_nor[warp] = k_nor; }
+    if (tid < SELECT_TARGETS) srank[tid] = plan.rank[tid];
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < SELECT_SMALL_THREADS / 32; ++w) { k_or |= s_or[w]; k_nor |= s_nor[w]; }
+        atomicOr(&g_or[0], k_or);
+        atomicOr(&g_or[1], k_nor);
+    }
+    grid.sync();
+    k_or = __ldcg(&g_or[0]);
+    k_nor = __ldcg(&g_or[1]);
+    const unsigned long long diff = k_or & k_nor;  // bits that are 1 in some key and 0 in another
+    int hi_bit = diff ? 64 - __clzll((long long)diff) : 0;
+    if (tid < SELECT_TARGETS) {
+        spre[tid] = hi_bit >= 64 ? 0ull : (k_or >> hi_bit);
+        scnt[tid] = (unsigned int)(n > 0xFFFFFFFFull ? 0xFFFFFFFFull : n);
+    }
+    if (tid == 0) s_total = (unsigned int)(n > 0xFFFFFFFFull ? 0xFFFFFFFFull : n);
+    __syncthreads();
+    int pass = 0;
+    while (hi_bit > 0 && s_total > SELECT_RANK_CAP) {
+        const int lo_bit = hi_bit > 8 ? hi_bit - 8 : 0;
+        const unsigned int dmask = (1u << (hi_bit - lo_bit)) - 1u;
+        unsigned int* gh = scratch + (size_t)pass * SELECT_TARGETS * 256;
+        for (int i = tid; i < SELECT_TARGETS * 256; i += SELECT_SMALL_THREADS) (&sh[0][0])[i] = 0;
+        if (tid < SELECT_TARGETS) {
+            unsigned long long p[SELECT_TARGETS];
+#pragma unroll
+            for (int u = 0; u < SELECT_TARGETS; ++u) p[u] = spre[u];
+            int g = tid;
+#pragma unroll
+            for (int u = SELECT_TARGETS - 1; u >= 0; --u)
+                if (u < tid && p[u] == p[tid]) g = u;
+            sgrp[tid] = g;
+            int pos = 0, nl = 0;
+#pragma unroll
+            for (int u = 0; u < SELECT_TARGETS; ++u) {
+                bool lead = true;
+#pragma unroll
+                for (int v = 0; v < SELECT_TARGETS; ++v) lead = lead && !(v < u && p[v] == p[u]);
+                pos += (lead && u < tid) ? 1 : 0;
+                nl += lead ? 1 : 0;
+            }
+            if (g == tid) { s_leadt[pos] = tid; s_leadpre[pos] = p[tid]; }
+            if (tid == 0) s_nlead = nl;
+        }
+        __syncthreads();
+        const int nlead = s_nlead;
+        if (valid) {
+            unsigned long long lpre[SELECT_TARGETS];
+            int lrow[SELECT_TARGETS];
+#pragma unroll
+            for (int k = 0; k < SELECT_TARGETS; ++k) {
+                lpre[k] = k < nlead ? s_leadpre[k] : ~0ull;
+                lrow[k] = k < nlead ? s_leadt[k] : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < SELECT_R; ++j) {
+                if (!((valid >> j) & 1u)) continue;
+                const unsigned long long pk = hi_bit >= 64 ? 0ull : (key[j] >> hi_bit);
+                const unsigned int d = (unsigned int)(key[j] >> lo_bit) & dmask;
+#pragma unroll
+                for (int k = 0; k < SELECT_TARGETS; ++k)
+                    if (k < nlead && pk == lpre[k]) atomicAdd(&sh[lrow[k]][d], 1u);
+            }
+        }
+        __syncthreads();
+        for (int i = tid; i < SELECT_TARGETS * 256; i += SELECT_SMALL_THREADS) {
+            const unsigned int v = (&sh[0][0])[i];
+            if (v) atomicAdd(&gh[i], v);
+        }
+        grid.sync();
+        for (int i = tid; i < SELECT_TARGETS * 256; i += SELECT_SMALL_THREADS) (&sh[0][0])[i] = __ldcg(&gh[i]);
+        __syncthreads();
+        if (warp < SELECT_TARGETS) {
+            const int t = warp;
+            const unsigned int* h = sh[sgrp[t]];
+            unsigned int c[8], tot = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                c[j] = h[lane * 8 + j];
+                tot += c[j];
+            }
+            unsigned int incl = tot;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const unsigned int o = __shfl_up_sync(0xffffffffu, incl, off);
+                if (lane >= off) incl += o;
+            }
+            const unsigned long long r = srank[t];
+            const unsigned long long excl = incl - tot;
+            const bool here = r >= excl && r < (unsigned long long)incl;
+            const unsigned int who = __ballot_sync(0xffffffffu, here);
+            const int src = who ? __ffs(who) - 1 : 31;
+            __syncwarp();
+            if (lane == src) {
+                unsigned long long rr = r - excl;
+                int j = 0;
+                for (; j < 7; ++j) {
+                    if (rr < c[j]) break;
+                    rr -= c[j];
+                }
+                spre[t] = (spre[t] << (hi_bit - lo_bit)) | (unsigned long long)(lane * 8 + j);
+                srank[t] = rr;
+                scnt[t] = c[j];
+            }
+        }
+        __syncthreads();
+        if (tid == 0) s_total = 0;
+        __syncthreads();
+        if (tid < SELECT_TARGETS) {
+            bool first = true;
+#pragma unroll
+            for (int u = 0; u < SELECT_TARGETS; ++u) first = first && !(u < tid && spre[u] == spre[tid]);
+            if (first) atomicAdd(&s_total, scnt[tid]);
+        }
+        if (valid) {
+            unsigned long long pre[SELECT_TARGETS];
+#pragma unroll
+            for (int t = 0; t < SELECT_TARGETS; ++t) pre[t] = spre[t];
+#pragma unroll
+            for (int j = 0; j < SELECT_R; ++j) {
+                if (!((valid >> j) & 1u)) continue;
+                const unsigned long long pk = key[j] >> lo_bit;
+                bool keep = false;
+#pragma unroll
+                for (int t = 0; t < SELECT_TARGETS; ++t) keep = keep || pk == pre[t];
+                if (!keep) valid &= ~(1u << j);
+            }
+        }
+        hi_bit = lo_bit;
+        ++pass;
+        __syncthreads();
+    }
+    if (hi_bit > 0 && n > 0) {
+        // few keys left over the whole grid: every CTA appends its survivors to one global list, then ranks them
+        if (valid) {
+#pragma unroll
+            for (int j = 0; j < SELECT_R; ++j)
+                if ((valid >> j) & 1u) {
+                    const unsigned int slot = atomicAdd(g_nlist, 1u);
+                    if (slot < SELECT_RANK_CAP) glist[slot] = key[j];
+                }
+        }
+        grid.sync();
+        const unsigned int nl = min(__ldcg(g_nlist), SELECT_RANK_CAP);
+        for (unsigned int i = tid; i < nl; i += SELECT_SMALL_THREADS) s_list[i] = __ldcg(&glist[i]);
+        __syncthreads();
+        if (warp < SELECT_TARGETS) {
+            const int t = warp;
+            const unsigned long long pre = spre[t], want = srank[t];
+            for (unsigned int i = lane; i < nl; i += 32) {
+                const unsigned long long ki = s_list[i];
+                if ((hi_bit >= 64 ? 0ull : (ki >> hi_bit)) != pre) continue;
+                unsigned long long before = 0;
+                for (unsigned int j = 0; j < nl; ++j) {
+                    const unsigned long long kj = s_list[j];
+                    if ((hi_bit >= 64 ? 0ull : (kj >> hi_bit)) != pre) continue;
+                    before += (kj < ki || (kj == ki && j < i)) ? 1ull : 0ull;
+                }
+                if (before == want) s_result[t] = ki;
+            }
+        }
+        __syncthreads();
+        if (tid < SELECT_TARGETS) spre[tid] = s_result[tid];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        double x[SELECT_TARGETS];
+#pragma unroll
+        for (int t = 0; t < SELECT_TARGETS; ++t) x[t] = n ? key_to_f64(spre[t]) : 0.0;
+        DeviceStats tmp;
+        finish_stats(x, plan, prm->iqr_multiple, &tmp);
+        sthr = tmp.threshold;
+        if (blockIdx.x == 0) {
+            st->median = tmp.median;
+            st->q1 = tmp.q1;
+            st->q3 = tmp.q3;
+            st->iqr = tmp.iqr;
+            st->threshold = tmp.threshold;
+        }
+    }
+    __syncthreads();
+    if (bits != nullptr) {  // new excluded set of this rank's cells, one bitmap word per warp step
+        const double thr = sthr;
+        const uint32_t n_words = (n_cells_local + 31) / 32;
+        unsigned int nn = 0, nr = 0, ne = 0;
+        for (uint32_t w = blockIdx.x * (SELECT_SMALL_THREADS / 32) + warp; w < n_words; w += gridDim.x * (SELECT_SMALL_THREADS / 32)) {
+            const uint32_t i = w * 32 + lane;
+            const bool ex = i < n_cells_local && norm_local[i] < thr;  // main.rs:331
+            const unsigned int word = __ballot_sync(0xffffffffu, ex);
+            if (lane == 0) {
+                const unsigned int old = bits[w];
+                bits[w] = word;
                 nn += __popc(word & ~old);
                 nr += __popc(old & ~word);
                 ne += __popc(word);
