@@ -305,6 +305,18 @@ int clx_final_locus_counts(clx_ctx* c, uint64_t* minority_ref_alt, uint64_t* maj
     return rc;
 }
 
+void* clx_alloc_pinned(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+void clx_free_pinned(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
 int clx_get_phase_ms(clx_ctx* c, int phase, double* total_ms, uint64_t* launches) {
     if (!c || phase < 0 || phase >= CLX_PHASE_COUNT) return CLX_ERR_ARG;
     if (total_ms) *total_ms = c->phase_ms[phase];

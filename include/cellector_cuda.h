@@ -136,6 +136,11 @@ int clx_posteriors(clx_ctx* ctx, double posterior_threshold, uint32_t min_loci_u
  * [n_loci0][2] = (ref, alt).  Replaces the third text pass of load_mtx_final. */
 int clx_final_locus_counts(clx_ctx* ctx, uint64_t* minority_ref_alt, uint64_t* majority_ref_alt);
 
+/* Page-locked host memory for the COO arrays handed to clx_load_coo (what a host parser fills; replaces the
+ * row-list Vec growth of load_data.rs:165-173).  Works without a context; returns NULL on failure. */
+void* clx_alloc_pinned(size_t bytes);
+void clx_free_pinned(void* p);
+
 /* Profiling helpers (not part of the reference surface). */
 int clx_get_phase_ms(clx_ctx* ctx, int phase, double* total_ms, uint64_t* launches);
 int clx_reset_phase_ms(clx_ctx* ctx);

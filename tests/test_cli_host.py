@@ -1,0 +1,113 @@
+"""Host side of the `cellector` CLI that needs no GPU: the single-pass multi-threaded mtx pair parser
+(replaces load_data.rs:190-223, 240-251) and the Rust-Display number formatting of the writers."""
+import gzip
+import os
+import struct
+import subprocess
+from decimal import Decimal
+
+import numpy as np
+import pytest
+
+from cellector_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CLI = os.path.join(ROOT, "cellector_b200", "bin", "cellector")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built():
+    if not os.path.exists(CLI):
+        from cellector_b200 import build
+        build.build_all()
+    assert os.path.exists(CLI)
+
+
+def fnv1a(a):
+    h = 1469598103934665603
+    for v in np.asarray(a, np.uint64).tolist():
+        h = ((h ^ v) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def parse_only(alt, ref, threads=4, extra=()):
+    r = subprocess.run([CLI, "-a", alt, "-r", ref, "-b", "/dev/null", "--output_directory", "/tmp", "--parse_only", "--threads", str(threads),
+                        *extra], capture_output=True, text=True, timeout=120)
+    return r
+
+
+def fields(out):
+    t = out.split()
+    return {t[i]: t[i + 1] for i in range(1, len(t) - 1, 2)}
+
+
+@pytest.mark.parametrize("threads", [1, 3, 8])
+def test_parser_matches_numpy(tmp_path, threads):
+    d = synth.generate(synth.SynthConfig(n_cells=700, n_loci=2500, density=0.03, seed=4, deep_frac=0.02, deep_mean=300.0))
+    paths = synth.write_mtx_pair(d, str(tmp_path))
+    r = parse_only(paths["alt.mtx"], paths["ref.mtx"], threads)
+    assert r.returncode == 0, r.stderr
+    f = fields(r.stdout)
+    assert int(f["loci"]) == d.n_loci and int(f["cells"]) == d.n_cells and int(f["pairs"]) == d.nnz
+    assert int(f["fnv_locus"]) == fnv1a(d.locus) and int(f["fnv_cell"]) == fnv1a(d.cell)
+    assert int(f["fnv_ref"]) == fnv1a(d.ref) and int(f["fnv_alt"]) == fnv1a(d.alt)
+
+
+def test_parser_gz_crlf_and_ragged(tmp_path):
+    # gz by extension (load_data.rs:246-247), CRLF / mixed whitespace (split_whitespace), no trailing newline,
+    # header nnz ignored, and izip! stopping at the shorter file
+    alt = "%%MatrixMarket matrix coordinate real general\r\n% c\r\n5 4 999\r\n1\t1\t2\r\n  3 2   0\r\n5\t4\t7\r\n4 4 1"
+    ref = "%%MatrixMarket matrix coordinate real general\n% c\n5\t4\t0\n9 9 1\n9 9 +3\n9 9 0\n"
+    a, r = tmp_path / "alt.mtx.gz", tmp_path / "ref.mtx"
+    with gzip.open(a, "wt", newline="") as f:
+        f.write(alt)
+    r.write_text(ref)
+    res = parse_only(str(a), str(r), 2)
+    assert res.returncode == 0, res.stderr
+    f = fields(res.stdout)
+    assert (int(f["loci"]), int(f["cells"]), int(f["pairs"])) == (5, 4, 3)
+    assert int(f["fnv_locus"]) == fnv1a([0, 2, 4]) and int(f["fnv_cell"]) == fnv1a([0, 1, 3])
+    assert int(f["fnv_alt"]) == fnv1a([2, 0, 7]) and int(f["fnv_ref"]) == fnv1a([1, 3, 0])
+
+
+@pytest.mark.parametrize("bad", ["1 1 2.0\n", "1 1\n", "0 1 1\n", "\n", "1 x 1\n"])
+def test_parser_rejects_what_the_reference_panics_on(tmp_path, bad):
+    hdr = "%%MatrixMarket matrix coordinate real general\n% c\n5 4 1\n"
+    (tmp_path / "alt.mtx").write_text(hdr + bad)
+    (tmp_path / "ref.mtx").write_text(hdr + "1 1 1\n")
+    res = parse_only(str(tmp_path / "alt.mtx"), str(tmp_path / "ref.mtx"))
+    assert res.returncode == 101 and "malformed" in res.stderr
+
+
+def rust_display(x: float) -> str:
+    if x != x:
+        return "NaN"
+    if x in (float("inf"), float("-inf")):
+        return "inf" if x > 0 else "-inf"
+    s = format(Decimal(repr(x)), "f")
+    if "." in s:
+        s = s.rstrip("0").rstrip(".")
+    return s
+
+
+def test_number_formatting_is_rust_display():
+    rng = np.random.default_rng(5)
+    vals = [0.0, -0.0, 17.0, 1e-7, 1e21, -2.055795012245653, 0.1, 1 / 3, 5e-324, 1.7976931348623157e308, 123456789.125,
+            float("nan"), float("inf"), float("-inf"), 0.999, 255.0, -80.0, 1e15, 1e16, 1e17, 123456789012345680.0]
+    vals += list(rng.standard_normal(200) * 10.0 ** rng.integers(-12, 12, 200))
+    vals += list(-np.abs(rng.standard_normal(100)) * 300)
+    inp = "\n".join(format(struct.unpack("<Q", struct.pack("<d", float(v)))[0], "x") for v in vals) + "\n"
+    r = subprocess.run([CLI, "--format_selftest"], input=inp, capture_output=True, text=True, timeout=60)
+    got = r.stdout.split("\n")[:-1]
+    assert len(got) == len(vals)
+    for v, g in zip(vals, got):
+        assert g == rust_display(float(v)), (v, g, rust_display(float(v)))
+        if v == v:
+            assert float(g) == float(v)  # round-trips
+
+
+def test_cli_flag_errors(tmp_path):
+    r = subprocess.run([CLI, "-a", "x"], capture_output=True, text=True)
+    assert r.returncode == 1 and "required arguments" in r.stderr
+    r = subprocess.run([CLI, "--bogus", "1"], capture_output=True, text=True)
+    assert r.returncode == 1 and "wasn't expected" in r.stderr
