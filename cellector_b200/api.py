@@ -69,6 +69,7 @@ ABI = {
     "final_locus_counts": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "get_phase_ms": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     "reset_phase_ms": (C.c_int, [C.c_void_p]),
+    "set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "get_stream": (C.c_void_p, [C.c_void_p]),
     "score_bytes": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
@@ -232,6 +233,9 @@ class Cellector(CtxApi):
             self._check(self._lib.clx_get_phase_ms(self._h, i, C.byref(ms), C.byref(n)), "get_phase_ms")
             out[name] = (ms.value, int(n.value))
         return out
+
+    def set_profiling(self, on: bool):
+        self._check(self._lib.clx_set_profiling(self._h, 1 if on else 0), "set_profiling")
 
     def reset_phase_ms(self):
         self._check(self._lib.clx_reset_phase_ms(self._h), "reset_phase_ms")

@@ -323,6 +323,15 @@ int clx_get_phase_ms(clx_ctx* c, int phase, double* total_ms, uint64_t* launches
     if (launches) *launches = c->phase_launches[phase];
     return CLX_OK;
 }
+int clx_set_profiling(clx_ctx* c, int on) {
+    if (!c) return CLX_ERR_ARG;
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    phase_resolve(c);
+    em_drop_graph(c);  // the events are nodes of the captured iteration
+    if (on) c->flags |= CLX_FLAG_PROFILE;
+    else c->flags &= ~CLX_FLAG_PROFILE;
+    return CLX_OK;
+}
 int clx_reset_phase_ms(clx_ctx* c) {
     if (!c) return CLX_ERR_ARG;
     for (int i = 0; i < CLX_PHASE_COUNT; ++i) {

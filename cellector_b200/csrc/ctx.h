@@ -109,6 +109,9 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> h_row_ptr;                      // [n_cells + 1]
     clx::DevBuf<uint32_t> hc_perm;                        // [n_heavy] CSC order -> index into the CSR-order lists
     clx::DevBuf<uint32_t> hc_col_ptr;                     // [n_loci + 1]
+    clx::DevBuf<uint32_t> hc_cell, hc_ref, hc_alt;        // [n_heavy] the heavy entries again, in CSC order (column pass)
+    clx::DevBuf<uint32_t> h2c;                            // [n_heavy] CSR-order index -> CSC-order index
+    clx::DevBuf<double> hv_c;                             // [n_heavy] EM-pass log_pmf of the heavy entries in CSC order
     clx::DevBuf<uint32_t> giant_idx;                      // [n_giant] heavy entries with total > HEAVY_GIANT_TOTAL
     uint32_t n_giant = 0;
     clx::DevBuf<double> hv_ll, hv_e;                      // [3 * n_heavy] values of the current scoring pass
@@ -122,12 +125,18 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> tl_pk_base;                 // [n_units + 1] first packet of every (cell block, tile) unit
     clx::DevBuf<uint32_t> tl_items;                   // [n_items][4] cell block, first tile, end tile, -
     clx::DevBuf<uint32_t> tl_cb_item;                 // [Pc + 1] first item of every cell block
+    clx::DevBuf<uint32_t> tl_order;                   // [n_items] items by decreasing entry count (work-queue order)
+    clx::DevBuf<uint32_t> tl_counter;                 // [1] work-queue cursor (k_score_finish re-arms it)
     clx::DevBuf<double> tl_part;                      // [n_items][NB][2] per-item partial (log_pmf, expected) sums
     clx::DevBuf<double> tab13;                        // [3][nT * TILE_L][13] compact memo records for the tiled kernel
     clx::DevBuf<uint32_t> n_used, row_len;            // [n_cells] loci_used_per_cell (main.rs:575) / stored row length
     // retained COO for clx_final_locus_counts
     clx::DevBuf<uint32_t> coo_locus, coo_cell, coo_ref, coo_alt;
     clx::DevBuf<double> lnfact;  // [171]
+    // lng[i] = ln_gamma((double)i), i in [1, lng_n): every ln_gamma argument of the EM pass is an integer-valued
+    // double (alpha, beta = allele counts + 1), so the per-iteration table build is lookups, not Lanczos series
+    clx::DevBuf<double> lng;
+    uint32_t lng_n = 0;
     double lbc10[10];
 
     // --- EM state (em.cu)

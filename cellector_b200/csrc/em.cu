@@ -18,6 +18,11 @@ namespace {
 
 constexpr int TPB = 256;
 
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
 int pick_group(double avg_len) {
     // lanes per row/column: every lane should have about one unrolled batch (SCORE_UNROLL 128-bit loads of two
     // entries) of work, so that all of a row's loads are in flight at once
@@ -34,10 +39,6 @@ Lbc10 make_lbc(const clx_ctx* c) {
 
 bool use_tiled(const clx_ctx* c) { return c->tiled_ready && !(c->flags & CLX_FLAG_KERNEL_V0); }
 
-int env_int(const char* name, int dflt) {
-    const char* v = getenv(name);
-    return (v && *v) ? atoi(v) : dflt;
-}
 
 template <int NT, bool WITH_E>
 void launch_score_rows(clx_ctx* c, int G) {
@@ -61,6 +62,17 @@ template <bool FUSE>
 void launch_columns(clx_ctx* c, int G) {
     const uint32_t n = c->n_loci;
     if (n == 0) return;
+    // k_columns_w (one warp per column, software-pipelined) measured slower than the G-lanes-per-column kernel on
+    // B200 at both bench sizes (C2: 33 vs 28 us, C3 shard: 197 vs 150 us): opt-in until that is understood
+    static const int warp_cols = env_int("CLX_COLUMNS_W", 0);
+    if (warp_cols) {
+        const unsigned grid = std::min<unsigned>((n + COLW_WARPS - 1) / COLW_WARPS, (unsigned)c->sm_count * (unsigned)env_int("CLX_COLW_CTAS", 3));
+        k_columns_w<FUSE><<<grid, COLW_WARPS * 32, 0, c->stream>>>(
+            c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_cell.p, c->hc_ref.p,
+            c->hc_alt.p, c->hv_c.p, c->loc_ll.p, c->loc_int.p, c->n_used.p, c->d_stats.p);
+        c->launches++;
+        return;
+    }
 #define CLX_COLS(GG)                                                                                                   \
     k_columns<GG, FUSE><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                          \
         c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_perm.p,            \
@@ -233,7 +245,7 @@ int enqueue_iteration(clx_ctx* c) {
     if (L) {
         k_tables<0><<<(L + TAB_LPB - 1) / TAB_LPB, TPB, 0, s>>>(
             c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), 0.0, 0.0, with_e,
-            c->loci_used.p, c->tab.p, c->tiled_ready ? c->tab13.p : nullptr, c->tl_nT * TILE_L, c->d_stats.p);
+            c->loci_used.p, c->tab.p, c->tiled_ready ? c->tab13.p : nullptr, c->tl_nT * TILE_L, c->d_stats.p, c->lng.p, c->lng_n);
         c->launches++;
     } else {
         CLX_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, sizeof(DeviceStats), s));
@@ -245,11 +257,12 @@ int enqueue_iteration(clx_ctx* c) {
     phase_begin(c, CLX_PHASE_HEAVY);
     if (c->n_heavy) {
         k_heavy_em<<<(unsigned)((c->n_heavy + HEAVY_HB - 1) / HEAVY_HB), TPB, 0, s>>>(
-            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, c->tab.p, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, c->tab.p, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p,
+            c->lng.p, c->lng_n, c->h2c.p, c->hv_c.p);
         c->launches++;
         if (c->n_giant) {
             k_heavy_giant<<<c->n_giant, TPB, 0, s>>>(c->giant_idx.p, c->n_giant, c->h_locus.p, c->h_ref.p, c->h_alt.p, c->tab.p,
-                                                     c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+                                                     c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, c->h2c.p, c->hv_c.p);
             c->launches++;
         }
     }
@@ -396,7 +409,7 @@ int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used
     if (L) {
         k_tables<1><<<3 * ((L + TAB_LPB - 1) / TAB_LPB), TPB, 0, s>>>(
             c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), mf_unclamped, mf, 0,
-            nullptr, c->tab.p, c->tiled_ready ? c->tab13.p : nullptr, c->tl_nT * TILE_L, nullptr);
+            nullptr, c->tab.p, c->tiled_ready ? c->tab13.p : nullptr, c->tl_nT * TILE_L, nullptr, c->lng.p, c->lng_n);
         c->launches++;
     }
     phase_end(c, CLX_PHASE_TABLES);

@@ -40,7 +40,8 @@ __global__ void __launch_bounds__(256) k_tables(const unsigned long long* __rest
                                                 Lbc10 lbc, double mf, double mf_clamped, int with_expected,
                                                 const uint8_t* __restrict__ used, double* __restrict__ tab,
                                                 double* __restrict__ tab13, uint32_t n_loci_pad,
-                                                DeviceStats* __restrict__ st_clear) {
+                                                DeviceStats* __restrict__ st_clear, const double* __restrict__ lng,
+                                                uint32_t lng_n) {
     static_assert(K_LIGHT == 3, "task layout below is for K_LIGHT == 3");
     constexpr int NTASK = MODE == 0 ? 12 : 18;
     constexpr int TDEN = NTASK - 1;  // task index of ln_gamma(alpha + beta)
@@ -103,7 +104,7 @@ __global__ void __launch_bounds__(256) k_tables(const unsigned long long* __rest
             const int pa = p < 2 ? p : (p < 5 ? p - 2 : p - 5);
             x = ((double)pa + alpha) + ((double)(pn - pa) + beta);
         }
-        s_g[ll][j] = ln_gamma(x);
+        s_g[ll][j] = MODE == 0 ? ln_gamma_int(x, lng, lng_n) : ln_gamma(x);
     }
     __syncthreads();
     // phase 2a: T(a | n) = lbc + (lga[a] + lgb[r] - lgab) - den for the nine pairs; record tail
@@ -191,7 +192,9 @@ __device__ __forceinline__ double heavy_ll_k(uint64_t n, uint64_t k, const doubl
 __global__ void __launch_bounds__(256) k_heavy_em(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                                   const uint32_t* __restrict__ h_alt, uint32_t n_heavy,
                                                   const double* __restrict__ tab, const double* __restrict__ lnfact,
-                                                  int with_expected, double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+                                                  int with_expected, double* __restrict__ hv_ll, double* __restrict__ hv_e,
+                                                  const double* __restrict__ lng, uint32_t lng_n,
+                                                  const uint32_t* __restrict__ h2c, double* __restrict__ hv_c) {
     __shared__ double s_g[HEAVY_CAP];
     __shared__ double s_ll[HEAVY_CAP];  // pmf k of the entry whose tasks start at g0 sits at s_ll[g0 + k]
     __shared__ double s_alpha[HEAVY_HB], s_beta[HEAVY_HB], s_den[HEAVY_HB];
@@ -215,6 +218,7 @@ __global__ void __launch_bounds__(256) k_heavy_em(const uint32_t* __restrict__ h
             if (!on) {
                 hv_ll[h] = 0.0;
                 hv_e[h] = 0.0;
+                hv_c[h2c[h]] = 0.0;
             } else if (nn <= HEAVY_GIANT) {
                 n = (uint32_t)nn;
                 ntask = with_expected ? 2 * (n + 1) + 1 : 3;
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(256) k_heavy_em(const uint32_t* __restrict__ h
             } else {
                 x = j == 0 ? (double)a + alpha : (j == 1 ? (double)(n - a) + beta : ((double)a + alpha) + ((double)(n - a) + beta));
             }
-            s_g[task] = ln_gamma(x);
+            s_g[task] = ln_gamma_int(x, lng, lng_n);
         }
         __syncthreads();
         if (with_expected) {
@@ -285,6 +289,7 @@ __global__ void __launch_bounds__(256) k_heavy_em(const uint32_t* __restrict__ h
                 if (s_off[e + 1] == s_off[e]) continue;  // switched off or giant
                 const uint32_t p0 = s_off[e] - base;
                 hv_ll[h0 + e] = s_ll[p0 + s_a[e]];
+                hv_c[h2c[h0 + e]] = s_ll[p0 + s_a[e]];
                 if (n <= HEAVY_CHAIN_MAX) {
                     double ex = 2.0 * s_ll[p0];
                     for (uint32_t k = 1; k <= n; ++k) ex = logsumexp2(ex, 2.0 * s_ll[p0 + k]);
@@ -311,7 +316,9 @@ __global__ void __launch_bounds__(256) k_heavy_em(const uint32_t* __restrict__ h
                 if (s_off[e + 1] == s_off[e]) continue;
                 const uint32_t g0 = s_off[e] - base, n = s_n[e], a = s_a[e];
                 const double num = s_g[g0] + s_g[g0 + 1] - s_g[g0 + 2];
-                hv_ll[h0 + e] = ln_binomial(n, a, lnfact) + num - s_den[e];
+                const double v = ln_binomial(n, a, lnfact) + num - s_den[e];
+                hv_ll[h0 + e] = v;
+                hv_c[h2c[h0 + e]] = v;
                 hv_e[h0 + e] = 0.0;
             }
         }
@@ -326,7 +333,8 @@ __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict_
                                                      const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                                      const uint32_t* __restrict__ h_alt, const double* __restrict__ tab,
                                                      const double* __restrict__ lnfact, int with_expected,
-                                                     double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+                                                     double* __restrict__ hv_ll, double* __restrict__ hv_e,
+                                                     const uint32_t* __restrict__ h2c, double* __restrict__ hv_c) {
     __shared__ double s_m[8], s_s[8];
     const uint32_t h = giant_idx[blockIdx.x];
     const double* rec = tab + (size_t)h_locus[h] * TAB_STRIDE;
@@ -334,7 +342,11 @@ __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict_
     if (!(den == den)) return;  // switched off: k_heavy_em wrote the zeros
     const uint64_t a = h_alt[h], r = h_ref[h], n = a + r;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) hv_ll[h] = log_beta_binomial_pmf_den((double)a, (double)r, alpha, beta, ln_binomial(n, a, lnfact), den);
+    if (tid == 0) {
+        const double v = log_beta_binomial_pmf_den((double)a, (double)r, alpha, beta, ln_binomial(n, a, lnfact), den);
+        hv_ll[h] = v;
+        hv_c[h2c[h]] = v;
+    }
     if (!with_expected) {
         if (tid == 0) hv_e[h] = 0.0;
         return;
@@ -608,6 +620,196 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
             if (f) atomicAdd(&st->n_loci_filtered, (unsigned long long)f);
             if (u) atomicAdd(&st->n_loci_in_use, (unsigned long long)u);
         }
+    }
+}
+
+// Lean variant of the column pass: ONE WARP PER COLUMN (persistent, warp-strided), one coalesced 8-byte load per
+// entry and lane (a warp load is 256 contiguous bytes), 32-bit indices relative to the column start, the column's
+// memo slots staged in shared memory per warp, majority counts derived from the totals (integers).  Same outputs
+// as k_columns; the old kernel spent ~100 instructions per 32 entries on 64-bit bounds checks.
+constexpr int COLW_WARPS = 8;
+constexpr int COLW_U = 4;
+struct ColAcc {
+    double s_min, s_maj;
+    uint32_t c_min, r_min, a_min, r_all, a_all;
+};
+__device__ __forceinline__ void colw_batch(const uint2 (&q)[COLW_U], uint32_t i0, uint32_t len, uint32_t lane,
+                                           const uint32_t* __restrict__ excl_bits, const double* __restrict__ rec, ColAcc& A) {
+    uint32_t w[COLW_U];
+#pragma unroll
+    for (int u = 0; u < COLW_U; ++u) w[u] = __ldg(excl_bits + (q[u].x >> 5));  // cell 0 for a slot past the end: a valid address
+#pragma unroll
+    for (int u = 0; u < COLW_U; ++u) {
+        const bool valid = i0 + 32u * u + lane < len;
+        const bool ex = valid && ((w[u] >> (q[u].x & 31u)) & 1u);
+        const uint32_t r = q[u].y & 0xFFFFu, a = q[u].y >> 16, n = r + a;
+        const bool light = (n - 1u) < (uint32_t)K_LIGHT;  // a slot past the end has n = 0; zero totals / the heavy marker are not light
+        const double v = light ? rec[((n - 1u) << 2) + a] : 0.0;
+        const uint32_t rl = light ? r : 0u, al = light ? a : 0u;
+        A.c_min += ex ? 1u : 0u;
+        A.s_min += ex ? v : 0.0;
+        A.s_maj += ex ? 0.0 : v;
+        A.r_min += ex ? rl : 0u;
+        A.a_min += ex ? al : 0u;
+        A.r_all += rl;
+        A.a_all += al;
+    }
+}
+// Software pipeline per warp: column pointers are fetched two columns ahead, the first COLW_U x 32 entries, the memo
+// slots and the tail operands (heavy range, in-use flag) one column ahead, so a warp always has a column's worth of
+// loads in flight while it sums the current one.
+template <bool FUSE_FILTER>
+__global__ void __launch_bounds__(COLW_WARPS * 32) k_columns_w(
+    const ColEntry* __restrict__ csc, const uint64_t* __restrict__ col_ptr, uint32_t n_loci, const double* __restrict__ tab,
+    uint8_t* __restrict__ used, const uint32_t* __restrict__ excl_bits, const uint32_t* __restrict__ hc_col_ptr,
+    const uint32_t* __restrict__ hc_cell, const uint32_t* __restrict__ hc_ref, const uint32_t* __restrict__ hc_alt,
+    const double* __restrict__ hv_c, double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int,
+    uint32_t* __restrict__ n_used, DeviceStats* __restrict__ st) {
+    constexpr int U = COLW_U;
+    __shared__ double s_rec[COLW_WARPS][12];
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t n_warps = gridDim.x * COLW_WARPS;
+    const size_t L = n_loci;
+    uint32_t f_cnt = 0, u_cnt = 0;
+    uint32_t l = blockIdx.x * COLW_WARPS + wib;
+    if (l >= n_loci) return;
+    uint32_t ln = l + n_warps;
+    uint64_t b0 = __ldg(col_ptr + l), e0 = __ldg(col_ptr + l + 1), b1 = 0, e1 = 0;
+    if (ln < n_loci) {
+        b1 = __ldg(col_ptr + ln);
+        e1 = __ldg(col_ptr + ln + 1);
+    }
+    uint2 q[U], qn[U];
+    double recv = 0.0, recn = 0.0;
+    uint32_t tp = 0, tpn = 0;  // lane 0: first heavy entry, lane 1: end of the heavy range, lane 2: in-use flag
+    auto prefetch = [&](uint32_t col, uint64_t begin, uint64_t end, uint2 (&dst)[U], double& rv, uint32_t& t) {
+        const uint32_t len = (uint32_t)(end - begin);
+        const uint2* __restrict__ p = reinterpret_cast<const uint2*>(csc + begin);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t idx = 32u * u + lane;
+            dst[u] = idx < len ? __ldg(p + idx) : make_uint2(0u, 0u);
+        }
+        rv = lane < 12 ? __ldg(tab + (size_t)col * TAB_STRIDE + lane) : 0.0;
+        t = lane < 2 ? __ldg(hc_col_ptr + col + lane) : (lane == 2 ? (uint32_t)used[col] : 0u);
+    };
+    prefetch(l, b0, e0, q, recv, tp);
+    for (;;) {
+        const uint32_t l2 = ln + n_warps;
+        uint64_t b2 = 0, e2 = 0;
+        if (ln < n_loci && l2 < n_loci) {
+            b2 = __ldg(col_ptr + l2);
+            e2 = __ldg(col_ptr + l2 + 1);
+        }
+        if (ln < n_loci) prefetch(ln, b1, e1, qn, recn, tpn);
+        // ---- current column
+        if (lane < 12) s_rec[wib][lane] = recv;
+        __syncwarp();
+        const uint32_t len = (uint32_t)(e0 - b0);
+        const uint2* __restrict__ p = reinterpret_cast<const uint2*>(csc + b0);
+        const uint32_t hb = __shfl_sync(0xffffffffu, tp, 0), he = __shfl_sync(0xffffffffu, tp, 1);
+        const bool on = __shfl_sync(0xffffffffu, tp, 2) != 0;  // entries were scored only if the locus was in use (main.rs:556)
+        // the column's heavy entries (CSC-ordered side arrays), one per lane: loads issued before the light entries are summed
+        uint32_t hcell = 0, href = 0, halt = 0;
+        double hval = 0.0;
+        if (hb + lane < he) {
+            hcell = __ldg(hc_cell + hb + lane);
+            href = __ldg(hc_ref + hb + lane);
+            halt = __ldg(hc_alt + hb + lane);
+            hval = __ldg(hv_c + hb + lane);
+        }
+        ColAcc A = {0.0, 0.0, 0u, 0u, 0u, 0u, 0u};
+        colw_batch(q, 0u, len, lane, excl_bits, s_rec[wib], A);
+        for (uint32_t i0 = 32u * U; i0 < len; i0 += 32u * U) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t idx = i0 + 32u * u + lane;
+                q[u] = idx < len ? __ldg(p + idx) : make_uint2(0u, 0u);
+            }
+            colw_batch(q, i0, len, lane, excl_bits, s_rec[wib], A);
+        }
+        unsigned long long hR_min = 0, hA_min = 0, hR_all = 0, hA_all = 0;
+        if (he > hb) {  // warp-uniform
+            for (uint32_t base = hb; base < he; base += 32u) {
+                if (base != hb && base + lane < he) {
+                    hcell = __ldg(hc_cell + base + lane);
+                    href = __ldg(hc_ref + base + lane);
+                    halt = __ldg(hc_alt + base + lane);
+                    hval = __ldg(hv_c + base + lane);
+                }
+                if (base + lane < he) {
+                    const bool ex = (__ldg(excl_bits + (hcell >> 5)) >> (hcell & 31u)) & 1u;
+                    A.s_min += ex ? hval : 0.0;
+                    A.s_maj += ex ? 0.0 : hval;
+                    hR_min += ex ? href : 0u;
+                    hA_min += ex ? halt : 0u;
+                    hR_all += href;
+                    hA_all += halt;
+                }
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                hR_min += __shfl_xor_sync(0xffffffffu, hR_min, off);
+                hA_min += __shfl_xor_sync(0xffffffffu, hA_min, off);
+                hR_all += __shfl_xor_sync(0xffffffffu, hR_all, off);
+                hA_all += __shfl_xor_sync(0xffffffffu, hA_all, off);
+            }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            A.s_min += __shfl_xor_sync(0xffffffffu, A.s_min, off);
+            A.s_maj += __shfl_xor_sync(0xffffffffu, A.s_maj, off);
+            A.c_min += __shfl_xor_sync(0xffffffffu, A.c_min, off);
+            A.r_min += __shfl_xor_sync(0xffffffffu, A.r_min, off);
+            A.a_min += __shfl_xor_sync(0xffffffffu, A.a_min, off);
+            A.r_all += __shfl_xor_sync(0xffffffffu, A.r_all, off);
+            A.a_all += __shfl_xor_sync(0xffffffffu, A.a_all, off);
+        }
+        bool filtered = false;
+        if (lane == 0) {
+            const double s_min = A.s_min, s_maj = A.s_maj;
+            const uint32_t c_min = A.c_min, c_maj = len - A.c_min;
+            const unsigned long long R_min = A.r_min + hR_min, A_min = A.a_min + hA_min,
+                                     R_maj = (A.r_all - A.r_min) + (hR_all - hR_min), A_maj = (A.a_all - A.a_min) + (hA_all - hA_min);
+            loc_ll[l] = on ? s_min : 0.0;
+            loc_ll[L + l] = on ? s_maj : 0.0;
+            loc_int[0 * L + l] = on ? c_min : 0;
+            loc_int[1 * L + l] = on ? c_maj : 0;
+            loc_int[2 * L + l] = on ? R_min : 0;
+            loc_int[3 * L + l] = on ? A_min : 0;
+            loc_int[4 * L + l] = on ? R_maj : 0;
+            loc_int[5 * L + l] = on ? A_maj : 0;
+            loc_int[6 * L + l] = R_min;  // init_alpha_betas subtracts every stored entry of an excluded cell (main.rs:603-608)
+            loc_int[7 * L + l] = A_min;
+            if (FUSE_FILTER) {  // main.rs:431-451 on this locus
+                const double per_cell = (on && c_min != 0) ? s_min / (double)c_min : 0.0;
+                if (per_cell < -80.0) {
+                    filtered = on;
+                    used[l] = 0;
+                    f_cnt += on ? 1u : 0u;
+                } else {
+                    u_cnt += on ? 1u : 0u;
+                }
+            }
+        }
+        if (FUSE_FILTER) {
+            // a locus switched off now stops counting toward loci_used_per_cell (main.rs:575) of the cells it covers
+            if (__shfl_sync(0xffffffffu, filtered ? 1 : 0, 0))
+                for (uint32_t i = lane; i < len; i += 32u) atomicSub(&n_used[p[i].x], 1u);
+        }
+        __syncwarp();  // s_rec[wib] is rewritten for the next column
+        if (ln >= n_loci) break;
+        l = ln;
+        ln = l2;
+        b0 = b1; e0 = e1; b1 = b2; e1 = e2;
+#pragma unroll
+        for (int u = 0; u < U; ++u) q[u] = qn[u];
+        recv = recn;
+        tp = tpn;
+    }
+    if (FUSE_FILTER && lane == 0) {
+        if (f_cnt) atomicAdd(&st->n_loci_filtered, (unsigned long long)f_cnt);
+        if (u_cnt) atomicAdd(&st->n_loci_in_use, (unsigned long long)u_cnt);
     }
 }
 

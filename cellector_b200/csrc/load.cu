@@ -154,6 +154,36 @@ __global__ void k_heavy_perm(const uint32_t* __restrict__ hcpos, const uint32_t*
     if (h < n_heavy) perm[h] = lower_bound_u32(hpos, n_heavy, (uint64_t)csc_src[hcpos[h]]);
 }
 
+__global__ void k_max_total(const unsigned long long* __restrict__ locus_tot, uint32_t n_loci, unsigned long long* __restrict__ out) {
+    unsigned long long m = 0;
+    for (uint32_t l = blockIdx.x * blockDim.x + threadIdx.x; l < n_loci; l += gridDim.x * blockDim.x) {
+        const unsigned long long t = locus_tot[2 * (size_t)l] + locus_tot[2 * (size_t)l + 1];
+        m = t > m ? t : m;
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        const unsigned long long o = __shfl_xor_sync(0xffffffffu, m, off);
+        m = o > m ? o : m;
+    }
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+}
+__global__ void k_lng_build(double* __restrict__ lng, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) lng[i] = i == 0 ? INFINITY : ln_gamma((double)i);
+}
+
+// the heavy lists once more in CSC order (the column pass reads them without the permutation hop) + the inverse map
+__global__ void k_heavy_csc(const uint32_t* __restrict__ perm, uint32_t n_heavy, const uint32_t* __restrict__ h_cell,
+                            const uint32_t* __restrict__ h_ref, const uint32_t* __restrict__ h_alt, uint32_t* __restrict__ hc_cell,
+                            uint32_t* __restrict__ hc_ref, uint32_t* __restrict__ hc_alt, uint32_t* __restrict__ h2c) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_heavy) return;
+    const uint32_t h = perm[j];
+    hc_cell[j] = h_cell[h];
+    hc_ref[j] = h_ref[h];
+    hc_alt[j] = h_alt[h];
+    h2c[h] = j;
+}
+
 int bits_for(uint64_t n) {
     int b = 1;
     while (b < 32 && (1ull << b) < n) ++b;
@@ -318,6 +348,25 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         c->launches += 2;
     }
     CLX_TRY(comm_allreduce_u64(c, c->locus_tot.p, 2 * (size_t)n_loci));
+    // ln_gamma memo over the integer arguments the EM pass can form: k + alpha, j + beta <= 2 * total + 2 and
+    // (a + alpha) + (r + beta) <= 2 * total + 2 for the deepest locus (capped; beyond the cap ln_gamma is direct)
+    {
+        DevBuf<unsigned long long> d_max;
+        CLX_CUDA(c, d_max.alloc(1));
+        CLX_CUDA(c, cudaMemsetAsync(d_max.p, 0, 8, s));
+        if (n_loci) {
+            k_max_total<<<grid_for(n_loci), TPB, 0, s>>>(c->locus_tot.p, n_loci, d_max.p);
+            c->launches++;
+        }
+        unsigned long long h_max = 0;
+        CLX_CUDA(c, cudaMemcpyAsync(&h_max, d_max.p, 8, cudaMemcpyDeviceToHost, s));
+        CLX_CUDA(c, cudaStreamSynchronize(s));
+        const unsigned long long want = 2 * h_max + 16, cap = 1ull << 22;  // at most 32 MB
+        c->lng_n = (uint32_t)(want < cap ? want : cap);
+        CLX_CUDA(c, c->lng.alloc(c->lng_n));
+        k_lng_build<<<(c->lng_n + TPB - 1) / TPB, TPB, 0, s>>>(c->lng.p, c->lng_n);
+        c->launches++;
+    }
 
     // ---- heavy side lists
     DevBuf<uint32_t> hpos, hcpos;
@@ -344,6 +393,11 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     CLX_CUDA(c, c->hv_ll.alloc(3 * (size_t)n_heavy));
     CLX_CUDA(c, c->hv_e.alloc(n_heavy));
     CLX_CUDA(c, hcpos.alloc(n_heavy));
+    CLX_CUDA(c, c->hc_cell.alloc(n_heavy));
+    CLX_CUDA(c, c->hc_ref.alloc(n_heavy));
+    CLX_CUDA(c, c->hc_alt.alloc(n_heavy));
+    CLX_CUDA(c, c->h2c.alloc(n_heavy));
+    CLX_CUDA(c, c->hv_c.alloc(n_heavy));
     if (n_heavy) {
         k_heavy_gather<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hpos.p, n_heavy, csr_src.p, c->csr.p, d_cell.p, d_ref.p,
                                                                d_alt.p, c->h_cell.p, c->h_locus.p, c->h_ref.p, c->h_alt.p);
@@ -353,7 +407,9 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         CLX_CUDA(c, tmp.alloc(tmp_bytes));
         CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, hcpos.p, n_sel.p, (int)nnz, f2, s));
         k_heavy_perm<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, csc_src.p, hpos.p, n_heavy, c->hc_perm.p);
-        c->launches += 4;
+        k_heavy_csc<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(c->hc_perm.p, n_heavy, c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hc_cell.p,
+                                                              c->hc_ref.p, c->hc_alt.p, c->h2c.p);
+        c->launches += 5;
     }
     // entries too deep for the batched heavy kernel get a CTA each (em_kernels.cuh: k_heavy_giant)
     c->n_giant = 0;

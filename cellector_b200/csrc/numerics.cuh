@@ -83,6 +83,13 @@ CLX_HD double ln_gamma(double x) {
     return log(s) + Lanczos::LN_2_SQRT_E_OVER_PI + (x - 0.5) * log((x - 0.5 + Lanczos::R) / Lanczos::E);
 }
 
+// ln_gamma of an integer-valued argument through the memo lng[i] = ln_gamma((double)i): the same double, bit for
+// bit (ln_gamma is a pure function of its argument); arguments beyond the memo are evaluated directly.
+CLX_HD double ln_gamma_int(double x, const double* __restrict__ lng, uint32_t lng_n) {
+    if (x < (double)lng_n) return lng[(uint32_t)x];
+    return ln_gamma(x);
+}
+
 // lnfact[i] = ln(i!) for i <= 170, computed on the host exactly like statrs (ln of the f64 product table).
 CLX_HD double ln_factorial(uint64_t n, const double* __restrict__ lnfact) {
     if (n <= 170) return lnfact[n];

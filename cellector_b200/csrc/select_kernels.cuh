@@ -53,10 +53,54 @@ __device__ __forceinline__ void finish_stats(const double* x, const SelectPlan& 
 // 8 bits per pass with all six ranks in flight (targets that still share a prefix share a histogram) and drops a
 // key as soon as it matches no target prefix, so later passes touch a handful of keys.  The same launch then
 // applies the exclusion rule (main.rs:330-335) to this rank's cells.
+// The few keys left after the radix passes are sorted in shared memory (bitonic network over SELECT_LIST_PAD
+// slots, pads = ~0) and target t is read at (start of its prefix group) + (its remaining rank): the keys of one
+// prefix group are contiguous once sorted.  Called by every thread of the CTA; results land in spre[].
+constexpr unsigned int SELECT_LIST_PAD = 256;
+__device__ __forceinline__ void select_from_list(unsigned long long* __restrict__ s_list, unsigned int nl, int hi_bit,
+                                                 unsigned long long* __restrict__ spre,
+                                                 const unsigned long long* __restrict__ srank) {
+    const unsigned int tid = threadIdx.x;
+    for (unsigned int i = tid; i < SELECT_LIST_PAD; i += blockDim.x)
+        if (i >= nl) s_list[i] = ~0ull;
+    __syncthreads();
+    for (unsigned int k = 2; k <= SELECT_LIST_PAD; k <<= 1)
+        for (unsigned int j = k >> 1; j > 0; j >>= 1) {
+            if (tid < SELECT_LIST_PAD) {
+                const unsigned int o = tid ^ j;
+                if (o > tid) {
+                    const unsigned long long a = s_list[tid], b = s_list[o];
+                    const bool up = (tid & k) == 0;
+                    if ((a > b) == up) {
+                        s_list[tid] = b;
+                        s_list[o] = a;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    unsigned long long res = 0ull;
+    if (tid < SELECT_TARGETS) {
+        const unsigned long long lo_key = hi_bit >= 64 ? 0ull : (spre[tid] << hi_bit);
+        unsigned int lo = 0, hi = nl;
+        while (lo < hi) {
+            const unsigned int mid = (lo + hi) >> 1;
+            if (s_list[mid] < lo_key) lo = mid + 1;
+            else hi = mid;
+        }
+        const unsigned long long at = (unsigned long long)lo + srank[tid];
+        res = s_list[at < SELECT_LIST_PAD ? at : SELECT_LIST_PAD - 1];
+    }
+    __syncthreads();
+    if (tid < SELECT_TARGETS) spre[tid] = res;
+    __syncthreads();
+}
+
 constexpr int SELECT_SMALL_THREADS = 1024;
 constexpr int SELECT_R = 16;
 constexpr unsigned int SELECT_RANK_CAP = 192;  // finish by direct ranking once this few keys are left
 static_assert(SELECT_SMALL_MAX == SELECT_SMALL_THREADS * SELECT_R, "keys per thread");
+static_assert(SELECT_RANK_CAP <= SELECT_LIST_PAD, "survivor list fits the sort network");
 __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_small(const double* __restrict__ vals, uint32_t n,
                                                                        SelectPlan plan, const IterParams* __restrict__ prm,
                                                                        DeviceStats* __restrict__ st,
@@ -69,7 +113,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_small(const dou
     __shared__ unsigned int scnt[SELECT_TARGETS], s_total, s_nlist;
     __shared__ int s_nlead, s_leadt[SELECT_TARGETS];
     __shared__ unsigned long long s_leadpre[SELECT_TARGETS], s_result[SELECT_TARGETS];
-    __shared__ unsigned long long s_list[SELECT_RANK_CAP];
+    __shared__ unsigned long long s_list[SELECT_LIST_PAD];
     __shared__ double sthr;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long key[SELECT_R];
@@ -232,25 +276,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_small(const dou
                 if ((valid >> j) & 1u) s_list[atomicAdd(&s_nlist, 1u)] = key[j];
         }
         __syncthreads();
-        if (warp < SELECT_TARGETS) {
-            const int t = warp;
-            const unsigned int nl = s_nlist;
-            const unsigned long long pre = spre[t], want = srank[t];
-            for (unsigned int i = lane; i < nl; i += 32) {
-                const unsigned long long ki = s_list[i];
-                if ((hi_bit >= 64 ? 0ull : (ki >> hi_bit)) != pre) continue;
-                unsigned long long before = 0;
-                for (unsigned int j = 0; j < nl; ++j) {
-                    const unsigned long long kj = s_list[j];
-                    if ((hi_bit >= 64 ? 0ull : (kj >> hi_bit)) != pre) continue;
-                    before += (kj < ki || (kj == ki && j < i)) ? 1ull : 0ull;
-                }
-                if (before == want) s_result[t] = ki;
-            }
-        }
-        __syncthreads();
-        if (tid < SELECT_TARGETS) spre[tid] = s_result[tid];
-        __syncthreads();
+        select_from_list(s_list, s_nlist, hi_bit, spre, srank);
     }
     if (tid == 0) {
         double x[SELECT_TARGETS];
@@ -305,7 +331,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
     __shared__ unsigned int scnt[SELECT_TARGETS], s_total;
     __shared__ int s_nlead, s_leadt[SELECT_TARGETS];
     __shared__ unsigned long long s_leadpre[SELECT_TARGETS], s_result[SELECT_TARGETS];
-    __shared__ unsigned long long s_list[SELECT_RANK_CAP];
+    __shared__ unsigned long long s_list[SELECT_LIST_PAD];
     __shared__ double sthr;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long* g_or = reinterpret_cast<unsigned long long*>(scratch + SELECT_COOP_HIST);
@@ -477,24 +503,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
         const unsigned int nl = min(__ldcg(g_nlist), SELECT_RANK_CAP);
         for (unsigned int i = tid; i < nl; i += SELECT_SMALL_THREADS) s_list[i] = __ldcg(&glist[i]);
         __syncthreads();
-        if (warp < SELECT_TARGETS) {
-            const int t = warp;
-            const unsigned long long pre = spre[t], want = srank[t];
-            for (unsigned int i = lane; i < nl; i += 32) {
-                const unsigned long long ki = s_list[i];
-                if ((hi_bit >= 64 ? 0ull : (ki >> hi_bit)) != pre) continue;
-                unsigned long long before = 0;
-                for (unsigned int j = 0; j < nl; ++j) {
-                    const unsigned long long kj = s_list[j];
-                    if ((hi_bit >= 64 ? 0ull : (kj >> hi_bit)) != pre) continue;
-                    before += (kj < ki || (kj == ki && j < i)) ? 1ull : 0ull;
-                }
-                if (before == want) s_result[t] = ki;
-            }
-        }
-        __syncthreads();
-        if (tid < SELECT_TARGETS) spre[tid] = s_result[tid];
-        __syncthreads();
+        select_from_list(s_list, nl, hi_bit, spre, srank);
     }
     if (tid == 0) {
         double x[SELECT_TARGETS];

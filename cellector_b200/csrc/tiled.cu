@@ -257,9 +257,14 @@ struct RunState {
 // One packet = n batches.  In a batch, lane l reads entry j at j * 32 + l (one conflict-free 64-byte warp load),
 // looks T and E up in the staged table tile and adds them to its run's sums, in file order; the last batch of a
 // group adds the run to the cell's accumulator (this warp owns the cell: plain read-modify-write).
+// Accumulator slot of a cell: the cells of one warp are cell_local = 32 q + w, and a group touches 32 of them at
+// once, so slot = w * Q + q puts them in neighbouring 16-byte slots (slot = cell_local would put all 32 in the
+// same banks: an 8-way conflict on every read-modify-write).
+__device__ __forceinline__ uint32_t acc_slot(uint32_t cell_local, uint32_t Q) { return (cell_local & 31u) * Q + (cell_local >> 5); }
+
 template <bool WITH_E>
 __device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ pk, const double* __restrict__ tab,
-                                             double2* __restrict__ acc, int lane, RunState& st) {
+                                             double2* __restrict__ acc, int lane, RunState& st, uint32_t Q) {
     const uint32_t nb = *reinterpret_cast<const uint32_t*>(pk);
     const unsigned char* p = pk + 16;
     for (uint32_t b = 0; b < nb; ++b) {
@@ -267,7 +272,8 @@ __device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ p
         const uint32_t m = hdr & 0xFFu;
         const uint16_t* e = reinterpret_cast<const uint16_t*>(p + 16);
         if (hdr & 0x100u) {  // first batch of a group: 32 cell ids
-            st.cell = e[lane];
+            const uint32_t c = e[lane];
+            st.cell = c == 0xFFFFu ? 0xFFFFu : acc_slot(c, Q);
             st.sT = 0.0;
             st.sE = 0.0;
             e += 32;
@@ -283,7 +289,7 @@ __device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ p
         st.sT = sT;
         st.sE = sE;
 #ifdef CLX_TILED_DEBUG
-        if (nb > 64 || m == 0 || m > BATCH_ITERS || ((hdr & 0x200u) && st.cell != 0xFFFFu && st.cell >= NB_MAX))
+        if (nb > 64 || m == 0 || m > BATCH_ITERS || ((hdr & 0x200u) && st.cell != 0xFFFFu && st.cell >= 32u * Q))
             printf("bad batch: blk %d w %d lane %d nb %u b %u hdr %x cell %u\n", blockIdx.x, threadIdx.x >> 5, lane, nb, b, hdr, st.cell);
 #endif
         if ((hdr & 0x200u) && st.cell != 0xFFFFu) {  // last batch of the group
@@ -299,8 +305,9 @@ __device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ p
 template <bool WITH_E>
 __global__ void __launch_bounds__(TL_WARPS * 32, 1)
     k_score_tiled(const uint32_t* __restrict__ stream, const uint32_t* __restrict__ pk_q, const uint32_t* __restrict__ pk_base,
-                  const uint32_t* __restrict__ items, uint32_t n_items, const double* __restrict__ tab13, uint32_t nT,
-                  uint32_t NB, double* __restrict__ part) {
+                  const uint32_t* __restrict__ items, uint32_t n_items, const uint32_t* __restrict__ order,
+                  uint32_t* __restrict__ counter, const double* __restrict__ tab13, uint32_t nT, uint32_t NB,
+                  double* __restrict__ part) {
     extern __shared__ __align__(128) unsigned char smem[];
     double2* acc = reinterpret_cast<double2*>(smem + 2 * TL_TAB_BUF);
     unsigned char* ring = smem + 2 * TL_TAB_BUF + TL_ACC_BYTES;
@@ -308,6 +315,7 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
     uint64_t* ring_full = tab_full + 2;
     unsigned int* tab_done = reinterpret_cast<unsigned int*>(ring_full + TL_WARPS * RING_STAGES);  // [2] warps done with a buffer
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t Q = (NB + 31u) / 32u;
     if (tid == 0) {
         mbar_init(&tab_full[0], 1);
         mbar_init(&tab_full[1], 1);
@@ -329,10 +337,18 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
     st.sT = 0.0;
     st.sE = 0.0;
     st.cell = 0xFFFFu;
-    for (uint32_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    __shared__ uint32_t s_next;
+    for (;;) {
+        // work queue: items are handed out largest first (the last statement of the body is a CTA barrier, so the slot
+        // is free to be rewritten here)
+        if (tid == 0) s_next = atomicAdd(counter, 1u);
+        __syncthreads();
+        const uint32_t qk = s_next;
+        if (qk >= n_items) break;
+        const uint32_t item = order[qk];
         const uint32_t cb = items[4 * item], t0 = items[4 * item + 1], ntile = items[4 * item + 2] - t0;
         const size_t sub0 = ((size_t)cb * nT + t0) * TL_WARPS + w;  // this warp's sub-unit of the item's first tile
-        for (uint32_t i = tid; i < NB; i += blockDim.x) acc[i] = make_double2(0.0, 0.0);
+        for (uint32_t i = tid; i < 32u * Q; i += blockDim.x) acc[i] = make_double2(0.0, 0.0);
         if (tid == 0) {
             for (uint32_t k = 0; k < 2 && k < ntile; ++k) {
                 const uint32_t g = g_tile + k;
@@ -382,7 +398,7 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
             for (uint32_t p = pk_base[sub0 + (size_t)k * TL_WARPS]; p < p_end; ++p) {
                 const uint32_t s = cons_c % RING_STAGES;
                 mbar_wait(&my_bar[s], (cons_c / RING_STAGES) & 1u);
-                tiled_packet<WITH_E>(my_ring + (size_t)s * STAGE_BYTES, tab, acc, lane, st);
+                tiled_packet<WITH_E>(my_ring + (size_t)s * STAGE_BYTES, tab, acc, lane, st, Q);
                 __syncwarp();
                 ++cons_c;
                 issue_one();  // refill the stage just drained
@@ -406,7 +422,7 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
         g_tile += ntile;
         __syncthreads();  // every warp has added its last run
         double2* dst = reinterpret_cast<double2*>(part) + (size_t)item * NB;
-        for (uint32_t i = tid; i < NB; i += blockDim.x) dst[i] = acc[i];
+        for (uint32_t i = tid; i < NB; i += blockDim.x) dst[i] = acc[acc_slot(i, Q)];
         __syncthreads();
     }
 }
@@ -421,7 +437,9 @@ __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__
                                                       const double* __restrict__ hv_ll, const double* __restrict__ hv_e,
                                                       const uint32_t* __restrict__ n_used, double* __restrict__ ll,
                                                       double* __restrict__ ell, uint32_t* __restrict__ nloci,
-                                                      double* __restrict__ norm, unsigned int* __restrict__ nan_flag) {
+                                                      double* __restrict__ norm, unsigned int* __restrict__ nan_flag,
+                                                      uint32_t* __restrict__ queue_counter) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) *queue_counter = 0u;  // re-arm the work queue of k_score_tiled
     // lanes 0..3 of a warp take cells c0..c0+3 for sub 0, lanes 4..7 the same cells for sub 1, ...: partial loads of one
     // sub are 4 consecutive double2 (64 B)
     const uint32_t warp_cell0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / FIN_LANES);
@@ -478,10 +496,12 @@ int score_tiled(clx_ctx* c, int table, bool with_e, bool em_outputs) {
         const unsigned grid = std::min<unsigned>(c->tl_n_items, (unsigned)c->sm_count);
         if (with_e)
             k_score_tiled<true><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_q.p, c->tl_pk_base.p, c->tl_items.p,
-                                                                    c->tl_n_items, tab, c->tl_nT, c->tl_NB, c->tl_part.p);
+                                                                    c->tl_n_items, c->tl_order.p, c->tl_counter.p, tab, c->tl_nT, c->tl_NB,
+                                                                    c->tl_part.p);
         else
             k_score_tiled<false><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_q.p, c->tl_pk_base.p, c->tl_items.p,
-                                                                     c->tl_n_items, tab, c->tl_nT, c->tl_NB, c->tl_part.p);
+                                                                     c->tl_n_items, c->tl_order.p, c->tl_counter.p, tab, c->tl_nT, c->tl_NB,
+                                                                     c->tl_part.p);
         c->launches++;
         CLX_DEBUG_SYNC(c, "k_score_tiled");
     }
@@ -489,10 +509,11 @@ int score_tiled(clx_ctx* c, int table, bool with_e, bool em_outputs) {
     const unsigned fgrid = (unsigned)(((uint64_t)N * FIN_LANES + 255) / 256);
     if (em_outputs)
         k_score_finish<true><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, hv, c->hv_e.p,
-                                                  c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag);
+                                                  c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag,
+                                                  c->tl_counter.p);
     else
         k_score_finish<false><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, hv, nullptr, nullptr,
-                                                   c->ll.p + (size_t)table * N, nullptr, nullptr, nullptr, nullptr);
+                                                   c->ll.p + (size_t)table * N, nullptr, nullptr, nullptr, nullptr, c->tl_counter.p);
     c->launches++;
     return CLX_OK;
 }
@@ -509,7 +530,9 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     c->tl_nT = L ? (L + TILE_L - 1) / TILE_L : 1;
     {
         uint32_t pc = N ? (N + NB_MAX - 1) / NB_MAX : 1;
-        const uint32_t want = (2u * (uint32_t)c->sm_count + c->tl_nT - 1) / c->tl_nT;
+        // one work item per SM, each at least ~4 consecutive tiles long (table copies pipeline inside an item, and the
+        // cut points of an item are whole tiles: short items balance badly)
+        const uint32_t want = (4u * (uint32_t)c->sm_count + c->tl_nT - 1) / c->tl_nT;
         const uint32_t pc_cap = N ? std::max<uint32_t>(1u, N / NB_MIN) : 1u;
         pc = std::max(pc, std::min(want, pc_cap));
         const char* env = getenv("CLX_TILED_PC");
@@ -633,11 +656,14 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     CLX_CUDA(c, cudaMemcpyAsync(c->tl_pk_q.p + n_packets, &total_q, 4, cudaMemcpyHostToDevice, s));
     CLX_CUDA(c, cudaStreamSynchronize(s));
 
-    // ---- work items: every cell block gets a share of (2 x SMs) items proportional to its entries; its tiles are cut
+    const char* env_it = getenv("CLX_TILED_ITEMS_PER_SM");
+    const int env_items = env_it && *env_it ? std::max(1, atoi(env_it)) : 2;
+    // ---- work items: every cell block gets a share of (items per SM x SMs) items proportional to its entries; its tiles are cut
     //      into that many consecutive ranges of about equal entry counts
     {
         std::vector<uint32_t> items, cb_item;
-        const uint64_t total_items = std::max<uint64_t>(1, 2ull * (uint64_t)c->sm_count);
+        std::vector<unsigned long long> item_entries;
+        const uint64_t total_items = std::max<uint64_t>(1, (uint64_t)env_items * (uint64_t)c->sm_count);
         for (uint32_t cb = 0; cb < c->tl_Pc; ++cb) {
             cb_item.push_back((uint32_t)(items.size() / 4));
             const unsigned long long* ue = h_unit.data() + (size_t)cb * c->tl_nT;
@@ -662,6 +688,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
                     items.push_back(t0);
                     items.push_back(t1);
                     items.push_back(0);
+                    item_entries.push_back(in_range);
                 }
                 t0 = t1;
             }
@@ -670,6 +697,13 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         c->tl_n_items = (uint32_t)(items.size() / 4);
         CLX_CUDA(c, c->tl_items.alloc(items.size() + 4));
         CLX_CUDA(c, c->tl_cb_item.alloc(cb_item.size()));
+        std::vector<uint32_t> order(c->tl_n_items);
+        for (uint32_t i = 0; i < c->tl_n_items; ++i) order[i] = i;
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_entries[a] > item_entries[b]; });
+        CLX_CUDA(c, c->tl_order.alloc(order.size() + 1));
+        CLX_CUDA(c, c->tl_counter.alloc(1));
+        CLX_CUDA(c, cudaMemsetAsync(c->tl_counter.p, 0, 4, s));
+        if (!order.empty()) CLX_CUDA(c, cudaMemcpyAsync(c->tl_order.p, order.data(), order.size() * 4, cudaMemcpyHostToDevice, s));
         if (!items.empty())
             CLX_CUDA(c, cudaMemcpyAsync(c->tl_items.p, items.data(), items.size() * 4, cudaMemcpyHostToDevice, s));
         CLX_CUDA(c, cudaMemcpyAsync(c->tl_cb_item.p, cb_item.data(), cb_item.size() * 4, cudaMemcpyHostToDevice, s));

@@ -143,6 +143,9 @@ void clx_free_pinned(void* p);
 
 /* Profiling helpers (not part of the reference surface). */
 int clx_get_phase_ms(clx_ctx* ctx, int phase, double* total_ms, uint64_t* launches);
+/* Switch CLX_FLAG_PROFILE on or off after clx_create (the phase events are extra nodes of the iteration graph and
+ * cost tens of microseconds per iteration: a throughput run keeps them off, a per-kernel timing run turns them on). */
+int clx_set_profiling(clx_ctx* ctx, int on);
 int clx_reset_phase_ms(clx_ctx* ctx);
 void* clx_get_stream(clx_ctx* ctx); /* cudaStream_t all kernels are launched on */
 /* Algorithmic bytes one launch of the scoring kernel must move (roofline accounting). */
