@@ -82,6 +82,8 @@ struct clx_ctx {
     int device = 0;
     unsigned flags = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;               // side branch of an iteration (heavy entries next to the table build)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int sm_count = 148;
     uint64_t launches = 0;
     uint64_t score_bytes = 0;  // algorithmic bytes of one launch of the scoring kernel

@@ -26,8 +26,11 @@ int env_int(const char* name, int dflt) {
 int pick_group(double avg_len) {
     // lanes per row/column: every lane should have about one unrolled batch (SCORE_UNROLL 128-bit loads of two
     // entries) of work, so that all of a row's loads are in flight at once
+    // measured on B200 (column pass, C2 and a C3 shard): 4 lanes per ~100-entry column beat 2, 8, 16 and 32 — the
+    // per-column tail (heavy entries, ten scalar stores, the -80 rule) runs once per lane GROUP, so narrow groups keep
+    // more columns' tails in flight per warp; widen only when a lane would get more than ~4 unrolled batches
     int g = 4;
-    while (g < 32 && avg_len > 2.0 * SCORE_UNROLL * g) g <<= 1;
+    while (g < 32 && avg_len > 8.0 * SCORE_UNROLL * g) g <<= 1;
     return g;
 }
 
@@ -78,6 +81,8 @@ void launch_columns(clx_ctx* c, int G) {
         c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_perm.p,            \
         c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hv_ll.p, c->loc_ll.p, c->loc_int.p, c->n_used.p, c->d_stats.p)
     switch (G) {
+        case 1: CLX_COLS(1); break;
+        case 2: CLX_COLS(2); break;
         case 4: CLX_COLS(4); break;
         case 8: CLX_COLS(8); break;
         case 16: CLX_COLS(16); break;
@@ -124,15 +129,18 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
     const SelectPlan plan = make_plan(n_real);
     cudaStream_t s = c->stream;
     const uint32_t N = c->n_cells;
-    static const int mode = env_int("CLX_SELECT_MODE", 0);  // tests: 1 forces the cooperative kernel, 2 the multi-launch path
-    if (mode == 0 && n_vals <= SELECT_SMALL_MAX && vals == c->norm.p) {  // one GPU, small: one CTA, exclusion fused
+    static const int mode = env_int("CLX_SELECT_MODE", 0);  // 0/1 cooperative kernel, 2 forces the multi-launch path, 3 the one-CTA kernel
+    if (mode == 3 && n_vals <= SELECT_SMALL_MAX && vals == c->norm.p) {  // one CTA, exclusion fused (kept for comparison)
         k_select_small<<<1, SELECT_SMALL_THREADS, 0, s>>>(vals, (uint32_t)n_vals, plan, c->d_params.p,
                                                                          c->d_stats.p, c->norm.p, N, c->excl_bits.p);
         c->launches++;
         return CLX_OK;
     }
-    const uint64_t per_cta = (uint64_t)SELECT_SMALL_THREADS * SELECT_R;
-    if (mode != 2 && n_vals <= per_cta * (uint64_t)c->sm_count) {  // cooperative grid, keys in registers, one launch
+    // cooperative grid, keys in registers, one launch: as few keys per thread as one CTA per SM allows (1, 4 or 16)
+    const uint64_t cap1 = (uint64_t)SELECT_SMALL_THREADS * (uint64_t)c->sm_count;
+    if (mode != 2 && n_vals <= 16 * cap1) {
+        const int R = n_vals <= cap1 ? 1 : (n_vals <= 4 * cap1 ? 4 : 16);
+        const uint64_t per_cta = (uint64_t)SELECT_SMALL_THREADS * R;
         CLX_CUDA(c, cudaMemsetAsync(c->sel_hist.p, 0, c->sel_hist.bytes(), s));
         const unsigned grid = (unsigned)std::max<uint64_t>(1, (n_vals + per_cta - 1) / per_cta);
         const double* norm_local = c->norm.p;
@@ -145,7 +153,8 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
         SelectPlan pl = plan;
         void* args[] = {(void*)&vals, (void*)&n_vals, (void*)&pl, (void*)&prm, (void*)&st, (void*)&scratch,
                         (void*)&glist, (void*)&norm_local, (void*)&n_local, (void*)&bits};
-        CLX_CUDA(c, cudaLaunchCooperativeKernel((const void*)k_select_coop, dim3(grid), dim3(SELECT_SMALL_THREADS), args, 0, s));
+        const void* fn = R == 1 ? (const void*)k_select_coop<1> : (R == 4 ? (const void*)k_select_coop<4> : (const void*)k_select_coop<16>);
+        CLX_CUDA(c, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SELECT_SMALL_THREADS), args, 0, s));
         c->launches++;
         return CLX_OK;
     }
@@ -240,34 +249,49 @@ int enqueue_iteration(clx_ctx* c) {
     const int with_e = (c->flags & CLX_FLAG_NO_EXPECTED) ? 0 : 1;
     CLX_CUDA(c, cudaMemcpyAsync(c->d_params.p, c->h_params, sizeof(IterParams), cudaMemcpyHostToDevice, s));
 
-    // 1. alpha/beta + memo tables from the CURRENT excluded set (main.rs:309); also clears d_stats
+    // 1. + 2a. alpha/beta + memo tables from the CURRENT excluded set (main.rs:309; also clears d_stats) and, as a
+    //    parallel branch on the side stream, the direct evaluation of the heavy entries (it derives alpha/beta from
+    //    the same counts).  With phase profiling on the two run back to back so that their event pairs mean something.
+    const bool fork = c->n_heavy != 0 && !(c->flags & CLX_FLAG_PROFILE);
+    cudaStream_t hs = fork ? c->stream2 : s;
+    const EmCounts cnts{c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, c->loci_used.p, c->lng.p, c->lng_n};
+    if (fork) {
+        CLX_CUDA(c, cudaEventRecord(c->ev_fork, s));
+        CLX_CUDA(c, cudaStreamWaitEvent(hs, c->ev_fork, 0));
+    }
+    auto heavy = [&]() -> int {
+        if (!c->n_heavy) return CLX_OK;
+        k_heavy_em<<<(unsigned)((c->n_heavy + HEAVY_HB - 1) / HEAVY_HB), TPB, 0, hs>>>(
+            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, c->h2c.p,
+            c->hv_c.p);
+        c->launches++;
+        if (c->n_giant) {
+            k_heavy_giant<<<c->n_giant, TPB, 0, hs>>>(c->giant_idx.p, c->n_giant, c->h_locus.p, c->h_ref.p, c->h_alt.p, cnts,
+                                                      c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, c->h2c.p, c->hv_c.p);
+            c->launches++;
+        }
+        return CLX_OK;
+    };
+    if (fork) {
+        CLX_TRY(heavy());
+        CLX_CUDA(c, cudaEventRecord(c->ev_join, hs));
+    }
     phase_begin(c, CLX_PHASE_TABLES);
     if (L) {
-        k_tables<0><<<(L + TAB_LPB - 1) / TAB_LPB, TPB, 0, s>>>(
-            c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), 0.0, 0.0, with_e,
-            c->loci_used.p, c->tab.p, c->tiled_ready ? c->tab13.p : nullptr, c->tl_nT * TILE_L, c->d_stats.p, c->lng.p, c->lng_n);
+        k_tables_em<<<(unsigned)((3ull * L + TPB - 1) / TPB), TPB, 0, s>>>(cnts, L, make_lbc(c), with_e, c->tab.p,
+                                                                           c->tiled_ready ? c->tab13.p : nullptr, c->d_stats.p);
         c->launches++;
     } else {
         CLX_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, sizeof(DeviceStats), s));
     }
     phase_end(c, CLX_PHASE_TABLES);
     CLX_DEBUG_SYNC(c, "k_tables");
-
-    // 2. heavy entries, then the per-cell scoring pass (main.rs:312)
     phase_begin(c, CLX_PHASE_HEAVY);
-    if (c->n_heavy) {
-        k_heavy_em<<<(unsigned)((c->n_heavy + HEAVY_HB - 1) / HEAVY_HB), TPB, 0, s>>>(
-            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, c->tab.p, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p,
-            c->lng.p, c->lng_n, c->h2c.p, c->hv_c.p);
-        c->launches++;
-        if (c->n_giant) {
-            k_heavy_giant<<<c->n_giant, TPB, 0, s>>>(c->giant_idx.p, c->n_giant, c->h_locus.p, c->h_ref.p, c->h_alt.p, c->tab.p,
-                                                     c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, c->h2c.p, c->hv_c.p);
-            c->launches++;
-        }
-    }
+    if (fork) CLX_CUDA(c, cudaStreamWaitEvent(s, c->ev_join, 0));
+    else CLX_TRY(heavy());
     phase_end(c, CLX_PHASE_HEAVY);
     CLX_DEBUG_SYNC(c, "k_heavy");
+    // 2b. the per-cell scoring pass (main.rs:312)
     phase_begin(c, CLX_PHASE_SCORE);
     if (use_tiled(c)) {
         CLX_TRY(score_tiled(c, 0, with_e != 0, true));

@@ -168,177 +168,189 @@ __global__ void __launch_bounds__(256) k_tables(const unsigned long long* __rest
 // ------------------------------------------------------------------------------------------------
 // Heavy entries (total > K_LIGHT): direct evaluation with the same expressions (stats.rs:41-53, 8-22).
 //
-// EM pass (k_heavy_em): a CTA takes HEAVY_HB consecutive entries.  An entry of total n needs
-//   ln_gamma(k + alpha), k = 0..n     ln_gamma(j + beta), j = 0..n     ln_gamma((a + alpha) + (r + beta))
-// (alpha, beta are integer-valued in the EM pass, so the third argument is the same double for every split k of n,
-// and pmf(k = alt) is the entry's own log_pmf).  These 2(n+1)+1 evaluations form a flat task list over the CTA —
-// all lanes busy — with results in shared memory; then ll_k = ln C(n,k) + (lga[k] + lgb[n-k] - lgab) - den, and the
-// expected-log-likelihood chain runs left to right per entry like stats.rs:17-22 (entries with n > HEAVY_CHAIN_MAX
-// use a warp-wide max/sum logsumexp instead: same value to ~1e-16 relative, diagnostic column only).
-// Entries with n > HEAVY_GIANT are left to k_heavy_giant (one CTA each).
-constexpr int HEAVY_HB = 64;
-constexpr int HEAVY_CAP = 2560;        // ln_gamma results per round (20 KB) + as many pmf slots
-constexpr uint32_t HEAVY_GIANT = HEAVY_GIANT_TOTAL;  // 2(n+1)+1 <= HEAVY_CAP
-static_assert(2 * (HEAVY_GIANT_TOTAL + 1) + 1 <= HEAVY_CAP, "a non-giant entry must fit one round");
-constexpr uint32_t HEAVY_CHAIN_MAX = 32;
-
-__device__ __forceinline__ double heavy_ll_k(uint64_t n, uint64_t k, const double* __restrict__ lga,
-                                             const double* __restrict__ lgb, double lgab, double den,
-                                             const double* __restrict__ lnfact) {
-    const double num = lga[k] + lgb[n - k] - lgab;
-    return ln_binomial(n, k, lnfact) + num - den;
+// EM pass (k_heavy_em): alpha, beta are integer-valued, so every ln_gamma argument is an integer and comes from the
+// lng memo (numerics.cuh ln_gamma_int: bit-identical to the Lanczos series), and the third argument
+// (a + alpha) + (r + beta) is the same double for every split k of n.  One thread per entry for n <= HEAVY_CHAIN_MAX:
+//   ll_k = ln C(n,k) + (lnG(k + alpha) + lnG(n - k + beta) - lnG(n + alpha + beta)) - den,   own log_pmf = ll_alt,
+// and the expected-log-likelihood chain runs left to right like stats.rs:17-22.  Deeper entries are taken by the
+// whole warp, one after the other, with a max / sum logsumexp over k (same value to ~1e-16 relative; diagnostic
+// column only).  Entries with n > HEAVY_GIANT are left to k_heavy_giant (one CTA each).
+// alpha, beta and ln B(alpha, beta) of the EM pass straight from the counts (same expressions as k_tables<0>), so the
+// heavy kernels do not wait for the table build: the two run as parallel branches of the iteration graph.
+struct EmCounts {
+    const unsigned long long* tot;          // [2L] (ref, alt) totals
+    const unsigned long long* raw_min_ref;  // [L]
+    const unsigned long long* raw_min_alt;  // [L]
+    const uint8_t* used;                    // [L]
+    const double* lng;
+    uint32_t lng_n;
+};
+__device__ __forceinline__ void em_alpha_beta(const EmCounts& k, uint32_t l, double* alpha, double* beta, double* den) {
+    const double a = (double)k.tot[2 * (size_t)l + 1] + 1.0 - (double)k.raw_min_alt[l];
+    const double b = (double)k.tot[2 * (size_t)l] + 1.0 - (double)k.raw_min_ref[l];
+    *alpha = a;
+    *beta = b;
+    if (k.used[l] != 0) *den = ln_gamma_int(0.0 + a, k.lng, k.lng_n) + ln_gamma_int(0.0 + b, k.lng, k.lng_n) - ln_gamma_int(a + b, k.lng, k.lng_n);
+    else *den = quiet_nan();  // switched off by the -80 rule: contributes nothing
 }
 
-__global__ void __launch_bounds__(256) k_heavy_em(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
-                                                  const uint32_t* __restrict__ h_alt, uint32_t n_heavy,
-                                                  const double* __restrict__ tab, const double* __restrict__ lnfact,
-                                                  int with_expected, double* __restrict__ hv_ll, double* __restrict__ hv_e,
-                                                  const double* __restrict__ lng, uint32_t lng_n,
-                                                  const uint32_t* __restrict__ h2c, double* __restrict__ hv_c) {
-    __shared__ double s_g[HEAVY_CAP];
-    __shared__ double s_ll[HEAVY_CAP];  // pmf k of the entry whose tasks start at g0 sits at s_ll[g0 + k]
-    __shared__ double s_alpha[HEAVY_HB], s_beta[HEAVY_HB], s_den[HEAVY_HB];
-    __shared__ uint32_t s_n[HEAVY_HB], s_a[HEAVY_HB], s_off[HEAVY_HB + 1];
-    __shared__ int s_range[2];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t h0 = blockIdx.x * HEAVY_HB;
-    const uint32_t n_here = n_heavy - h0 < (uint32_t)HEAVY_HB ? n_heavy - h0 : (uint32_t)HEAVY_HB;
-    if (tid < HEAVY_HB) {
-        uint32_t ntask = 0, n = 0, a = 0;
-        double alpha = 1.0, beta = 1.0, den = 0.0;
-        if ((uint32_t)tid < n_here) {
-            const uint32_t h = h0 + tid;
-            const double* rec = tab + (size_t)h_locus[h] * TAB_STRIDE;
-            a = h_alt[h];
-            const uint64_t nn = (uint64_t)a + h_ref[h];
-            alpha = rec[TAB_ALPHA];
-            beta = rec[TAB_BETA];
-            den = rec[TAB_DEN];
-            const bool on = den == den;  // NaN den marks a locus that is switched off: contributes nothing
-            if (!on) {
-                hv_ll[h] = 0.0;
-                hv_e[h] = 0.0;
-                hv_c[h2c[h]] = 0.0;
-            } else if (nn <= HEAVY_GIANT) {
-                n = (uint32_t)nn;
-                ntask = with_expected ? 2 * (n + 1) + 1 : 3;
-            }
-        }
-        s_alpha[tid] = alpha; s_beta[tid] = beta; s_den[tid] = den;
-        s_n[tid] = n; s_a[tid] = a;
-        s_off[tid + 1] = ntask;
-    }
-    if (tid == 0) s_off[0] = 0;
-    __syncthreads();
-    if (tid == 0) {
-        for (int i = 0; i < HEAVY_HB; ++i) s_off[i + 1] += s_off[i];
-        s_range[0] = 0;
-    }
-    __syncthreads();
-    for (;;) {
-        const int e0 = s_range[0];
-        if (e0 >= (int)n_here) break;
-        __syncthreads();
-        if (tid == 0) {  // as many consecutive entries as fit in the result buffer
-            int e1 = e0 + 1;
-            while (e1 < (int)n_here && s_off[e1 + 1] - s_off[e0] <= (uint32_t)HEAVY_CAP) ++e1;
-            s_range[1] = e1;
-        }
-        __syncthreads();
-        const int e1 = s_range[1];
-        const uint32_t base = s_off[e0], total = s_off[e1] - base;
-        // phase 1: flat ln_gamma tasks
-        for (uint32_t task = tid; task < total; task += blockDim.x) {
-            int lo = e0, hi = e1 - 1;  // entry e with s_off[e] <= base + task < s_off[e + 1]
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (s_off[mid] <= base + task) lo = mid;
-                else hi = mid - 1;
-            }
-            const uint32_t j = base + task - s_off[lo], n = s_n[lo], a = s_a[lo];
-            const double alpha = s_alpha[lo], beta = s_beta[lo];
-            double x;
-            if (with_expected) {
-                if (j <= n) x = (double)j + alpha;
-                else if (j <= 2 * n + 1) x = (double)(j - n - 1) + beta;
-                else x = ((double)a + alpha) + ((double)(n - a) + beta);
-            } else {
-                x = j == 0 ? (double)a + alpha : (j == 1 ? (double)(n - a) + beta : ((double)a + alpha) + ((double)(n - a) + beta));
-            }
-            s_g[task] = ln_gamma_int(x, lng, lng_n);
-        }
-        __syncthreads();
-        if (with_expected) {
-            // phase 2a: ll_k for every (entry, k)
-            for (uint32_t task = tid; task < total; task += blockDim.x) {
-                int lo = e0, hi = e1 - 1;
-                while (lo < hi) {
-                    const int mid = (lo + hi + 1) >> 1;
-                    if (s_off[mid] <= base + task) lo = mid;
-                    else hi = mid - 1;
-                }
-                const uint32_t j = base + task - s_off[lo], n = s_n[lo];
-                if (j > n) continue;
-                const uint32_t g0 = s_off[lo] - base;
-                s_ll[g0 + j] = heavy_ll_k(n, j, s_g + g0, s_g + g0 + n + 1, s_g[g0 + 2 * n + 2], s_den[lo], lnfact);
-            }
-            __syncthreads();
-            // phase 2b: per entry, own log_pmf = ll_{alt}; chain over k
-            for (int e = e0 + tid; e < e1; e += blockDim.x) {
-                const uint32_t n = s_n[e];
-                if (s_off[e + 1] == s_off[e]) continue;  // switched off or giant
-                const uint32_t p0 = s_off[e] - base;
-                hv_ll[h0 + e] = s_ll[p0 + s_a[e]];
-                hv_c[h2c[h0 + e]] = s_ll[p0 + s_a[e]];
-                if (n <= HEAVY_CHAIN_MAX) {
-                    double ex = 2.0 * s_ll[p0];
-                    for (uint32_t k = 1; k <= n; ++k) ex = logsumexp2(ex, 2.0 * s_ll[p0 + k]);
-                    hv_e[h0 + e] = ex;
-                }
-            }
-            // deep entries: one warp each, max / sum form of the same logsumexp
-            for (int e = e0 + warp; e < e1; e += (int)(blockDim.x >> 5)) {
-                const uint32_t n = s_n[e];
-                if (s_off[e + 1] == s_off[e] || n <= HEAVY_CHAIN_MAX) continue;
-                const uint32_t p0 = s_off[e] - base;
-                double m = -INFINITY;
-                for (uint32_t k = lane; k <= n; k += 32) m = fmax(m, 2.0 * s_ll[p0 + k]);
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, off));
-                double sum = 0.0;
-                for (uint32_t k = lane; k <= n; k += 32) sum += exp(2.0 * s_ll[p0 + k] - m);
-#pragma unroll
-                for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
-                if (lane == 0) hv_e[h0 + e] = m + log(sum);
-            }
+constexpr int HEAVY_HB = 256;           // entries per CTA (one thread each)
+constexpr uint32_t HEAVY_GIANT = HEAVY_GIANT_TOTAL;
+constexpr uint32_t HEAVY_CHAIN_MAX = 32;
+
+__device__ __forceinline__ double ln_factorial_int(uint64_t n, const double* __restrict__ lnfact, const double* __restrict__ lng,
+                                                   uint32_t lng_n) {
+    return n <= 170 ? lnfact[n] : ln_gamma_int((double)n + 1.0, lng, lng_n);  // statrs ln_factorial
+}
+__device__ __forceinline__ double ln_binomial_int(uint64_t n, uint64_t k, const double* __restrict__ lnfact,
+                                                  const double* __restrict__ lng, uint32_t lng_n) {
+    return ln_factorial_int(n, lnfact, lng, lng_n) - ln_factorial_int(k, lnfact, lng, lng_n) - ln_factorial_int(n - k, lnfact, lng, lng_n);
+}
+// ll_k of stats.rs:12-16 for an entry of total n at a locus with integer-valued (alpha, beta)
+static __device__ __noinline__ double heavy_ll_k(uint64_t n, uint64_t k, double alpha, double beta, double lgab, double den,
+                                             const double* __restrict__ lnfact, const double* __restrict__ lng, uint32_t lng_n) {
+    const double num = ln_gamma_int((double)k + alpha, lng, lng_n) + ln_gamma_int((double)(n - k) + beta, lng, lng_n) - lgab;
+    return ln_binomial_int(n, k, lnfact, lng, lng_n) + num - den;
+}
+
+__global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
+                                                       const uint32_t* __restrict__ h_alt, uint32_t n_heavy, EmCounts cnts,
+                                                       const double* __restrict__ lnfact, int with_expected,
+                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e,
+                                                       const uint32_t* __restrict__ h2c, double* __restrict__ hv_c) {
+    const double* __restrict__ lng = cnts.lng;
+    const uint32_t lng_n = cnts.lng_n;
+    const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31u;
+    const bool live = h < n_heavy;
+    uint64_t a = 0, n = 0;
+    double alpha = 1.0, beta = 1.0, den = 0.0, lgab = 0.0;
+    bool on = false;
+    if (live) {
+        a = h_alt[h];
+        n = a + (uint64_t)h_ref[h];
+        em_alpha_beta(cnts, h_locus[h], &alpha, &beta, &den);
+        on = den == den;  // NaN den marks a locus that is switched off: contributes nothing
+        if (!on) {
+            hv_ll[h] = 0.0;
+            hv_e[h] = 0.0;
+            hv_c[h2c[h]] = 0.0;
         } else {
-            for (int e = e0 + tid; e < e1; e += blockDim.x) {
-                if (s_off[e + 1] == s_off[e]) continue;
-                const uint32_t g0 = s_off[e] - base, n = s_n[e], a = s_a[e];
-                const double num = s_g[g0] + s_g[g0 + 1] - s_g[g0 + 2];
-                const double v = ln_binomial(n, a, lnfact) + num - s_den[e];
-                hv_ll[h0 + e] = v;
-                hv_c[h2c[h0 + e]] = v;
-                hv_e[h0 + e] = 0.0;
-            }
+            lgab = ln_gamma_int(((double)a + alpha) + ((double)(n - a) + beta), lng, lng_n);
         }
-        __syncthreads();
-        if (tid == 0) s_range[0] = e1;
-        __syncthreads();
     }
+    if (live && on && n <= HEAVY_CHAIN_MAX) {
+        const double own = heavy_ll_k(n, a, alpha, beta, lgab, den, lnfact, lng, lng_n);
+        double ex = 0.0;
+        if (with_expected) {
+            ex = 2.0 * heavy_ll_k(n, 0, alpha, beta, lgab, den, lnfact, lng, lng_n);
+            for (uint64_t k = 1; k <= n; ++k) ex = logsumexp2(ex, 2.0 * heavy_ll_k(n, k, alpha, beta, lgab, den, lnfact, lng, lng_n));
+        }
+        hv_ll[h] = own;
+        hv_c[h2c[h]] = own;
+        hv_e[h] = ex;
+    }
+    // deep entries of this warp, one at a time over all 32 lanes
+    unsigned int deep = __ballot_sync(0xffffffffu, live && on && n > HEAVY_CHAIN_MAX && n <= HEAVY_GIANT);
+    while (deep) {
+        const int src = __ffs(deep) - 1;
+        deep &= deep - 1;
+        const uint64_t dn = __shfl_sync(0xffffffffu, (unsigned long long)n, src), da = __shfl_sync(0xffffffffu, (unsigned long long)a, src);
+        const double dal = __shfl_sync(0xffffffffu, alpha, src), dbe = __shfl_sync(0xffffffffu, beta, src);
+        const double dden = __shfl_sync(0xffffffffu, den, src), dlgab = __shfl_sync(0xffffffffu, lgab, src);
+        const uint32_t dh = h - lane + (uint32_t)src;
+        double ex = 0.0;
+        if (with_expected) {
+            double m = -INFINITY;
+            for (uint64_t k = lane; k <= dn; k += 32) m = fmax(m, 2.0 * heavy_ll_k(dn, k, dal, dbe, dlgab, dden, lnfact, lng, lng_n));
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, off));
+            double sum = 0.0;
+            for (uint64_t k = lane; k <= dn; k += 32) sum += exp(2.0 * heavy_ll_k(dn, k, dal, dbe, dlgab, dden, lnfact, lng, lng_n) - m);
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+            ex = m + log(sum);
+        }
+        if ((int)lane == src) {
+            const double own = heavy_ll_k(dn, da, dal, dbe, dlgab, dden, lnfact, lng, lng_n);
+            hv_ll[dh] = own;
+            hv_c[h2c[dh]] = own;
+            hv_e[dh] = ex;
+        }
+    }
+}
+
+// EM-pass table build (init_alpha_betas main.rs:598-611 + the memo record of numerics.cuh) as lookups: one thread
+// per (locus, n), n = 1..3.  alpha and beta are integer-valued here, so every ln_gamma comes out of the lng memo and
+// the record costs 2(n+1)+4 loads, n+1 additions chains and n logsumexp steps — no Lanczos series, no shared-memory
+// phases.  Expressions are those of k_tables<0> / build_locus_table, operation for operation.  Thread 0.. of block
+// 0 also clears the per-iteration DeviceStats.
+__global__ void __launch_bounds__(256) k_tables_em(EmCounts cnts, uint32_t n_loci, Lbc10 lbc, int with_expected,
+                                                   double* __restrict__ tab, double* __restrict__ tab13,
+                                                   DeviceStats* __restrict__ st_clear) {
+    __shared__ double s_lbc[10];
+    if (threadIdx.x < 10) s_lbc[threadIdx.x] = lbc.v[threadIdx.x];
+    if (st_clear != nullptr && blockIdx.x == 0 && threadIdx.x < sizeof(DeviceStats) / 8)
+        reinterpret_cast<unsigned long long*>(st_clear)[threadIdx.x] = 0ull;
+    __syncthreads();
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t l = t / 3u;
+    const int n = (int)(t % 3u) + 1;
+    if (l >= n_loci) return;
+    double alpha, beta, den;
+    em_alpha_beta(cnts, l, &alpha, &beta, &den);
+    const bool on = den == den;
+    double* rec = tab + (size_t)l * TAB_STRIDE;
+    double* r13 = tab13 != nullptr ? tab13 + (size_t)l * TAB13 : nullptr;
+    if (n == 1) {
+        rec[3] = on ? 0.0 : quiet_nan();
+        rec[TAB_DEN] = den;
+        rec[TAB_ALPHA] = alpha;
+        rec[TAB_BETA] = beta;
+        if (r13) r13[12] = 0.0;
+    }
+    // rolled loops on purpose (small code: the kernel runs for microseconds and instruction fetch showed up first)
+    double pm0 = 0.0, pm1 = 0.0, pm2 = 0.0, pm3 = 0.0;
+    double e = on ? 0.0 : quiet_nan();
+    if (on) {
+        const double lgab = ln_gamma_int((0.0 + alpha) + ((double)n + beta), cnts.lng, cnts.lng_n);
+#pragma unroll 1
+        for (int a = 0; a <= n; ++a) {
+            const double num = ln_gamma_int((double)a + alpha, cnts.lng, cnts.lng_n) +
+                               ln_gamma_int((double)(n - a) + beta, cnts.lng, cnts.lng_n) - lgab;
+            const double v = s_lbc[lbc_idx(a, n)] + num - den;
+            if (a == 0) pm0 = v;
+            else if (a == 1) pm1 = v;
+            else if (a == 2) pm2 = v;
+            else pm3 = v;
+        }
+        if (with_expected) {  // stats.rs:17-22, left to right
+            e = 2.0 * pm0;
+#pragma unroll 1
+            for (int k = 1; k <= n; ++k) e = logsumexp2(e, 2.0 * (k == 1 ? pm1 : (k == 2 ? pm2 : pm3)));
+        }
+    }
+#pragma unroll 1
+    for (int a = 0; a <= n; ++a) {
+        const double v = a == 0 ? pm0 : (a == 1 ? pm1 : (a == 2 ? pm2 : pm3));
+        rec[tab_idx_T(a, n)] = on ? v : quiet_nan();
+        if (r13) r13[tab13_T(a, n)] = on ? v : 0.0;
+    }
+    rec[tab_idx_E(n)] = e;
+    if (r13) r13[tab13_E(n)] = on ? e : 0.0;
 }
 
 // One CTA per giant entry (total > HEAVY_GIANT): streaming max / sum logsumexp over k = 0..n in fixed chunks.
 __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict__ giant_idx, uint32_t n_giant,
                                                      const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
-                                                     const uint32_t* __restrict__ h_alt, const double* __restrict__ tab,
+                                                     const uint32_t* __restrict__ h_alt, EmCounts cnts,
                                                      const double* __restrict__ lnfact, int with_expected,
                                                      double* __restrict__ hv_ll, double* __restrict__ hv_e,
                                                      const uint32_t* __restrict__ h2c, double* __restrict__ hv_c) {
     __shared__ double s_m[8], s_s[8];
     const uint32_t h = giant_idx[blockIdx.x];
-    const double* rec = tab + (size_t)h_locus[h] * TAB_STRIDE;
-    const double alpha = rec[TAB_ALPHA], beta = rec[TAB_BETA], den = rec[TAB_DEN];
+    double alpha, beta, den;
+    em_alpha_beta(cnts, h_locus[h], &alpha, &beta, &den);
     if (!(den == den)) return;  // switched off: k_heavy_em wrote the zeros
     const uint64_t a = h_alt[h], r = h_ref[h], n = a + r;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

@@ -85,9 +85,20 @@ CLX_HD double ln_gamma(double x) {
 
 // ln_gamma of an integer-valued argument through the memo lng[i] = ln_gamma((double)i): the same double, bit for
 // bit (ln_gamma is a pure function of its argument); arguments beyond the memo are evaluated directly.
+#ifdef __CUDACC__
+// out of line: the Lanczos series is ~700 instructions and is the cold path here; inlined at every call site it
+// made the lookup kernels instruction-fetch bound
+static __device__ __noinline__ double ln_gamma_outofline(double x) { return ln_gamma(x); }
+#else
+inline double ln_gamma_outofline(double x) { return ln_gamma(x); }
+#endif
 CLX_HD double ln_gamma_int(double x, const double* __restrict__ lng, uint32_t lng_n) {
     if (x < (double)lng_n) return lng[(uint32_t)x];
+#ifdef __CUDA_ARCH__
+    return ln_gamma_outofline(x);
+#else
     return ln_gamma(x);
+#endif
 }
 
 // lnfact[i] = ln(i!) for i <= 170, computed on the host exactly like statrs (ln of the f64 product table).

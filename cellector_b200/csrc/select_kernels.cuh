@@ -61,24 +61,31 @@ __device__ __forceinline__ void select_from_list(unsigned long long* __restrict_
                                                  unsigned long long* __restrict__ spre,
                                                  const unsigned long long* __restrict__ srank) {
     const unsigned int tid = threadIdx.x;
-    for (unsigned int i = tid; i < SELECT_LIST_PAD; i += blockDim.x)
-        if (i >= nl) s_list[i] = ~0ull;
-    __syncthreads();
-    for (unsigned int k = 2; k <= SELECT_LIST_PAD; k <<= 1)
-        for (unsigned int j = k >> 1; j > 0; j >>= 1) {
-            if (tid < SELECT_LIST_PAD) {
-                const unsigned int o = tid ^ j;
-                if (o > tid) {
-                    const unsigned long long a = s_list[tid], b = s_list[o];
-                    const bool up = (tid & k) == 0;
-                    if ((a > b) == up) {
-                        s_list[tid] = b;
-                        s_list[o] = a;
+    // warp 0 alone runs the network (__syncwarp between steps) over the next power of two >= nl: the usual case is a
+    // dozen survivors, where 36 CTA-wide barriers would cost more than the whole select
+    unsigned int P = 32;
+    while (P < nl) P <<= 1;
+    if (tid < 32) {
+        for (unsigned int i = tid; i < P; i += 32)
+            if (i >= nl) s_list[i] = ~0ull;
+        __syncwarp();
+        for (unsigned int k = 2; k <= P; k <<= 1)
+            for (unsigned int j = k >> 1; j > 0; j >>= 1) {
+                for (unsigned int i = tid; i < P; i += 32) {
+                    const unsigned int o = i ^ j;
+                    if (o > i) {
+                        const unsigned long long a = s_list[i], b = s_list[o];
+                        const bool up = (i & k) == 0;
+                        if ((a > b) == up) {
+                            s_list[i] = b;
+                            s_list[o] = a;
+                        }
                     }
                 }
+                __syncwarp();
             }
-            __syncthreads();
-        }
+    }
+    __syncthreads();
     unsigned long long res = 0ull;
     if (tid < SELECT_TARGETS) {
         const unsigned long long lo_key = hi_bit >= 64 ? 0ull : (spre[tid] << hi_bit);
@@ -89,7 +96,7 @@ __device__ __forceinline__ void select_from_list(unsigned long long* __restrict_
             else hi = mid;
         }
         const unsigned long long at = (unsigned long long)lo + srank[tid];
-        res = s_list[at < SELECT_LIST_PAD ? at : SELECT_LIST_PAD - 1];
+        res = s_list[at < P ? at : P - 1];
     }
     __syncthreads();
     if (tid < SELECT_TARGETS) spre[tid] = res;
@@ -319,6 +326,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_small(const dou
 // (main.rs:330-335) for this rank's cells runs in the same launch.
 constexpr int SELECT_COOP_HIST = 8 * SELECT_TARGETS * 256;  // u32 words
 constexpr int SELECT_COOP_SCRATCH = SELECT_COOP_HIST + 8;   // + {or, nor} (2 x u64) + n_list + pad
+template <int R>
 __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
     const double* __restrict__ vals, uint64_t n, SelectPlan plan, const IterParams* __restrict__ prm,
     DeviceStats* __restrict__ st, unsigned int* __restrict__ scratch, unsigned long long* __restrict__ glist,
@@ -336,12 +344,12 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long* g_or = reinterpret_cast<unsigned long long*>(scratch + SELECT_COOP_HIST);
     unsigned int* g_nlist = scratch + SELECT_COOP_HIST + 4;
-    unsigned long long key[SELECT_R];
+    unsigned long long key[R];
     unsigned int valid = 0;
     unsigned long long k_or = 0ull, k_nor = 0ull;
 #pragma unroll
-    for (int j = 0; j < SELECT_R; ++j) {
-        const uint64_t i = ((uint64_t)blockIdx.x * SELECT_R + j) * SELECT_SMALL_THREADS + tid;
+    for (int j = 0; j < R; ++j) {
+        const uint64_t i = ((uint64_t)blockIdx.x * R + j) * SELECT_SMALL_THREADS + tid;
         key[j] = 0ull;
         if (i < n) {
             key[j] = f64_to_key(vals[i]);
@@ -412,7 +420,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
                 lrow[k] = k < nlead ? s_leadt[k] : 0;
             }
 #pragma unroll
-            for (int j = 0; j < SELECT_R; ++j) {
+            for (int j = 0; j < R; ++j) {
                 if (!((valid >> j) & 1u)) continue;
                 const unsigned long long pk = hi_bit >= 64 ? 0ull : (key[j] >> hi_bit);
                 const unsigned int d = (unsigned int)(key[j] >> lo_bit) & dmask;
@@ -476,7 +484,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
 #pragma unroll
             for (int t = 0; t < SELECT_TARGETS; ++t) pre[t] = spre[t];
 #pragma unroll
-            for (int j = 0; j < SELECT_R; ++j) {
+            for (int j = 0; j < R; ++j) {
                 if (!((valid >> j) & 1u)) continue;
                 const unsigned long long pk = key[j] >> lo_bit;
                 bool keep = false;
@@ -493,7 +501,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
         // few keys left over the whole grid: every CTA appends its survivors to one global list, then ranks them
         if (valid) {
 #pragma unroll
-            for (int j = 0; j < SELECT_R; ++j)
+            for (int j = 0; j < R; ++j)
                 if ((valid >> j) & 1u) {
                     const unsigned int slot = atomicAdd(g_nlist, 1u);
                     if (slot < SELECT_RANK_CAP) glist[slot] = key[j];
