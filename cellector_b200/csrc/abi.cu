@@ -186,6 +186,8 @@ void clx_destroy(clx_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    alloc_stream() = c->stream;
+    p2p_teardown(c);
     comm_destroy(c);
     phase_resolve(c);
     em_drop_graph(c);

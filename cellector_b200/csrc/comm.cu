@@ -135,6 +135,15 @@ int comm_allgather_f64(clx_ctx* c, const double* send, double* recv, size_t n_pe
     return CLX_OK;
 }
 
+int comm_allgather_u64(clx_ctx* c, const unsigned long long* send, unsigned long long* recv, size_t n_per_rank) {
+    if (c->world <= 1 || n_per_rank == 0) return CLX_OK;
+    Api& a = api();
+    const int rc = a.AllGather(send, recv, n_per_rank, ncclUint64, (ncclComm_t)c->nccl_comm, c->stream);
+    if (rc != ncclSuccess) return nccl_fail(c, "ncclAllGather", rc);
+    c->launches++;
+    return CLX_OK;
+}
+
 int comm_allgather_u64_host(clx_ctx* c, uint64_t v, std::vector<uint64_t>* out) {
     out->assign((size_t)c->world, 0);
     if (c->world <= 1) {

@@ -92,6 +92,15 @@ struct clx_ctx {
     int rank = 0, world = 1;
     void* nccl_comm = nullptr;
 
+    // --- peer-memory window (p2p.cu): the per-iteration exchanges as NVLink stores/loads instead of NCCL launches
+    bool p2p = false;
+    void* win = nullptr;
+    size_t win_bytes = 0, win_off_counters = 0, win_off_norm = 0, win_off_part_ll = 0, win_off_part_int = 0, win_off_tot_ll = 0,
+           win_off_tot_int = 0;
+    std::vector<void*> peer_win;          // [world] every rank's window as mapped here (own window at [rank])
+    clx::DevBuf<void*> d_peer_win;        // the same table in device memory
+    unsigned long long p2p_epoch = 0;     // one per iteration; barrier flags only grow
+
     // --- matrix (load.cu)
     bool loaded = false;
     uint32_t n_cells = 0;          // local cells
@@ -219,11 +228,18 @@ int comm_allreduce_f64(clx_ctx* c, double* buf, size_t n);
 int comm_group_begin(clx_ctx* c);
 int comm_group_end(clx_ctx* c);
 int comm_allgather_f64(clx_ctx* c, const double* send, double* recv, size_t n_per_rank);
+int comm_allgather_u64(clx_ctx* c, const unsigned long long* send, unsigned long long* recv, size_t n_per_rank);
 int comm_allgather_u64_host(clx_ctx* c, uint64_t v, std::vector<uint64_t>* out);
 void comm_destroy(clx_ctx* c);
 int comm_unique_id(void* out128);
 int comm_init(clx_ctx* c, int rank, int world, const void* id128);
 
+// p2p.cu
+int p2p_setup(clx_ctx* c, size_t L, size_t max_local);  // collective; leaves c->p2p false if peer mapping is not possible
+void p2p_teardown(clx_ctx* c);
+int p2p_barrier(clx_ctx* c, int phase);
+int p2p_put_norm(clx_ctx* c);
+int p2p_reduce(clx_ctx* c);
 // load.cu
 int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, const uint32_t* locus,
              const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt);

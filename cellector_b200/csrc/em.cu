@@ -65,6 +65,9 @@ template <bool FUSE>
 void launch_columns(clx_ctx* c, int G) {
     const uint32_t n = c->n_loci;
     if (n == 0) return;
+    // sharded over peer memory: the partial sums go into this rank's window, where the slice owners read them
+    double* out_ll = c->p2p ? reinterpret_cast<double*>((unsigned char*)c->win + c->win_off_part_ll) : c->loc_ll.p;
+    unsigned long long* out_int = c->p2p ? reinterpret_cast<unsigned long long*>((unsigned char*)c->win + c->win_off_part_int) : c->loc_int.p;
     // k_columns_w (one warp per column, software-pipelined) measured slower than the G-lanes-per-column kernel on
     // B200 at both bench sizes (C2: 33 vs 28 us, C3 shard: 197 vs 150 us): opt-in until that is understood
     static const int warp_cols = env_int("CLX_COLUMNS_W", 0);
@@ -72,14 +75,14 @@ void launch_columns(clx_ctx* c, int G) {
         const unsigned grid = std::min<unsigned>((n + COLW_WARPS - 1) / COLW_WARPS, (unsigned)c->sm_count * (unsigned)env_int("CLX_COLW_CTAS", 3));
         k_columns_w<FUSE><<<grid, COLW_WARPS * 32, 0, c->stream>>>(
             c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_cell.p, c->hc_ref.p,
-            c->hc_alt.p, c->hv_c.p, c->loc_ll.p, c->loc_int.p, c->n_used.p, c->d_stats.p);
+            c->hc_alt.p, c->hv_c.p, out_ll, out_int, c->n_used.p, c->d_stats.p);
         c->launches++;
         return;
     }
 #define CLX_COLS(GG)                                                                                                   \
     k_columns<GG, FUSE><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                          \
         c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_perm.p,            \
-        c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hv_ll.p, c->loc_ll.p, c->loc_int.p, c->n_used.p, c->d_stats.p)
+        c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hv_ll.p, out_ll, out_int, c->n_used.p, c->d_stats.p)
     switch (G) {
         case 1: CLX_COLS(1); break;
         case 2: CLX_COLS(2); break;
@@ -206,6 +209,7 @@ int em_alloc(clx_ctx* c) {
         CLX_CUDA(c, cudaMemcpyAsync(c->norm.p, inf.data(), norm_n * 8, cudaMemcpyHostToDevice, c->stream));
         CLX_CUDA(c, cudaStreamSynchronize(c->stream));
     }
+    CLX_TRY(p2p_setup(c, L, c->max_local_cells));
     c->score_G = env_int("CLX_SCORE_G", pick_group(N ? (double)c->nnz / N : 0.0));
     c->col_G = env_int("CLX_COL_G", pick_group(L ? (double)c->nnz / L : 0.0));
     // roofline accounting of the gather scoring kernel: packed entries + row pointers + outputs + table
@@ -306,7 +310,14 @@ int enqueue_iteration(clx_ctx* c) {
     //    + new excluded set and change counts (main.rs:330-335)
     const double* sel_vals = c->norm.p;
     uint64_t n_vals = N;
-    if (c->world > 1) {
+    if (c->world > 1 && c->p2p) {
+        phase_begin(c, CLX_PHASE_COMM);
+        CLX_TRY(p2p_put_norm(c));   // all-gather = remote stores into every rank's window (also bumps the barrier epoch)
+        CLX_TRY(p2p_barrier(c, 0));
+        phase_end(c, CLX_PHASE_COMM);
+        sel_vals = reinterpret_cast<const double*>((unsigned char*)c->win + c->win_off_norm);
+        n_vals = (uint64_t)c->world * c->max_local_cells;
+    } else if (c->world > 1) {
         phase_begin(c, CLX_PHASE_COMM);
         CLX_TRY(comm_allgather_f64(c, c->norm.p, c->norm_all.p, c->max_local_cells));
         phase_end(c, CLX_PHASE_COMM);
@@ -326,12 +337,27 @@ int enqueue_iteration(clx_ctx* c) {
     CLX_DEBUG_SYNC(c, "k_columns");
     if (c->world > 1) {
         phase_begin(c, CLX_PHASE_COMM);
-        // one fused NCCL launch: per-locus sums and counts + the three change counters of the exclusion step
-        CLX_TRY(comm_group_begin(c));
-        CLX_TRY(comm_allreduce_u64(c, &c->d_stats.p->n_new, 3));
-        CLX_TRY(comm_allreduce_f64(c, c->loc_ll.p, 2 * (size_t)L));
-        CLX_TRY(comm_allreduce_u64(c, c->loc_int.p, 8 * (size_t)L));
-        CLX_TRY(comm_group_end(c));
+        if (c->p2p) {
+            unsigned char* w = (unsigned char*)c->win;
+            // this rank's change counters next to its partial sums, then: barrier, slice-owner reduction that stores the
+            // totals into every window, barrier, totals into the arrays the rest of the code reads
+            CLX_CUDA(c, cudaMemcpyAsync(w + c->win_off_counters, &c->d_stats.p->n_new, 24, cudaMemcpyDeviceToDevice, s));
+            CLX_TRY(p2p_barrier(c, 1));
+            CLX_TRY(p2p_reduce(c));
+            CLX_TRY(p2p_barrier(c, 2));
+            if (L) {
+                CLX_CUDA(c, cudaMemcpyAsync(c->loc_ll.p, w + c->win_off_tot_ll, 2 * (size_t)L * 8, cudaMemcpyDeviceToDevice, s));
+                CLX_CUDA(c, cudaMemcpyAsync(c->loc_int.p, w + c->win_off_tot_int, 8 * (size_t)L * 8, cudaMemcpyDeviceToDevice, s));
+            }
+            CLX_CUDA(c, cudaMemcpyAsync(&c->d_stats.p->n_new, w + c->win_off_counters + 32, 24, cudaMemcpyDeviceToDevice, s));
+        } else {
+            // one fused NCCL launch: per-locus sums and counts + the three change counters of the exclusion step
+            CLX_TRY(comm_group_begin(c));
+            CLX_TRY(comm_allreduce_u64(c, &c->d_stats.p->n_new, 3));
+            CLX_TRY(comm_allreduce_f64(c, c->loc_ll.p, 2 * (size_t)L));
+            CLX_TRY(comm_allreduce_u64(c, c->loc_int.p, 8 * (size_t)L));
+            CLX_TRY(comm_group_end(c));
+        }
         phase_end(c, CLX_PHASE_COMM);
         phase_begin(c, CLX_PHASE_COLUMN);
         if (L) {
@@ -351,9 +377,10 @@ int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
     if (!c->loaded) return fail(c, CLX_ERR_STATE, "clx_em_iteration before clx_load_coo");
     cudaStream_t s = c->stream;
     c->h_params->iqr_multiple = iqr_multiple;
-    // One-GPU contexts replay the iteration as a CUDA graph (a dozen launches, ~40 us of work at 10x scale:
-    // launch gaps matter).  Sharded contexts enqueue directly: NCCL calls sit between the kernels.
-    const bool use_graph = c->world == 1 && !(c->flags & CLX_FLAG_NO_GRAPH);
+    // The iteration is replayed as a CUDA graph (a dozen launches, ~100 us of work at 10x scale: launch gaps matter),
+    // also when cells are sharded and the exchanges go over peer memory (barrier kernels inside the graph).  Only
+    // the NCCL fallback enqueues directly: collective calls sit between the kernels there.
+    const bool use_graph = (c->world == 1 || c->p2p) && !(c->flags & CLX_FLAG_NO_GRAPH);
     if (use_graph && !c->iter_graph_exec) {
         cudaGraph_t graph = nullptr;
         const uint64_t launches0 = c->launches;
@@ -388,6 +415,7 @@ int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
     CLX_CUDA(c, cudaGetLastError());
     phase_resolve(c);
     const DeviceStats& st = *c->h_stats;
+    if (st.pad) return fail(c, CLX_ERR_NCCL, "a peer-memory barrier timed out (a rank is missing or failed)");
     if (st.nan_flag) return fail(c, CLX_ERR_NAN, "NaN normalized log likelihood (the reference panics in argsort, main.rs:504)");
     c->n_excluded_global = st.n_excluded;
     if (out) {

@@ -95,7 +95,7 @@ def main():
             parity.assert_equal(gp[k], op[k], f"posterior {k}")
         for k in ("ll_major", "ll_minor"):
             parity.assert_close(gp[k], op[k], f"posterior {k}")
-        print(f"MULTI_OK case={case} world={world} iterations={n_it} cells={len(gp['label'])}", flush=True)
+        print(f"MULTI_OK case={case} world={world} iterations={n_it} cells={len(gp['label'])} CLX_P2P={os.environ.get('CLX_P2P')}", flush=True)
     gpu.close()
     dist.destroy_process_group()
 
