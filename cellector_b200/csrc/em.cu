@@ -154,8 +154,12 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
         uint32_t* bits = c->excl_bits.p;
         uint32_t n_local = N;
         SelectPlan pl = plan;
+        unsigned char* const* win = c->p2p ? (unsigned char* const*)c->d_peer_win.p : nullptr;
+        int rank = c->rank, world = c->world;
+        size_t off_counters = c->win_off_counters;
         void* args[] = {(void*)&vals, (void*)&n_vals, (void*)&pl, (void*)&prm, (void*)&st, (void*)&scratch,
-                        (void*)&glist, (void*)&norm_local, (void*)&n_local, (void*)&bits};
+                        (void*)&glist, (void*)&norm_local, (void*)&n_local, (void*)&bits, (void*)&win, (void*)&rank,
+                        (void*)&world, (void*)&off_counters};
         const void* fn = R == 1 ? (const void*)k_select_coop<1> : (R == 4 ? (const void*)k_select_coop<4> : (const void*)k_select_coop<16>);
         CLX_CUDA(c, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SELECT_SMALL_THREADS), args, 0, s));
         c->launches++;
@@ -312,8 +316,11 @@ int enqueue_iteration(clx_ctx* c) {
     uint64_t n_vals = N;
     if (c->world > 1 && c->p2p) {
         phase_begin(c, CLX_PHASE_COMM);
-        CLX_TRY(p2p_put_norm(c));   // all-gather = remote stores into every rank's window (also bumps the barrier epoch)
-        CLX_TRY(p2p_barrier(c, 0));
+        CLX_TRY(p2p_put_norm(c));   // all-gather = remote stores into every rank's window (also bumps the barrier epoch);
+                                    // barrier 0 sits at the head of the cooperative select kernel
+        if (env_int("CLX_SELECT_MODE", 0) == 2 ||
+            (uint64_t)c->world * c->max_local_cells > 16ull * SELECT_SMALL_THREADS * (uint64_t)c->sm_count)
+            CLX_TRY(p2p_barrier(c, 0));  // the multi-launch select has no barrier of its own
         phase_end(c, CLX_PHASE_COMM);
         sel_vals = reinterpret_cast<const double*>((unsigned char*)c->win + c->win_off_norm);
         n_vals = (uint64_t)c->world * c->max_local_cells;
@@ -338,18 +345,9 @@ int enqueue_iteration(clx_ctx* c) {
     if (c->world > 1) {
         phase_begin(c, CLX_PHASE_COMM);
         if (c->p2p) {
-            unsigned char* w = (unsigned char*)c->win;
-            // this rank's change counters next to its partial sums, then: barrier, slice-owner reduction that stores the
-            // totals into every window, barrier, totals into the arrays the rest of the code reads
-            CLX_CUDA(c, cudaMemcpyAsync(w + c->win_off_counters, &c->d_stats.p->n_new, 24, cudaMemcpyDeviceToDevice, s));
-            CLX_TRY(p2p_barrier(c, 1));
+            // barrier 1 + slice-owner reduction that stores the totals into every window (one launch); barrier 2, the
+            // copy of the totals and the -80 rule are fused into k_locus_filter_p2p below
             CLX_TRY(p2p_reduce(c));
-            CLX_TRY(p2p_barrier(c, 2));
-            if (L) {
-                CLX_CUDA(c, cudaMemcpyAsync(c->loc_ll.p, w + c->win_off_tot_ll, 2 * (size_t)L * 8, cudaMemcpyDeviceToDevice, s));
-                CLX_CUDA(c, cudaMemcpyAsync(c->loc_int.p, w + c->win_off_tot_int, 8 * (size_t)L * 8, cudaMemcpyDeviceToDevice, s));
-            }
-            CLX_CUDA(c, cudaMemcpyAsync(&c->d_stats.p->n_new, w + c->win_off_counters + 32, 24, cudaMemcpyDeviceToDevice, s));
         } else {
             // one fused NCCL launch: per-locus sums and counts + the three change counters of the exclusion step
             CLX_TRY(comm_group_begin(c));
@@ -360,7 +358,12 @@ int enqueue_iteration(clx_ctx* c) {
         }
         phase_end(c, CLX_PHASE_COMM);
         phase_begin(c, CLX_PHASE_COLUMN);
-        if (L) {
+        if (c->p2p) {
+            k_locus_filter_p2p<<<std::max(1u, (L + TPB - 1) / TPB), TPB, 0, s>>>(
+                (unsigned char* const*)c->d_peer_win.p, c->rank, c->world, c->win_off_counters, c->win_off_tot_ll, c->win_off_tot_int,
+                c->loc_ll.p, c->loc_int.p, L, c->loci_used.p, c->csc.p, c->col_ptr.p, c->n_used.p, c->d_stats.p);
+            c->launches++;
+        } else if (L) {
             k_locus_filter<<<(L + TPB - 1) / TPB, TPB, 0, s>>>(c->loc_ll.p, c->loc_int.p, L, c->loci_used.p, c->csc.p, c->col_ptr.p,
                                                                c->n_used.p, c->d_stats.p);
             c->launches++;

@@ -5,6 +5,7 @@
 
 #include "ctx.h"
 #include "numerics.cuh"
+#include "p2p_dev.cuh"
 
 namespace clx {
 
@@ -853,4 +854,52 @@ __global__ void __launch_bounds__(256) k_locus_filter(const double* __restrict__
     }
 }
 
+}  // namespace clx
+
+namespace clx {
+// Sharded over peer memory: waits for barrier 2 (every slice owner has stored its totals into this rank's window),
+// copies the totals and the summed change counters into the arrays the rest of the code reads, and applies the -80
+// rule — k_locus_filter with the exchange fused in front.
+__global__ void __launch_bounds__(256) k_locus_filter_p2p(unsigned char* const* __restrict__ win, int rank, int world,
+                                                          size_t off_counters, size_t off_tot_ll, size_t off_tot_int,
+                                                          double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int,
+                                                          uint32_t n_loci, uint8_t* __restrict__ used, const ColEntry* __restrict__ csc,
+                                                          const uint64_t* __restrict__ col_ptr, uint32_t* __restrict__ n_used,
+                                                          DeviceStats* __restrict__ st) {
+    p2p_sync_head(win, rank, world, 2, off_counters, &st->pad);
+    const double* tot_ll = reinterpret_cast<const double*>(win[rank] + off_tot_ll);
+    const unsigned long long* tot_int = reinterpret_cast<const unsigned long long*>(win[rank] + off_tot_int);
+    if (blockIdx.x == 0 && threadIdx.x < 3)
+        (&st->n_new)[threadIdx.x] = reinterpret_cast<const unsigned long long*>(win[rank] + off_counters)[4 + threadIdx.x];
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t L = n_loci;
+    bool filtered = false, in_use = false;
+    if (l < n_loci) {
+        const double s_min = tot_ll[l];
+        loc_ll[l] = s_min;
+        loc_ll[L + l] = tot_ll[L + l];
+        unsigned long long cm = 0;
+#pragma unroll
+        for (int a = 0; a < 8; ++a) {
+            const unsigned long long v = tot_int[(size_t)a * L + l];
+            loc_int[(size_t)a * L + l] = v;
+            if (a == 0) cm = v;
+        }
+        const double per_cell = cm != 0 ? s_min / (double)cm : 0.0;
+        const bool was = used[l] != 0;
+        if (per_cell < -80.0) {
+            filtered = was;
+            used[l] = 0;
+            if (was)
+                for (uint64_t i = col_ptr[l]; i < col_ptr[l + 1]; ++i) atomicSub(&n_used[csc[i].cell], 1u);
+        } else {
+            in_use = was;
+        }
+    }
+    const uint32_t f = __popc(__ballot_sync(0xffffffffu, filtered)), u = __popc(__ballot_sync(0xffffffffu, in_use));
+    if ((threadIdx.x & 31) == 0) {
+        if (f) atomicAdd(&st->n_loci_filtered, (unsigned long long)f);
+        if (u) atomicAdd(&st->n_loci_in_use, (unsigned long long)u);
+    }
+}
 }  // namespace clx

@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "ctx.h"
+#include "p2p_dev.cuh"
 
 namespace clx {
 namespace {
@@ -25,15 +26,6 @@ constexpr size_t WIN_FLAGS_BYTES = 4096;
 constexpr int P2P_PHASES = 3;
 // the counters block sits 256 bytes before the norm area (p2p_setup)
 __host__ __device__ constexpr size_t off_norm_to_counters(size_t off_norm) { return off_norm - 256; }
-
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
 
 // window base pointers of all ranks (this rank's own included), in device memory
 // The epoch lives in the window (slot 8 of the counters block) and is bumped by k_p2p_put_norm at the head of every
@@ -72,7 +64,12 @@ __global__ void k_p2p_put_norm(unsigned char* const* __restrict__ win, int rank,
 
 // reduce-scatter + all-gather in one kernel: rank r owns loci [L r / world, L (r+1) / world) of each of the ten arrays
 __global__ void k_p2p_reduce(unsigned char* const* __restrict__ win, int rank, int world, size_t off_part_ll, size_t off_part_int,
-                             size_t off_tot_ll, size_t off_tot_int, size_t off_counters, uint32_t L) {
+                             size_t off_tot_ll, size_t off_tot_int, size_t off_counters, uint32_t L,
+                             const unsigned long long* __restrict__ my_counters, unsigned int* __restrict__ err) {
+    // this rank's change counters go next to its partial sums, then barrier 1 (every rank's column pass is done)
+    if (blockIdx.x == 0 && threadIdx.x < 3) reinterpret_cast<unsigned long long*>(win[rank] + off_counters)[threadIdx.x] = my_counters[threadIdx.x];
+    __syncthreads();
+    p2p_sync_head(win, rank, world, 1, off_counters, err);
     const uint32_t l0 = (uint32_t)((uint64_t)L * rank / world), l1 = (uint32_t)((uint64_t)L * (rank + 1) / world);
     const uint32_t n = l1 - l0;
     // ten arrays of L: a = 0, 1 are the f64 arrays, 2..9 the u64 arrays
@@ -114,19 +111,6 @@ int p2p_setup(clx_ctx* c, size_t L, size_t max_local) {
     if (c->world <= 1) return CLX_OK;
     const char* env = getenv("CLX_P2P");
     const bool want = !(env && env[0] == '0');
-    // peers may still be reading the old window: everyone closes its mappings, then a collective, then the free
-    for (size_t r = 0; r < c->peer_win.size(); ++r)
-        if ((int)r != c->rank && c->peer_win[r]) cudaIpcCloseMemHandle(c->peer_win[r]);
-    c->peer_win.clear();
-    c->p2p = false;
-    DevBuf<unsigned long long> sync;
-    CLX_CUDA(c, sync.alloc(2));
-    CLX_CUDA(c, cudaMemsetAsync(sync.p, 0, 16, c->stream));
-    CLX_TRY(comm_allreduce_u64(c, sync.p, 1));
-    CLX_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (c->win) cudaFree(c->win);
-    c->win = nullptr;
-
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
     c->win_off_counters = WIN_FLAGS_BYTES;
     c->win_off_norm = c->win_off_counters + 256;
@@ -134,7 +118,31 @@ int p2p_setup(clx_ctx* c, size_t L, size_t max_local) {
     c->win_off_part_int = c->win_off_part_ll + up(2 * L * 8 + 8);
     c->win_off_tot_ll = c->win_off_part_int + up(8 * L * 8 + 8);
     c->win_off_tot_int = c->win_off_tot_ll + up(2 * L * 8 + 8);
-    c->win_bytes = c->win_off_tot_int + up(8 * L * 8 + 8);
+    const size_t need = c->win_off_tot_int + up(8 * L * 8 + 8);
+    // a window that is already mapped everywhere and large enough is kept (mapping costs milliseconds): the layout
+    // depends only on global sizes, flags and epoch simply continue.  Unanimous or not at all.
+    DevBuf<unsigned long long> sync;
+    CLX_CUDA(c, sync.alloc(2));
+    {
+        const unsigned long long keep = (c->p2p && want && c->win && need <= c->win_bytes) ? 1ull : 0ull;
+        CLX_CUDA(c, cudaMemcpyAsync(sync.p, &keep, 8, cudaMemcpyHostToDevice, c->stream));
+        CLX_TRY(comm_allreduce_u64(c, sync.p, 1));
+        unsigned long long n_keep = 0;
+        CLX_CUDA(c, cudaMemcpyAsync(&n_keep, sync.p, 8, cudaMemcpyDeviceToHost, c->stream));
+        CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (n_keep == (unsigned long long)c->world) return CLX_OK;
+    }
+    // peers may still be reading the old window: everyone closes its mappings, then a collective, then the free
+    for (size_t r = 0; r < c->peer_win.size(); ++r)
+        if ((int)r != c->rank && c->peer_win[r]) cudaIpcCloseMemHandle(c->peer_win[r]);
+    c->peer_win.clear();
+    c->p2p = false;
+    CLX_CUDA(c, cudaMemsetAsync(sync.p, 0, 16, c->stream));
+    CLX_TRY(comm_allreduce_u64(c, sync.p, 1));
+    CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->win) cudaFree(c->win);
+    c->win = nullptr;
+    c->win_bytes = need + need / 4;  // slack: the next load of a similar matrix reuses the mapping
     unsigned long long ok = 0;
     cudaIpcMemHandle_t mine;
     memset(&mine, 0, sizeof(mine));
@@ -217,7 +225,7 @@ int p2p_reduce(clx_ctx* c) {
     const uint64_t work = 10ull * (L / c->world + 1);
     k_p2p_reduce<<<(unsigned)std::min<uint64_t>((work + 255) / 256, (uint64_t)c->sm_count * 2), 256, 0, c->stream>>>(
         (unsigned char* const*)c->d_peer_win.p, c->rank, c->world, c->win_off_part_ll, c->win_off_part_int, c->win_off_tot_ll,
-        c->win_off_tot_int, c->win_off_counters, L);
+        c->win_off_tot_int, c->win_off_counters, L, &c->d_stats.p->n_new, &c->d_stats.p->pad);
     c->launches++;
     return CLX_OK;
 }

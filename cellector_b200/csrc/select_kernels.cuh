@@ -13,6 +13,7 @@
 
 #include "ctx.h"
 #include "numerics.cuh"
+#include "p2p_dev.cuh"
 
 namespace clx {
 
@@ -330,8 +331,11 @@ template <int R>
 __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
     const double* __restrict__ vals, uint64_t n, SelectPlan plan, const IterParams* __restrict__ prm,
     DeviceStats* __restrict__ st, unsigned int* __restrict__ scratch, unsigned long long* __restrict__ glist,
-    const double* __restrict__ norm_local, uint32_t n_cells_local, uint32_t* __restrict__ bits) {
+    const double* __restrict__ norm_local, uint32_t n_cells_local, uint32_t* __restrict__ bits,
+    unsigned char* const* __restrict__ win, int rank, int world, size_t off_counters) {
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    // sharded over peer memory: barrier 0 — every rank has stored its normalized values into this rank's window
+    if (win != nullptr) p2p_sync_head(win, rank, world, 0, off_counters, &st->pad);
     __shared__ unsigned int sh[SELECT_TARGETS][256];
     __shared__ unsigned long long spre[SELECT_TARGETS], srank[SELECT_TARGETS];
     __shared__ int sgrp[SELECT_TARGETS];
