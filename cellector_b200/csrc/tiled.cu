@@ -16,7 +16,7 @@
 //     group is stored TRANSPOSED — entry j of lane l at j * 32 + l, shorter runs padded with a null entry that
 //     points at an all-zero record — so one lane sums one run with conflict-free 64-byte warp loads, no per-lane
 //     trip counts, no shuffles; runs of a group have similar lengths, so padding is small (~2.6 B per nonzero);
-//   * groups are cut into BATCHES of at most BATCH_ITERS iterations ([16 B header][32 cells if first][entries])
+//   * groups are cut into BATCHES of at most BATCH_ITERS iterations ([16 B header][32 one-byte cell indices if first][entries])
 //     and batches are packed into PACKETS of at most STAGE_BYTES — one TMA bulk copy each into the warp's ring;
 //   * a work ITEM = one cell block x a range of consecutive tiles; the CTA keeps the block's accumulators in
 //     shared memory across the range and writes one partial per cell at the end; k_score_finish adds the
@@ -38,9 +38,9 @@ constexpr uint32_t NB_MAX = 3072;        // cells per block: 16 B of accumulator
 constexpr uint32_t NB_MIN = 256;
 constexpr int RING_STAGES = 2;           // packets per warp: one being summed, one in flight
 constexpr uint32_t STAGE_BYTES = 1024;
-constexpr uint32_t BATCH_ITERS = 14;     // 16 + 16 + 64 + 64 * 14 = 992 <= STAGE_BYTES
+constexpr uint32_t BATCH_ITERS = 15;     // 16 + 16 + 32 + 64 * 15 = 1024 <= STAGE_BYTES
 constexpr uint32_t NULL_ENTRY = (uint32_t)TILE_L << 6;  // record TILE_L of a staged tile is all zeros
-static_assert(16 + 16 + 64 + 64 * BATCH_ITERS <= STAGE_BYTES, "a packet holds at least one full batch");
+static_assert(16 + 16 + 32 + 64 * BATCH_ITERS <= STAGE_BYTES, "a packet holds at least one full batch");
 static_assert(TL_WARPS == 32, "one CTA of 1024 threads");
 
 inline unsigned grid_for(uint64_t n, int tpb = TPB, unsigned cap = 148u * 16u) {
@@ -108,15 +108,14 @@ __global__ void k_sub_runs(const unsigned long long* __restrict__ key2_sorted, u
     const uint64_t su = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     if (su <= n_sub) sub_run[su] = (uint32_t)lower_bound_dev<unsigned long long>(key2_sorted, 0, n_runs, su << 16);
 }
-// light entries of every unit (for the work-item partition); ukeys is sorted by unit
-__global__ void k_unit_entries(const unsigned long long* __restrict__ ukeys, const unsigned long long* __restrict__ run_start,
-                               uint32_t n_runs, unsigned long long n_light, uint32_t n_units,
-                               unsigned long long* __restrict__ unit_entries) {
+// cost of every unit for the work-item partition: the stream bytes (in quads) of its 32 sub-units — padded groups
+// included, so a ragged cell block whose groups are mostly padding is not mistaken for cheap work
+__global__ void k_unit_cost(const uint32_t* __restrict__ n_quads, uint32_t n_units, unsigned long long* __restrict__ unit_cost) {
     const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
     if (u >= n_units) return;
-    const uint64_t a = lower_bound_dev<unsigned long long>(ukeys, 0, n_runs, (unsigned long long)u << 12);
-    const uint64_t b = lower_bound_dev<unsigned long long>(ukeys, 0, n_runs, (unsigned long long)(u + 1) << 12);
-    unit_entries[u] = (b < n_runs ? run_start[b] : n_light) - (a < n_runs ? run_start[a] : n_light);
+    unsigned long long sum = 0;
+    for (uint32_t w = 0; w < (uint32_t)TL_WARPS; ++w) sum += n_quads[(size_t)u * TL_WARPS + w];
+    unit_cost[u] = sum;
 }
 
 // The packets of one sub-unit, generated in order; F is called once per batch with
@@ -131,7 +130,7 @@ __device__ __forceinline__ void walk_sub_unit(const uint32_t* __restrict__ idx_s
         for (uint32_t j0 = 0; j0 < M; j0 += BATCH_ITERS) {
             const uint32_t m = min(BATCH_ITERS, M - j0);
             const bool first = j0 == 0, last = j0 + m >= M;
-            const uint32_t bytes = 16u + (first ? 64u : 0u) + 64u * m;
+            const uint32_t bytes = 16u + (first ? 32u : 0u) + 64u * m;
             if (pk_batches && pk_bytes + bytes > STAGE_BYTES) {
                 on_packet(pk, pk_start, pk_bytes, pk_batches);
                 pk_start += pk_bytes;
@@ -192,8 +191,9 @@ __global__ void k_sub_fill(const uint32_t* __restrict__ sub_run, const uint32_t*
             }
             uint16_t* p16 = reinterpret_cast<uint16_t*>(base + off + 16);
             if (first) {
-                p16[lane] = (uint16_t)cell;
-                p16 += 32;
+                // the run's cell as q = cell_local / 32 (cell_local % 32 is the owning warp): one byte, 0xFF = no run
+                reinterpret_cast<uint8_t*>(p16)[lane] = cell == 0xFFFFu ? (uint8_t)0xFF : (uint8_t)(cell >> 5);
+                p16 += 16;
             }
             for (uint32_t j = 0; j < m; ++j) {
                 const uint32_t jj = j0 + j;
@@ -264,19 +264,19 @@ __device__ __forceinline__ uint32_t acc_slot(uint32_t cell_local, uint32_t Q) { 
 
 template <bool WITH_E>
 __device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ pk, const double* __restrict__ tab,
-                                             double2* __restrict__ acc, int lane, RunState& st, uint32_t Q) {
+                                             double2* __restrict__ acc, int lane, int w, RunState& st, uint32_t Q) {
     const uint32_t nb = *reinterpret_cast<const uint32_t*>(pk);
     const unsigned char* p = pk + 16;
     for (uint32_t b = 0; b < nb; ++b) {
         const uint32_t hdr = *reinterpret_cast<const uint32_t*>(p);
         const uint32_t m = hdr & 0xFFu;
         const uint16_t* e = reinterpret_cast<const uint16_t*>(p + 16);
-        if (hdr & 0x100u) {  // first batch of a group: 32 cell ids
-            const uint32_t c = e[lane];
-            st.cell = c == 0xFFFFu ? 0xFFFFu : acc_slot(c, Q);
+        if (hdr & 0x100u) {  // first batch of a group: 32 one-byte cell indices
+            const uint32_t q = reinterpret_cast<const uint8_t*>(e)[lane];
+            st.cell = q == 0xFFu ? 0xFFFFu : (uint32_t)w * Q + q;  // accumulator slot (acc_slot of cell 32 q + w)
             st.sT = 0.0;
             st.sE = 0.0;
-            e += 32;
+            e += 16;
         }
         double sT = st.sT, sE = st.sE;
 #pragma unroll 4
@@ -298,7 +298,7 @@ __device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ p
             a.y += sE;
             acc[st.cell] = a;
         }
-        p += 16u + ((hdr & 0x100u) ? 64u : 0u) + 64u * m;
+        p += 16u + ((hdr & 0x100u) ? 32u : 0u) + 64u * m;
     }
 }
 
@@ -398,7 +398,7 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
             for (uint32_t p = pk_base[sub0 + (size_t)k * TL_WARPS]; p < p_end; ++p) {
                 const uint32_t s = cons_c % RING_STAGES;
                 mbar_wait(&my_bar[s], (cons_c / RING_STAGES) & 1u);
-                tiled_packet<WITH_E>(my_ring + (size_t)s * STAGE_BYTES, tab, acc, lane, st, Q);
+                tiled_packet<WITH_E>(my_ring + (size_t)s * STAGE_BYTES, tab, acc, lane, w, st, Q);
                 __syncwarp();
                 ++cons_c;
                 issue_one();  // refill the stage just drained
@@ -538,7 +538,18 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         const char* env = getenv("CLX_TILED_PC");
         if (env && *env) pc = std::max<uint32_t>(pc, (uint32_t)atoi(env));
         c->tl_Pc = pc;
-        c->tl_NB = N ? (N + pc - 1) / pc : 1;
+        uint32_t nb = N ? (N + pc - 1) / pc : 1;
+        // whole groups: 32 warps x 32 lanes = 1024 cells give every (tile, warp) exactly 32 runs; a ragged tail of a few
+        // runs per warp costs a whole padded group per tile
+        const uint32_t nb_even = (nb + 31) / 32 * 32;
+        if (nb >= 1024) {
+            const uint32_t nb_whole = std::min<uint32_t>(NB_MAX, nb / 1024 * 1024);
+            const uint32_t tail = N % nb_whole;  // cells of the ragged last block
+            nb = (tail == 0 || 2 * tail >= nb_whole) ? nb_whole : nb_even;
+        } else {
+            nb = nb_even;
+        }
+        c->tl_NB = nb;
         c->tl_Pc = N ? (N + c->tl_NB - 1) / c->tl_NB : 1;
     }
     c->tl_n_units = c->tl_Pc * c->tl_nT;
@@ -621,8 +632,8 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         c->launches += 7;
     }
     k_sub_runs<<<(unsigned)((n_sub + 1 + TPB - 1) / TPB), TPB, 0, s>>>(key2_sorted.p, R, n_sub, sub_run.p);
-    k_unit_entries<<<(n_units + TPB - 1) / TPB, TPB, 0, s>>>(ukeys.p, run_start.p, R, n_light, n_units, unit_entries.p);
     k_sub_count<<<(unsigned)((n_sub + 1 + TPB - 1) / TPB), TPB, 0, s>>>(sub_run.p, ridx_sorted.p, counts.p, n_sub, n_pk.p, n_quads.p);
+    k_unit_cost<<<(n_units + TPB - 1) / TPB, TPB, 0, s>>>(n_quads.p, n_units, unit_entries.p);
     CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tb, n_pk.p, c->tl_pk_base.p, (int)(n_sub + 1), s));
     CLX_CUDA(c, tmp.alloc(tb));
     CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, n_pk.p, c->tl_pk_base.p, (int)(n_sub + 1), s));
@@ -663,6 +674,8 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     {
         std::vector<uint32_t> items, cb_item;
         std::vector<unsigned long long> item_entries;
+        unsigned long long cost_total = 0;
+        for (uint32_t u = 0; u < n_units; ++u) cost_total += h_unit[u];
         const uint64_t total_items = std::max<uint64_t>(1, (uint64_t)env_items * (uint64_t)c->sm_count);
         for (uint32_t cb = 0; cb < c->tl_Pc; ++cb) {
             cb_item.push_back((uint32_t)(items.size() / 4));
@@ -670,7 +683,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
             unsigned long long cb_total = 0;
             for (uint32_t t = 0; t < c->tl_nT; ++t) cb_total += ue[t];
             if (cb_total == 0) continue;
-            uint64_t want = n_light ? (cb_total * total_items + n_light / 2) / n_light : 1;
+            uint64_t want = cost_total ? (cb_total * total_items + cost_total / 2) / cost_total : 1;
             want = std::max<uint64_t>(1, std::min<uint64_t>(want, c->tl_nT));
             unsigned long long acc = 0;
             uint32_t t0 = 0;
