@@ -327,8 +327,8 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_small(const dou
 // (main.rs:330-335) for this rank's cells runs in the same launch.
 constexpr int SELECT_COOP_HIST = 8 * SELECT_TARGETS * 256;  // u32 words
 constexpr int SELECT_COOP_SCRATCH = SELECT_COOP_HIST + 8;   // + {or, nor} (2 x u64) + n_list + pad
-template <int R>
-__global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
+template <int R, int T>
+__global__ void __launch_bounds__(T) k_select_coop(
     const double* __restrict__ vals, uint64_t n, SelectPlan plan, const IterParams* __restrict__ prm,
     DeviceStats* __restrict__ st, unsigned int* __restrict__ scratch, unsigned long long* __restrict__ glist,
     const double* __restrict__ norm_local, uint32_t n_cells_local, uint32_t* __restrict__ bits,
@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
     unsigned long long k_or = 0ull, k_nor = 0ull;
 #pragma unroll
     for (int j = 0; j < R; ++j) {
-        const uint64_t i = ((uint64_t)blockIdx.x * R + j) * SELECT_SMALL_THREADS + tid;
+        const uint64_t i = ((uint64_t)blockIdx.x * R + j) * T + tid;
         key[j] = 0ull;
         if (i < n) {
             key[j] = f64_to_key(vals[i]);
@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
     if (tid < SELECT_TARGETS) srank[tid] = plan.rank[tid];
     __syncthreads();
     if (tid == 0) {
-        for (int w = 1; w < SELECT_SMALL_THREADS / 32; ++w) { k_or |= s_or[w]; k_nor |= s_nor[w]; }
+        for (int w = 1; w < T / 32; ++w) { k_or |= s_or[w]; k_nor |= s_nor[w]; }
         atomicOr(&g_or[0], k_or);
         atomicOr(&g_or[1], k_nor);
     }
@@ -391,7 +391,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
         const int lo_bit = hi_bit > 8 ? hi_bit - 8 : 0;
         const unsigned int dmask = (1u << (hi_bit - lo_bit)) - 1u;
         unsigned int* gh = scratch + (size_t)pass * SELECT_TARGETS * 256;
-        for (int i = tid; i < SELECT_TARGETS * 256; i += SELECT_SMALL_THREADS) (&sh[0][0])[i] = 0;
+        for (int i = tid; i < SELECT_TARGETS * 256; i += T) (&sh[0][0])[i] = 0;
         if (tid < SELECT_TARGETS) {
             unsigned long long p[SELECT_TARGETS];
 #pragma unroll
@@ -434,12 +434,12 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
             }
         }
         __syncthreads();
-        for (int i = tid; i < SELECT_TARGETS * 256; i += SELECT_SMALL_THREADS) {
+        for (int i = tid; i < SELECT_TARGETS * 256; i += T) {
             const unsigned int v = (&sh[0][0])[i];
             if (v) atomicAdd(&gh[i], v);
         }
         grid.sync();
-        for (int i = tid; i < SELECT_TARGETS * 256; i += SELECT_SMALL_THREADS) (&sh[0][0])[i] = __ldcg(&gh[i]);
+        for (int i = tid; i < SELECT_TARGETS * 256; i += T) (&sh[0][0])[i] = __ldcg(&gh[i]);
         __syncthreads();
         if (warp < SELECT_TARGETS) {
             const int t = warp;
@@ -513,7 +513,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
         }
         grid.sync();
         const unsigned int nl = min(__ldcg(g_nlist), SELECT_RANK_CAP);
-        for (unsigned int i = tid; i < nl; i += SELECT_SMALL_THREADS) s_list[i] = __ldcg(&glist[i]);
+        for (unsigned int i = tid; i < nl; i += T) s_list[i] = __ldcg(&glist[i]);
         __syncthreads();
         select_from_list(s_list, nl, hi_bit, spre, srank);
     }
@@ -537,7 +537,7 @@ __global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_coop(
         const double thr = sthr;
         const uint32_t n_words = (n_cells_local + 31) / 32;
         unsigned int nn = 0, nr = 0, ne = 0;
-        for (uint32_t w = blockIdx.x * (SELECT_SMALL_THREADS / 32) + warp; w < n_words; w += gridDim.x * (SELECT_SMALL_THREADS / 32)) {
+        for (uint32_t w = blockIdx.x * (T / 32) + warp; w < n_words; w += gridDim.x * (T / 32)) {
             const uint32_t i = w * 32 + lane;
             const bool ex = i < n_cells_local && norm_local[i] < thr;  // main.rs:331
             const unsigned int word = __ballot_sync(0xffffffffu, ex);
