@@ -59,6 +59,8 @@ ABI = {
     "comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "load_coo": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                            C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
+    "load_coo_packed": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
     "get_locus_ids": (C.c_int, [C.c_void_p, C.c_void_p]),
     "reset": (C.c_int, [C.c_void_p]),
     "em_iteration": (C.c_int, [C.c_void_p, C.c_double, C.POINTER(IterStats)]),
@@ -135,6 +137,17 @@ class CtxApi:
         nl, nz = C.c_uint32(0), C.c_uint64(0)
         self._check(self._f("load_coo")(self._h, nnz0, n_loci0, n_cells, *[_ptr(a) for a in arrs], min_ref, min_alt,
                                         C.byref(nl), C.byref(nz)), "load_coo")
+        self.n_cells, self.n_loci0 = int(n_cells), int(n_loci0)
+        self.n_loci_used, self.nnz_used = int(nl.value), int(nz.value)
+        return self.n_loci_used, self.nnz_used
+
+    def load_cell_data_packed(self, locus, cell, ref_alt, n_loci0, n_cells, min_ref=4, min_alt=4):
+        """load_cell_data with both counts of an entry in one word (ref | alt << 16)."""
+        arrs = [np.ascontiguousarray(x, dtype=np.uint32) for x in (locus, cell, ref_alt)]
+        nnz0 = arrs[0].shape[0]
+        nl, nz = C.c_uint32(0), C.c_uint64(0)
+        self._check(self._f("load_coo_packed")(self._h, nnz0, n_loci0, n_cells, *[_ptr(a) for a in arrs], min_ref, min_alt,
+                                               C.byref(nl), C.byref(nz)), "load_coo_packed")
         self.n_cells, self.n_loci0 = int(n_cells), int(n_loci0)
         self.n_loci_used, self.nnz_used = int(nl.value), int(nz.value)
         return self.n_loci_used, self.nnz_used

@@ -233,6 +233,18 @@ int clx_load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, 
     return CLX_OK;
 }
 
+int clx_load_coo_packed(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, const uint32_t* locus,
+                        const uint32_t* cell, const uint32_t* ref_alt, uint32_t min_ref, uint32_t min_alt,
+                        uint32_t* n_loci_used, uint64_t* nnz_used) {
+    if (!c) return CLX_ERR_ARG;
+    cudaSetDevice(c->device);
+    alloc_stream() = c->stream;
+    CLX_TRY(load_coo(c, nnz0, n_loci0, n_cells, locus, cell, ref_alt, nullptr, min_ref, min_alt));
+    if (n_loci_used) *n_loci_used = c->n_loci;
+    if (nnz_used) *nnz_used = c->nnz;
+    return CLX_OK;
+}
+
 int clx_get_locus_ids(clx_ctx* c, uint32_t* ids) {
     if (!c || !c->loaded) return c ? fail(c, CLX_ERR_STATE, "not loaded") : CLX_ERR_ARG;
     CLX_TRY(d2h(c, ids, c->locus_ids.p, c->n_loci));

@@ -241,6 +241,7 @@ int p2p_barrier(clx_ctx* c, int phase);
 int p2p_put_norm(clx_ctx* c);
 int p2p_reduce(clx_ctx* c);
 // load.cu
+// `alt` == nullptr: `ref` holds both counts of an entry, ref | alt << 16 (clx_load_coo_packed)
 int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, const uint32_t* locus,
              const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt);
 // tiled.cu

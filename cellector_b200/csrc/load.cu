@@ -184,6 +184,14 @@ __global__ void k_heavy_csc(const uint32_t* __restrict__ perm, uint32_t n_heavy,
     h2c[h] = j;
 }
 
+__global__ void k_unpack_counts(const uint32_t* __restrict__ packed, uint64_t n, uint32_t* __restrict__ ref, uint32_t* __restrict__ alt) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t v = packed[i];
+        ref[i] = v & 0xFFFFu;
+        alt[i] = v >> 16;
+    }
+}
+
 int bits_for(uint64_t n) {
     int b = 1;
     while (b < 32 && (1ull << b) < n) ++b;
@@ -197,7 +205,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     cudaStream_t s = c->stream;
     c->loaded = false;
     if (nnz0 >= 0xFFFFFFFFull) return fail(c, CLX_ERR_ARG, "more than 2^32-1 nonzeros per GPU: shard the cells over more ranks");
-    if (nnz0 > 0 && (!locus || !cell || !ref || !alt)) return fail(c, CLX_ERR_ARG, "null COO array");
+    if (nnz0 > 0 && (!locus || !cell || !ref)) return fail(c, CLX_ERR_ARG, "null COO array");
     c->n_cells = n_cells;
     c->n_loci0 = n_loci0;
     c->nnz0 = nnz0;
@@ -226,8 +234,16 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     if (nnz0) {
         CLX_CUDA(c, cudaMemcpyAsync(d_locus.p, locus, nnz0 * 4, cudaMemcpyHostToDevice, s));
         CLX_CUDA(c, cudaMemcpyAsync(d_cell.p, cell, nnz0 * 4, cudaMemcpyHostToDevice, s));
-        CLX_CUDA(c, cudaMemcpyAsync(d_ref.p, ref, nnz0 * 4, cudaMemcpyHostToDevice, s));
-        CLX_CUDA(c, cudaMemcpyAsync(d_alt.p, alt, nnz0 * 4, cudaMemcpyHostToDevice, s));
+        if (alt) {
+            CLX_CUDA(c, cudaMemcpyAsync(d_ref.p, ref, nnz0 * 4, cudaMemcpyHostToDevice, s));
+            CLX_CUDA(c, cudaMemcpyAsync(d_alt.p, alt, nnz0 * 4, cudaMemcpyHostToDevice, s));
+        } else {  // both counts in one word: 4 bytes less per entry over PCIe, split on the device
+            DevBuf<uint32_t> d_packed;
+            CLX_CUDA(c, d_packed.alloc(nnz0));
+            CLX_CUDA(c, cudaMemcpyAsync(d_packed.p, ref, nnz0 * 4, cudaMemcpyHostToDevice, s));
+            k_unpack_counts<<<grid_for(nnz0), TPB, 0, s>>>(d_packed.p, nnz0, d_ref.p, d_alt.p);
+            c->launches++;
+        }
     }
 
     // ---- pass 1: locus filter

@@ -156,3 +156,51 @@ def test_determinism_bitwise(libs):
     for a, b in zip(outs[0], outs[1]):
         for k in a:
             assert np.array_equal(a[k], b[k]), k
+
+
+def test_packed_load_is_the_same_load(libs):
+    """clx_load_coo_packed (ref | alt << 16) must build the very state clx_load_coo builds."""
+    gpu, _ = _pair(libs)
+    d = synth.generate(CASES["c1_slice"])
+    outs = []
+    with gpu:
+        for packed in (False, True):
+            if packed:
+                ra = d.ref.astype(np.uint32) | (d.alt.astype(np.uint32) << 16)
+                used = gpu.load_cell_data_packed(d.locus, d.cell, ra, d.n_loci, d.n_cells)
+            else:
+                used = gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+            gpu.run_em()
+            outs.append((used, gpu.locus_ids(), gpu.cell_vectors(), gpu.locus_vectors(), gpu.calculate_posteriors()))
+    assert outs[0][0] == outs[1][0]
+    assert np.array_equal(outs[0][1], outs[1][1])
+    for a, b in zip(outs[0][2:], outs[1][2:]):
+        for k in a:
+            assert np.array_equal(a[k], b[k]), k
+
+
+def test_gpu_against_committed_golden(libs):
+    """The CUDA path against tests/golden/oracle_c1_slice.json with no oracle in the loop: integers and the excluded
+    sets identical, fp64 sums and quantiles within 1e-9 relative."""
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "oracle_c1_slice.json")))
+    d = synth.generate(synth.SynthConfig(**g["config"]))
+    gpu, _ = _pair(libs)
+    with gpu:
+        assert list(gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)) == g["loaded"]
+        for want in g["iterations"]:
+            st = gpu.compute_new_excluded(5.0).as_dict()
+            for k, v in want["stats"].items():
+                if isinstance(v, float):
+                    assert st[k] == pytest.approx(v, rel=1e-9, abs=1e-12), k
+                else:
+                    assert st[k] == v, (k, st[k], v)
+            cv = gpu.cell_vectors()
+            assert float(cv["ll"].sum()) == pytest.approx(want["ll_sum"], rel=1e-9)
+            assert float(cv["expected_ll"].sum()) == pytest.approx(want["expected_ll_sum"], rel=1e-9)
+            assert int(cv["n_loci"].sum()) == want["n_loci_sum"]
+            assert np.flatnonzero(cv["excluded"]).tolist() == want["excluded"]
+        p = gpu.calculate_posteriors()
+        assert np.bincount(p["label"], minlength=4).tolist() == g["label_counts"]
+        assert float(p["ll_minor"].sum()) == pytest.approx(g["ll_minor_sum"], rel=1e-9)
