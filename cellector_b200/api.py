@@ -88,7 +88,8 @@ def bind(lib: C.CDLL, prefix: str, names=None):
     return lib
 
 
-def load_library(path: str = LIB_PATH) -> C.CDLL:
+def load_library(path: str = "") -> C.CDLL:
+    path = path or os.environ.get("CLX_LIB_PATH") or LIB_PATH  # CLX_LIB_PATH: A/B runs of two builds of the library
     if not os.path.exists(path):
         raise RuntimeError(
             f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "

@@ -132,8 +132,8 @@ struct clx_ctx {
     uint32_t tl_NB = 0, tl_Pc = 0, tl_nT = 0, tl_n_items = 0, tl_n_units = 0;
     uint64_t tl_n_light = 0, tl_stream_len = 0;       // light entries; stream length incl. slice padding
     clx::DevBuf<uint32_t> tl_stream;                  // [tl_stream_len] packets of runs (tiled.cu), 4-byte words
-    clx::DevBuf<uint32_t> tl_pk_q;                    // [n_packets + 1] packet starts, in quads (16 B)
-    clx::DevBuf<uint32_t> tl_pk_base;                 // [n_units + 1] first packet of every (cell block, tile) unit
+    clx::DevBuf<uint2> tl_pk_d;                       // [n_packets] packet descriptors {start, size}, in quads (16 B)
+    clx::DevBuf<uint32_t> tl_pk_base;                 // [n_sub + 1] first packet of every (cell block, warp, tile) sub-unit
     clx::DevBuf<uint32_t> tl_items;                   // [n_items][4] cell block, first tile, end tile, -
     clx::DevBuf<uint32_t> tl_cb_item;                 // [Pc + 1] first item of every cell block
     clx::DevBuf<uint32_t> tl_order;                   // [n_items] items by decreasing entry count (work-queue order)

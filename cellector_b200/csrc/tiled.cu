@@ -18,6 +18,10 @@
 //     trip counts, no shuffles; runs of a group have similar lengths, so padding is small (~2.6 B per nonzero);
 //   * groups are cut into BATCHES of at most BATCH_ITERS iterations ([16 B header][32 one-byte cell indices if first][entries])
 //     and batches are packed into PACKETS of at most STAGE_BYTES — one TMA bulk copy each into the warp's ring;
+//   * sub-units are numbered warp-major ((cell block, warp), then tile): the packets one warp consumes over the
+//     consecutive tiles of a work item are ONE consecutive range of the descriptor list {start, size}, which the
+//     warp reads 32 at a time with one coalesced load and hands round by shuffle (no dependent global load sits
+//     between two packets); a packet's header names its tile, and that is how the warp learns a tile has ended;
 //   * a work ITEM = one cell block x a range of consecutive tiles; the CTA keeps the block's accumulators in
 //     shared memory across the range and writes one partial per cell at the end; k_score_finish adds the
 //     partials of a cell block in item order (fixed order: deterministic), appends the heavy values and normalises.
@@ -90,16 +94,24 @@ __device__ __forceinline__ uint64_t lower_bound_dev(const T* __restrict__ a, uin
     return lo;
 }
 
-// runs (unique keys + counts, from cub::DeviceRunLengthEncode) -> sort key (sub-unit << 16 | 0xFFFF - count), sub-unit
-// = unit * TL_WARPS + owning warp: longest first inside a sub-unit
+// Sub-unit = the runs of one warp in one (cell block, tile) unit.  Sub-units are numbered warp-major,
+// su = (cell block * TL_WARPS + warp) * nT + tile, so that the packets a warp consumes over consecutive tiles of a
+// work item are consecutive in the packet list and in the stream.
+__device__ __forceinline__ unsigned long long sub_unit_of(unsigned long long unit, uint32_t w, uint32_t nT) {
+    const unsigned long long cb = unit / nT, t = unit % nT;
+    return (cb * TL_WARPS + w) * nT + t;
+}
+// runs (unique keys + counts, from cub::DeviceRunLengthEncode) -> sort key (sub-unit << 16 | 0xFFFF - count): longest
+// first inside a sub-unit
 __global__ void k_run_keys(const unsigned long long* __restrict__ ukeys, const int* __restrict__ counts, uint32_t n_runs,
-                           unsigned long long* __restrict__ key2, uint32_t* __restrict__ idx, unsigned int* __restrict__ too_long) {
+                           uint32_t nT, unsigned long long* __restrict__ key2, uint32_t* __restrict__ idx,
+                           unsigned int* __restrict__ too_long) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_runs) return;
     const uint32_t cnt = (uint32_t)counts[r];
     if (cnt > 0xFFFFu) atomicOr(too_long, 1u);
     const unsigned long long unit = ukeys[r] >> 12, cl = ukeys[r] & 0xFFFull;
-    key2[r] = ((unit * TL_WARPS + (cl % TL_WARPS)) << 16) | (unsigned long long)(0xFFFFu - (cnt > 0xFFFFu ? 0xFFFFu : cnt));
+    key2[r] = (sub_unit_of(unit, (uint32_t)(cl % TL_WARPS), nT) << 16) | (unsigned long long)(0xFFFFu - (cnt > 0xFFFFu ? 0xFFFFu : cnt));
     idx[r] = r;
 }
 // first sorted run of every sub-unit, su in [0, n_sub]
@@ -110,11 +122,12 @@ __global__ void k_sub_runs(const unsigned long long* __restrict__ key2_sorted, u
 }
 // cost of every unit for the work-item partition: the stream bytes (in quads) of its 32 sub-units — padded groups
 // included, so a ragged cell block whose groups are mostly padding is not mistaken for cheap work
-__global__ void k_unit_cost(const uint32_t* __restrict__ n_quads, uint32_t n_units, unsigned long long* __restrict__ unit_cost) {
+__global__ void k_unit_cost(const uint32_t* __restrict__ n_quads, uint32_t n_units, uint32_t nT,
+                            unsigned long long* __restrict__ unit_cost) {
     const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
     if (u >= n_units) return;
     unsigned long long sum = 0;
-    for (uint32_t w = 0; w < (uint32_t)TL_WARPS; ++w) sum += n_quads[(size_t)u * TL_WARPS + w];
+    for (uint32_t w = 0; w < (uint32_t)TL_WARPS; ++w) sum += n_quads[sub_unit_of(u, w, nT)];
     unit_cost[u] = sum;
 }
 
@@ -161,13 +174,13 @@ __global__ void k_sub_count(const uint32_t* __restrict__ sub_run, const uint32_t
     n_quads[su] = bytes >> 4;
 }
 
-// one warp per sub-unit writes its packets: packet header {n_batches}, batch header {m | first << 8 | last << 9},
-// the 32 cell ids of a first batch, and the transposed entries
+// one warp per sub-unit writes its packets: packet header {n_batches, tile}, batch header {m | first << 8 | last << 9},
+// the 32 cell ids of a first batch, and the transposed entries; and the packet's descriptor {start quad, size in quads}
 __global__ void k_sub_fill(const uint32_t* __restrict__ sub_run, const uint32_t* __restrict__ pk_base,
                            const uint32_t* __restrict__ q_base, const uint32_t* __restrict__ idx_sorted,
                            const unsigned long long* __restrict__ ukeys, const int* __restrict__ counts,
                            const unsigned long long* __restrict__ run_start, const uint16_t* __restrict__ vals_sorted,
-                           uint64_t n_sub, uint32_t* __restrict__ pk_q, uint32_t* __restrict__ stream) {
+                           uint64_t n_sub, uint32_t nT, uint2* __restrict__ pk_d, uint32_t* __restrict__ stream) {
     const uint64_t su = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31;
     if (su >= n_sub) return;
@@ -200,12 +213,12 @@ __global__ void k_sub_fill(const uint32_t* __restrict__ sub_run, const uint32_t*
                 p16[j * 32 + lane] = jj < cnt ? vals_sorted[src + jj] : (uint16_t)NULL_ENTRY;
             }
         },
-        [&](uint32_t pk, uint32_t start, uint32_t, uint32_t nb) {
+        [&](uint32_t pk, uint32_t start, uint32_t sz, uint32_t nb) {
             if (lane == 0) {
-                pk_q[pkb + pk] = qb + (start >> 4);
+                pk_d[pkb + pk] = make_uint2(qb + (start >> 4), sz >> 4);
                 uint32_t* ph = reinterpret_cast<uint32_t*>(base + start);
                 ph[0] = nb;
-                ph[1] = 0;
+                ph[1] = (uint32_t)(su % nT);  // the locus tile this packet indexes
                 ph[2] = 0;
                 ph[3] = 0;
             }
@@ -304,7 +317,7 @@ __device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ p
 
 template <bool WITH_E>
 __global__ void __launch_bounds__(TL_WARPS * 32, 1)
-    k_score_tiled(const uint32_t* __restrict__ stream, const uint32_t* __restrict__ pk_q, const uint32_t* __restrict__ pk_base,
+    k_score_tiled(const uint32_t* __restrict__ stream, const uint2* __restrict__ pk_d, const uint32_t* __restrict__ pk_base,
                   const uint32_t* __restrict__ items, uint32_t n_items, const uint32_t* __restrict__ order,
                   uint32_t* __restrict__ counter, const double* __restrict__ tab13, uint32_t nT, uint32_t NB,
                   double* __restrict__ part) {
@@ -329,8 +342,8 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
         z[tid % TAB13] = 0.0;
     }
     __syncthreads();
-    uint32_t g_tile = 0;             // tiles consumed by this CTA so far (buffer = g & 1, parity = (g >> 1) & 1)
-    uint32_t cons_c = 0, iss_c = 0;  // packets consumed / issued by this warp so far (stage = c % STAGES)
+    uint32_t g_tile = 0;  // tiles consumed by this CTA so far (buffer = g & 1, parity = (g >> 1) & 1)
+    uint32_t cons_c = 0;  // packets consumed by this warp so far (stage = c % STAGES, parity = (c / STAGES) & 1)
     unsigned char* my_ring = ring + (size_t)w * RING_STAGES * STAGE_BYTES;
     uint64_t* my_bar = ring_full + w * RING_STAGES;
     RunState st;
@@ -347,7 +360,14 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
         if (qk >= n_items) break;
         const uint32_t item = order[qk];
         const uint32_t cb = items[4 * item], t0 = items[4 * item + 1], ntile = items[4 * item + 2] - t0;
-        const size_t sub0 = ((size_t)cb * nT + t0) * TL_WARPS + w;  // this warp's sub-unit of the item's first tile
+        // this warp's packets over the item's tiles are one consecutive range of the packet list (warp-major sub-units)
+        const size_t su0 = ((size_t)cb * TL_WARPS + w) * nT + t0;
+        const uint32_t P0 = pk_base[su0], np = pk_base[su0 + ntile] - P0;
+        // descriptor window: lane l holds packet win0 + l (and win0 + 32 + l prefetched), one coalesced load per 32
+        // packets; nothing on the packet path waits for a dependent global load
+        uint32_t win0 = 0;
+        uint2 dwin = lane < np ? pk_d[P0 + lane] : make_uint2(0u, 0u);
+        uint2 dnxt = 32u + lane < np ? pk_d[P0 + 32u + lane] : make_uint2(0u, 0u);
         for (uint32_t i = tid; i < 32u * Q; i += blockDim.x) acc[i] = make_double2(0.0, 0.0);
         if (tid == 0) {
             for (uint32_t k = 0; k < 2 && k < ntile; ++k) {
@@ -357,54 +377,33 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
                          &tab_full[g & 1]);
             }
         }
-        // the warp's packets, tile after tile; the issue cursor runs RING_STAGES packets ahead of the consumer
-        uint32_t ik = 0, ip = 0, ip_end = 0;
-        bool i_more = ntile > 0;
-        if (i_more) {
-            ip = pk_base[sub0];
-            ip_end = pk_base[sub0 + 1];
-        }
-        auto issue_one = [&]() {
-            while (i_more && ip >= ip_end) {
-                ++ik;
-                if (ik >= ntile) {
-                    i_more = false;
-                    break;
-                }
-                ip = pk_base[sub0 + (size_t)ik * TL_WARPS];
-                ip_end = pk_base[sub0 + (size_t)ik * TL_WARPS + 1];
+        // packet i of this warp goes to ring stage (cons_c at item start + i) % STAGES; issue runs STAGES ahead
+        const uint32_t c_base = cons_c;
+        auto issue = [&](uint32_t i) {
+            if (i >= np) return;
+            if (i >= win0 + 32u) {
+                win0 += 32u;
+                dwin = dnxt;
+                dnxt = win0 + 32u + lane < np ? pk_d[P0 + win0 + 32u + lane] : make_uint2(0u, 0u);
             }
-            if (!i_more) return;
-            const uint32_t q0 = pk_q[ip], bytes = (pk_q[ip + 1] - q0) * 16u;
-            const uint32_t s = iss_c % RING_STAGES;
+            const uint32_t q0 = __shfl_sync(0xffffffffu, dwin.x, (int)(i - win0));
+            const uint32_t bytes = __shfl_sync(0xffffffffu, dwin.y, (int)(i - win0)) * 16u;
+            const uint32_t s = (c_base + i) % RING_STAGES;
 #ifdef CLX_TILED_DEBUG
             if (lane == 0 && (bytes == 0 || bytes > STAGE_BYTES))
-                printf("bad packet: blk %d w %d item %u ik %u ip %u q0 %u bytes %u\n", blockIdx.x, w, item, ik, ip, q0, bytes);
+                printf("bad packet: blk %d w %d item %u i %u q0 %u bytes %u\n", blockIdx.x, w, item, i, q0, bytes);
 #endif
             if (lane == 0) {
                 mbar_expect_tx(&my_bar[s], bytes);
                 bulk_g2s(my_ring + (size_t)s * STAGE_BYTES, stream + (size_t)q0 * 4, bytes, &my_bar[s]);
             }
-            ++ip;
-            ++iss_c;
         };
-        for (int i = 0; i < RING_STAGES; ++i) issue_one();
+        for (uint32_t i = 0; i < (uint32_t)RING_STAGES; ++i) issue(i);
         __syncthreads();  // accumulators cleared
-        for (uint32_t k = 0; k < ntile; ++k) {
+        // hand a table buffer over: the last warp to leave tile k starts the copy of tile k + 2 into it.  No CTA
+        // barrier: cells never change warps, so accumulators need none, and warps drift by at most two tiles.
+        auto leave_tile = [&](uint32_t k) {
             const uint32_t g = g_tile + k;
-            const double* tab = reinterpret_cast<const double*>(smem + (size_t)(g & 1) * TL_TAB_BUF);
-            mbar_wait(&tab_full[g & 1], (g >> 1) & 1u);
-            const uint32_t p_end = pk_base[sub0 + (size_t)k * TL_WARPS + 1];
-            for (uint32_t p = pk_base[sub0 + (size_t)k * TL_WARPS]; p < p_end; ++p) {
-                const uint32_t s = cons_c % RING_STAGES;
-                mbar_wait(&my_bar[s], (cons_c / RING_STAGES) & 1u);
-                tiled_packet<WITH_E>(my_ring + (size_t)s * STAGE_BYTES, tab, acc, lane, w, st, Q);
-                __syncwarp();
-                ++cons_c;
-                issue_one();  // refill the stage just drained
-            }
-            // hand the table buffer over: the last warp to finish tile k starts the copy of tile k + 2 into it.  No
-            // CTA barrier: cells never change warps, so accumulators need none, and warps drift by at most two tiles.
             __syncwarp();
             if (lane == 0) {
                 const unsigned int done = atomicAdd(&tab_done[g & 1], 1u);
@@ -418,6 +417,34 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
                     }
                 }
             }
+        };
+        // every warp walks every tile of the item in order (waits for its table, leaves it), with or without packets
+        uint32_t k = 0;
+        mbar_wait(&tab_full[g_tile & 1], (g_tile >> 1) & 1u);
+        for (uint32_t i = 0; i < np; ++i) {
+            const uint32_t s = cons_c % RING_STAGES;
+            mbar_wait(&my_bar[s], (cons_c / RING_STAGES) & 1u);
+            const unsigned char* pk = my_ring + (size_t)s * STAGE_BYTES;
+            const uint32_t kt = reinterpret_cast<const uint32_t*>(pk)[1] - t0;  // tile of this packet, item-local
+#ifdef CLX_TILED_DEBUG
+            if (lane == 0 && (kt >= ntile || kt < k))
+                printf("bad tile: blk %d w %d item %u i %u kt %u k %u ntile %u\n", blockIdx.x, w, item, i, kt, k, ntile);
+#endif
+            while (k < kt) {
+                leave_tile(k);
+                ++k;
+                mbar_wait(&tab_full[(g_tile + k) & 1], ((g_tile + k) >> 1) & 1u);
+            }
+            const double* tab = reinterpret_cast<const double*>(smem + (size_t)((g_tile + k) & 1) * TL_TAB_BUF);
+            tiled_packet<WITH_E>(pk, tab, acc, lane, w, st, Q);
+            __syncwarp();
+            ++cons_c;
+            issue(i + RING_STAGES);  // refill the stage just drained
+        }
+        for (;;) {
+            leave_tile(k);
+            if (++k >= ntile) break;
+            mbar_wait(&tab_full[(g_tile + k) & 1], ((g_tile + k) >> 1) & 1u);
         }
         g_tile += ntile;
         __syncthreads();  // every warp has added its last run
@@ -495,11 +522,11 @@ int score_tiled(clx_ctx* c, int table, bool with_e, bool em_outputs) {
     if (c->tl_n_items) {
         const unsigned grid = std::min<unsigned>(c->tl_n_items, (unsigned)c->sm_count);
         if (with_e)
-            k_score_tiled<true><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_q.p, c->tl_pk_base.p, c->tl_items.p,
+            k_score_tiled<true><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_d.p, c->tl_pk_base.p, c->tl_items.p,
                                                                     c->tl_n_items, c->tl_order.p, c->tl_counter.p, tab, c->tl_nT, c->tl_NB,
                                                                     c->tl_part.p);
         else
-            k_score_tiled<false><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_q.p, c->tl_pk_base.p, c->tl_items.p,
+            k_score_tiled<false><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_d.p, c->tl_pk_base.p, c->tl_items.p,
                                                                      c->tl_n_items, c->tl_order.p, c->tl_counter.p, tab, c->tl_nT, c->tl_NB,
                                                                      c->tl_part.p);
         c->launches++;
@@ -623,7 +650,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt64, run_start.p, (int)R, s));
         CLX_CUDA(c, tmp.alloc(tb));
         CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, cnt64, run_start.p, (int)R, s));
-        k_run_keys<<<(R + TPB - 1) / TPB, TPB, 0, s>>>(ukeys.p, counts.p, R, key2.p, ridx.p, too_long.p);
+        k_run_keys<<<(R + TPB - 1) / TPB, TPB, 0, s>>>(ukeys.p, counts.p, R, c->tl_nT, key2.p, ridx.p, too_long.p);
         int bits2 = 17;
         while (bits2 < 63 && (1ull << bits2) <= (n_sub << 16)) ++bits2;
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tb, key2.p, key2_sorted.p, ridx.p, ridx_sorted.p, (int)R, 0, bits2, s));
@@ -633,7 +660,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     }
     k_sub_runs<<<(unsigned)((n_sub + 1 + TPB - 1) / TPB), TPB, 0, s>>>(key2_sorted.p, R, n_sub, sub_run.p);
     k_sub_count<<<(unsigned)((n_sub + 1 + TPB - 1) / TPB), TPB, 0, s>>>(sub_run.p, ridx_sorted.p, counts.p, n_sub, n_pk.p, n_quads.p);
-    k_unit_cost<<<(n_units + TPB - 1) / TPB, TPB, 0, s>>>(n_quads.p, n_units, unit_entries.p);
+    k_unit_cost<<<(n_units + TPB - 1) / TPB, TPB, 0, s>>>(n_quads.p, n_units, c->tl_nT, unit_entries.p);
     CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tb, n_pk.p, c->tl_pk_base.p, (int)(n_sub + 1), s));
     CLX_CUDA(c, tmp.alloc(tb));
     CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, n_pk.p, c->tl_pk_base.p, (int)(n_sub + 1), s));
@@ -657,14 +684,13 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     }
     c->tl_stream_len = (uint64_t)total_q * 4;  // in 4-byte words
     CLX_CUDA(c, c->tl_stream.alloc(c->tl_stream_len + 4));
-    CLX_CUDA(c, c->tl_pk_q.alloc((size_t)n_packets + 2));
+    CLX_CUDA(c, c->tl_pk_d.alloc((size_t)n_packets + 2));
     if (n_packets) {
         k_sub_fill<<<(unsigned)((n_sub * 32 + TPB - 1) / TPB), TPB, 0, s>>>(sub_run.p, c->tl_pk_base.p, q_base.p, ridx_sorted.p, ukeys.p,
-                                                                          counts.p, run_start.p, vals_sorted.p, n_sub, c->tl_pk_q.p,
-                                                                          c->tl_stream.p);
+                                                                          counts.p, run_start.p, vals_sorted.p, n_sub, c->tl_nT,
+                                                                          c->tl_pk_d.p, c->tl_stream.p);
         c->launches++;
     }
-    CLX_CUDA(c, cudaMemcpyAsync(c->tl_pk_q.p + n_packets, &total_q, 4, cudaMemcpyHostToDevice, s));
     CLX_CUDA(c, cudaStreamSynchronize(s));
 
     const char* env_it = getenv("CLX_TILED_ITEMS_PER_SM");
@@ -738,7 +764,7 @@ extern "C" int clx_debug_tiled_sizes(clx_ctx* c, uint64_t* out8) {
     if (!c || !out8) return CLX_ERR_ARG;
     out8[0] = c->tiled_ready ? 1 : 0;
     out8[1] = c->tl_stream_len;
-    out8[2] = c->tl_pk_q.n;
+    out8[2] = c->tl_pk_d.n;
     out8[3] = c->tl_pk_base.n;
     out8[4] = c->tl_n_items;
     out8[5] = c->tl_NB;
@@ -746,11 +772,11 @@ extern "C" int clx_debug_tiled_sizes(clx_ctx* c, uint64_t* out8) {
     out8[7] = c->tl_n_light;
     return CLX_OK;
 }
-extern "C" int clx_debug_tiled_copy(clx_ctx* c, uint32_t* stream, uint32_t* pk_q, uint32_t* pk_base, uint32_t* items) {
+extern "C" int clx_debug_tiled_copy(clx_ctx* c, uint32_t* stream, uint32_t* pk_d, uint32_t* pk_base, uint32_t* items) {
     if (!c || !c->tiled_ready) return CLX_ERR_STATE;
     cudaStreamSynchronize(c->stream);
     if (stream) cudaMemcpy(stream, c->tl_stream.p, c->tl_stream_len * 4, cudaMemcpyDeviceToHost);
-    if (pk_q) cudaMemcpy(pk_q, c->tl_pk_q.p, c->tl_pk_q.n * 4, cudaMemcpyDeviceToHost);
+    if (pk_d) cudaMemcpy(pk_d, c->tl_pk_d.p, c->tl_pk_d.n * 8, cudaMemcpyDeviceToHost);
     if (pk_base) cudaMemcpy(pk_base, c->tl_pk_base.p, c->tl_pk_base.n * 4, cudaMemcpyDeviceToHost);
     if (items) cudaMemcpy(items, c->tl_items.p, (size_t)c->tl_n_items * 16, cudaMemcpyDeviceToHost);
     return cudaGetLastError() == cudaSuccess ? CLX_OK : CLX_ERR_CUDA;
