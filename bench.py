@@ -312,7 +312,9 @@ def main():
     achieved = algo_bytes / k_s / 1e9 if sc_ms > 0 else 0.0
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "score_kernel_traffic.json"))).get("dram_bytes_per_launch")
+        tj = json.load(open(os.path.join(ROOT, "profiles", "score_kernel_traffic.json")))
+        if tj.get("workload") == args.workload and world == 1:  # the capture is of this workload on one GPU
+            traffic = tj.get("dram_bytes_per_launch")
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
