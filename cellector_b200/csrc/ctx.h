@@ -134,9 +134,10 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> tl_stream;                  // [tl_stream_len] packets of runs (tiled.cu), 4-byte words
     clx::DevBuf<uint2> tl_pk_d;                       // [n_packets] packet descriptors {start, size}, in quads (16 B)
     clx::DevBuf<uint32_t> tl_pk_base;                 // [n_sub + 1] first packet of every (cell block, warp, tile) sub-unit
-    clx::DevBuf<uint32_t> tl_items;                   // [n_items][4] cell block, first tile, end tile, -
+    clx::DevBuf<uint4> tl_item_q;                     // [n_items] work queue, largest first: cell block, first tile, n tiles, item id
+    clx::DevBuf<uint2> tl_item_pk;                    // [n_items][TL_WARPS] per queue slot and warp: first packet, n packets
+    uint32_t tl_grid = 0;                             // CTAs of k_score_tiled (the first tl_grid queue slots are taken statically)
     clx::DevBuf<uint32_t> tl_cb_item;                 // [Pc + 1] first item of every cell block
-    clx::DevBuf<uint32_t> tl_order;                   // [n_items] items by decreasing entry count (work-queue order)
     clx::DevBuf<uint32_t> tl_counter;                 // [1] work-queue cursor (k_score_finish re-arms it)
     clx::DevBuf<double> tl_part;                      // [n_items][NB][2] per-item partial (log_pmf, expected) sums
     clx::DevBuf<double> tab13;                        // [3][nT * TILE_L][13] compact memo records for the tiled kernel

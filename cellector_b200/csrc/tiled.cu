@@ -315,12 +315,26 @@ __device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ p
     }
 }
 
+// per queue slot and warp: the warp's packet range over the item's tiles (one consecutive range, see sub_unit_of)
+__global__ void k_item_pk(const uint4* __restrict__ item_q, uint32_t n_items, const uint32_t* __restrict__ pk_base, uint32_t nT,
+                          uint2* __restrict__ item_pk) {
+    const uint32_t q = blockIdx.x, w = threadIdx.x;
+    if (q >= n_items || w >= (uint32_t)TL_WARPS) return;
+    const uint4 it = item_q[q];
+    const size_t su0 = ((size_t)it.x * TL_WARPS + w) * nT + it.y;
+    const uint32_t P0 = pk_base[su0];
+    item_pk[(size_t)q * TL_WARPS + w] = make_uint2(P0, pk_base[su0 + it.z] - P0);
+}
+
+// Work queue: CTA b takes queue slot b first, later slots come from an atomic cursor that starts at gridDim.x; the
+// cursor for the NEXT item is fetched while the current one is being scored, so no item waits for the atomic.  The
+// start of an item costs two dependent global loads (slot record + packet range, then the descriptor window) before
+// the first bulk copy goes out.
 template <bool WITH_E>
 __global__ void __launch_bounds__(TL_WARPS * 32, 1)
-    k_score_tiled(const uint32_t* __restrict__ stream, const uint2* __restrict__ pk_d, const uint32_t* __restrict__ pk_base,
-                  const uint32_t* __restrict__ items, uint32_t n_items, const uint32_t* __restrict__ order,
-                  uint32_t* __restrict__ counter, const double* __restrict__ tab13, uint32_t nT, uint32_t NB,
-                  double* __restrict__ part) {
+    k_score_tiled(const uint32_t* __restrict__ stream, const uint2* __restrict__ pk_d, const uint4* __restrict__ item_q,
+                  const uint2* __restrict__ item_pk, uint32_t n_items, uint32_t* __restrict__ counter,
+                  const double* __restrict__ tab13, uint32_t NB, double* __restrict__ part) {
     extern __shared__ __align__(128) unsigned char smem[];
     double2* acc = reinterpret_cast<double2*>(smem + 2 * TL_TAB_BUF);
     unsigned char* ring = smem + 2 * TL_TAB_BUF + TL_ACC_BYTES;
@@ -341,6 +355,7 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
         double* z = reinterpret_cast<double*>(smem + (size_t)(tid / TAB13) * TL_TAB_BUF) + (size_t)TILE_L * TAB13;
         z[tid % TAB13] = 0.0;
     }
+    for (uint32_t i = tid; i < 32u * Q; i += blockDim.x) acc[i] = make_double2(0.0, 0.0);
     __syncthreads();
     uint32_t g_tile = 0;  // tiles consumed by this CTA so far (buffer = g & 1, parity = (g >> 1) & 1)
     uint32_t cons_c = 0;  // packets consumed by this warp so far (stage = c % STAGES, parity = (c / STAGES) & 1)
@@ -351,24 +366,19 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
     st.sE = 0.0;
     st.cell = 0xFFFFu;
     __shared__ uint32_t s_next;
-    for (;;) {
-        // work queue: items are handed out largest first (the last statement of the body is a CTA barrier, so the slot
-        // is free to be rewritten here)
-        if (tid == 0) s_next = atomicAdd(counter, 1u);
-        __syncthreads();
-        const uint32_t qk = s_next;
-        if (qk >= n_items) break;
-        const uint32_t item = order[qk];
-        const uint32_t cb = items[4 * item], t0 = items[4 * item + 1], ntile = items[4 * item + 2] - t0;
-        // this warp's packets over the item's tiles are one consecutive range of the packet list (warp-major sub-units)
-        const size_t su0 = ((size_t)cb * TL_WARPS + w) * nT + t0;
-        const uint32_t P0 = pk_base[su0], np = pk_base[su0 + ntile] - P0;
+    uint32_t qk = blockIdx.x;
+    while (qk < n_items) {
+        uint32_t nxt = 0;
+        if (tid == 0) nxt = atomicAdd(counter, 1u);  // used at the end of this item
+        const uint4 it = item_q[qk];
+        const uint2 rng = item_pk[(size_t)qk * TL_WARPS + w];
+        const uint32_t t0 = it.y, ntile = it.z, item = it.w;
+        const uint32_t P0 = rng.x, np = rng.y;
         // descriptor window: lane l holds packet win0 + l (and win0 + 32 + l prefetched), one coalesced load per 32
         // packets; nothing on the packet path waits for a dependent global load
         uint32_t win0 = 0;
         uint2 dwin = lane < np ? pk_d[P0 + lane] : make_uint2(0u, 0u);
         uint2 dnxt = 32u + lane < np ? pk_d[P0 + 32u + lane] : make_uint2(0u, 0u);
-        for (uint32_t i = tid; i < 32u * Q; i += blockDim.x) acc[i] = make_double2(0.0, 0.0);
         if (tid == 0) {
             for (uint32_t k = 0; k < 2 && k < ntile; ++k) {
                 const uint32_t g = g_tile + k;
@@ -399,7 +409,6 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
             }
         };
         for (uint32_t i = 0; i < (uint32_t)RING_STAGES; ++i) issue(i);
-        __syncthreads();  // accumulators cleared
         // hand a table buffer over: the last warp to leave tile k starts the copy of tile k + 2 into it.  No CTA
         // barrier: cells never change warps, so accumulators need none, and warps drift by at most two tiles.
         auto leave_tile = [&](uint32_t k) {
@@ -447,9 +456,16 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
             mbar_wait(&tab_full[(g_tile + k) & 1], ((g_tile + k) >> 1) & 1u);
         }
         g_tile += ntile;
-        __syncthreads();  // every warp has added its last run
+        if (tid == 0) s_next = nxt;
+        __syncthreads();  // every warp has added its last run; the next queue slot is posted
+        // partials out, accumulators cleared for the next item in the same sweep
         double2* dst = reinterpret_cast<double2*>(part) + (size_t)item * NB;
-        for (uint32_t i = tid; i < NB; i += blockDim.x) dst[i] = acc[acc_slot(i, Q)];
+        for (uint32_t i = tid; i < 32u * Q; i += blockDim.x) {
+            const uint32_t slot = acc_slot(i, Q);
+            if (i < NB) dst[i] = acc[slot];
+            acc[slot] = make_double2(0.0, 0.0);
+        }
+        qk = s_next;
         __syncthreads();
     }
 }
@@ -465,8 +481,8 @@ __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__
                                                       const uint32_t* __restrict__ n_used, double* __restrict__ ll,
                                                       double* __restrict__ ell, uint32_t* __restrict__ nloci,
                                                       double* __restrict__ norm, unsigned int* __restrict__ nan_flag,
-                                                      uint32_t* __restrict__ queue_counter) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) *queue_counter = 0u;  // re-arm the work queue of k_score_tiled
+                                                      uint32_t* __restrict__ queue_counter, uint32_t first_round) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) *queue_counter = first_round;  // re-arm the work queue of k_score_tiled
     // lanes 0..3 of a warp take cells c0..c0+3 for sub 0, lanes 4..7 the same cells for sub 1, ...: partial loads of one
     // sub are 4 consecutive double2 (64 B)
     const uint32_t warp_cell0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / FIN_LANES);
@@ -520,15 +536,13 @@ int score_tiled(clx_ctx* c, int table, bool with_e, bool em_outputs) {
     }
     const double* tab = c->tab13.p + (size_t)table * c->tl_nT * TILE_L * TAB13;
     if (c->tl_n_items) {
-        const unsigned grid = std::min<unsigned>(c->tl_n_items, (unsigned)c->sm_count);
+        const unsigned grid = c->tl_grid;
         if (with_e)
-            k_score_tiled<true><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_d.p, c->tl_pk_base.p, c->tl_items.p,
-                                                                    c->tl_n_items, c->tl_order.p, c->tl_counter.p, tab, c->tl_nT, c->tl_NB,
-                                                                    c->tl_part.p);
+            k_score_tiled<true><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_d.p, c->tl_item_q.p, c->tl_item_pk.p,
+                                                                    c->tl_n_items, c->tl_counter.p, tab, c->tl_NB, c->tl_part.p);
         else
-            k_score_tiled<false><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_d.p, c->tl_pk_base.p, c->tl_items.p,
-                                                                     c->tl_n_items, c->tl_order.p, c->tl_counter.p, tab, c->tl_nT, c->tl_NB,
-                                                                     c->tl_part.p);
+            k_score_tiled<false><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_d.p, c->tl_item_q.p, c->tl_item_pk.p,
+                                                                     c->tl_n_items, c->tl_counter.p, tab, c->tl_NB, c->tl_part.p);
         c->launches++;
         CLX_DEBUG_SYNC(c, "k_score_tiled");
     }
@@ -537,10 +551,11 @@ int score_tiled(clx_ctx* c, int table, bool with_e, bool em_outputs) {
     if (em_outputs)
         k_score_finish<true><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, hv, c->hv_e.p,
                                                   c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag,
-                                                  c->tl_counter.p);
+                                                  c->tl_counter.p, c->tl_grid);
     else
         k_score_finish<false><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, hv, nullptr, nullptr,
-                                                   c->ll.p + (size_t)table * N, nullptr, nullptr, nullptr, nullptr, c->tl_counter.p);
+                                                   c->ll.p + (size_t)table * N, nullptr, nullptr, nullptr, nullptr, c->tl_counter.p,
+                                                   c->tl_grid);
     c->launches++;
     return CLX_OK;
 }
@@ -734,17 +749,25 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         }
         cb_item.push_back((uint32_t)(items.size() / 4));
         c->tl_n_items = (uint32_t)(items.size() / 4);
-        CLX_CUDA(c, c->tl_items.alloc(items.size() + 4));
+        c->tl_grid = std::min<uint32_t>(c->tl_n_items, (uint32_t)c->sm_count);
+        CLX_CUDA(c, c->tl_item_q.alloc((size_t)c->tl_n_items + 1));
+        CLX_CUDA(c, c->tl_item_pk.alloc((size_t)c->tl_n_items * TL_WARPS + 1));
         CLX_CUDA(c, c->tl_cb_item.alloc(cb_item.size()));
         std::vector<uint32_t> order(c->tl_n_items);
         for (uint32_t i = 0; i < c->tl_n_items; ++i) order[i] = i;
         std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_entries[a] > item_entries[b]; });
-        CLX_CUDA(c, c->tl_order.alloc(order.size() + 1));
+        std::vector<uint4> queue(c->tl_n_items);  // largest first
+        for (uint32_t q = 0; q < c->tl_n_items; ++q) {
+            const uint32_t i = order[q];
+            queue[q] = make_uint4(items[4 * i], items[4 * i + 1], items[4 * i + 2] - items[4 * i + 1], i);
+        }
         CLX_CUDA(c, c->tl_counter.alloc(1));
-        CLX_CUDA(c, cudaMemsetAsync(c->tl_counter.p, 0, 4, s));
-        if (!order.empty()) CLX_CUDA(c, cudaMemcpyAsync(c->tl_order.p, order.data(), order.size() * 4, cudaMemcpyHostToDevice, s));
-        if (!items.empty())
-            CLX_CUDA(c, cudaMemcpyAsync(c->tl_items.p, items.data(), items.size() * 4, cudaMemcpyHostToDevice, s));
+        CLX_CUDA(c, cudaMemcpyAsync(c->tl_counter.p, &c->tl_grid, 4, cudaMemcpyHostToDevice, s));
+        if (!queue.empty()) {
+            CLX_CUDA(c, cudaMemcpyAsync(c->tl_item_q.p, queue.data(), queue.size() * sizeof(uint4), cudaMemcpyHostToDevice, s));
+            k_item_pk<<<c->tl_n_items, TL_WARPS, 0, s>>>(c->tl_item_q.p, c->tl_n_items, c->tl_pk_base.p, c->tl_nT, c->tl_item_pk.p);
+            c->launches++;
+        }
         CLX_CUDA(c, cudaMemcpyAsync(c->tl_cb_item.p, cb_item.data(), cb_item.size() * 4, cudaMemcpyHostToDevice, s));
         CLX_CUDA(c, cudaStreamSynchronize(s));
     }
@@ -772,12 +795,12 @@ extern "C" int clx_debug_tiled_sizes(clx_ctx* c, uint64_t* out8) {
     out8[7] = c->tl_n_light;
     return CLX_OK;
 }
-extern "C" int clx_debug_tiled_copy(clx_ctx* c, uint32_t* stream, uint32_t* pk_d, uint32_t* pk_base, uint32_t* items) {
+extern "C" int clx_debug_tiled_copy(clx_ctx* c, uint32_t* stream, uint32_t* pk_d, uint32_t* pk_base, uint32_t* item_q) {
     if (!c || !c->tiled_ready) return CLX_ERR_STATE;
     cudaStreamSynchronize(c->stream);
     if (stream) cudaMemcpy(stream, c->tl_stream.p, c->tl_stream_len * 4, cudaMemcpyDeviceToHost);
     if (pk_d) cudaMemcpy(pk_d, c->tl_pk_d.p, c->tl_pk_d.n * 8, cudaMemcpyDeviceToHost);
     if (pk_base) cudaMemcpy(pk_base, c->tl_pk_base.p, c->tl_pk_base.n * 4, cudaMemcpyDeviceToHost);
-    if (items) cudaMemcpy(items, c->tl_items.p, (size_t)c->tl_n_items * 16, cudaMemcpyDeviceToHost);
+    if (item_q) cudaMemcpy(item_q, c->tl_item_q.p, (size_t)c->tl_n_items * 16, cudaMemcpyDeviceToHost);
     return cudaGetLastError() == cudaSuccess ? CLX_OK : CLX_ERR_CUDA;
 }
