@@ -148,7 +148,7 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
         const int R = t256 ? 1 : (n_vals <= cap1 ? 1 : (n_vals <= 4 * cap1 ? 4 : 16));
         const int threads = t256 ? 256 : SELECT_SMALL_THREADS;
         const uint64_t per_cta = (uint64_t)threads * R;
-        CLX_CUDA(c, cudaMemsetAsync(c->sel_hist.p, 0, c->sel_hist.bytes(), s));
+        // the histogram scratch was zeroed at the head of the iteration (k_tables_em)
         const unsigned grid = (unsigned)std::max<uint64_t>(1, (n_vals + per_cta - 1) / per_cta);
         const double* norm_local = c->norm.p;
         const IterParams* prm = c->d_params.p;
@@ -175,7 +175,6 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
     SelectState* d_state = (SelectState*)c->sel_state.p;
     unsigned int* hist = c->sel_hist.p;
     unsigned int* ticket = hist + 8 * SELECT_TARGETS * 256;
-    CLX_CUDA(c, cudaMemsetAsync(hist, 0, c->sel_hist.bytes(), s));
     const unsigned grid = (unsigned)std::min<uint64_t>((n_vals + 512 * 8 - 1) / (512 * 8), (uint64_t)c->sm_count * 2);
     k_select_keys<<<grid, 512, 0, s>>>(vals, n_vals, keys, plan, d_state);
     for (int pass = 0; pass < 8; ++pass)
@@ -293,10 +292,12 @@ int enqueue_iteration(clx_ctx* c) {
     phase_begin(c, CLX_PHASE_TABLES);
     if (L) {
         k_tables_em<<<(unsigned)((3ull * L + TPB - 1) / TPB), TPB, 0, s>>>(cnts, L, make_lbc(c), with_e, c->tab.p,
-                                                                           c->tiled_ready ? c->tab13.p : nullptr, c->d_stats.p);
+                                                                           c->tiled_ready ? c->tab13.p : nullptr, c->d_stats.p,
+                                                                           c->sel_hist.p, (uint32_t)c->sel_hist.n);
         c->launches++;
     } else {
         CLX_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, sizeof(DeviceStats), s));
+        CLX_CUDA(c, cudaMemsetAsync(c->sel_hist.p, 0, c->sel_hist.bytes(), s));
     }
     phase_end(c, CLX_PHASE_TABLES);
     CLX_DEBUG_SYNC(c, "k_tables");

@@ -288,13 +288,16 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
 // 0 also clears the per-iteration DeviceStats.
 __global__ void __launch_bounds__(256) k_tables_em(EmCounts cnts, uint32_t n_loci, Lbc10 lbc, int with_expected,
                                                    double* __restrict__ tab, double* __restrict__ tab13,
-                                                   DeviceStats* __restrict__ st_clear) {
+                                                   DeviceStats* __restrict__ st_clear, unsigned int* __restrict__ zero_buf,
+                                                   uint32_t zero_words) {
     __shared__ double s_lbc[10];
     if (threadIdx.x < 10) s_lbc[threadIdx.x] = lbc.v[threadIdx.x];
     if (st_clear != nullptr && blockIdx.x == 0 && threadIdx.x < sizeof(DeviceStats) / 8)
         reinterpret_cast<unsigned long long*>(st_clear)[threadIdx.x] = 0ull;
     __syncthreads();
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    // the select's histogram scratch of this iteration (saves a memset node in the iteration graph)
+    for (uint32_t i = t; i < zero_words; i += gridDim.x * blockDim.x) zero_buf[i] = 0u;
     const uint32_t l = t / 3u;
     const int n = (int)(t % 3u) + 1;
     if (l >= n_loci) return;
