@@ -120,9 +120,6 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> h_row_ptr;                      // [n_cells + 1]
     clx::DevBuf<uint32_t> hc_perm;                        // [n_heavy] CSC order -> index into the CSR-order lists
     clx::DevBuf<uint32_t> hc_col_ptr;                     // [n_loci + 1]
-    clx::DevBuf<uint32_t> hc_cell, hc_ref, hc_alt;        // [n_heavy] the heavy entries again, in CSC order (column pass)
-    clx::DevBuf<uint32_t> h2c;                            // [n_heavy] CSR-order index -> CSC-order index
-    clx::DevBuf<double> hv_c;                             // [n_heavy] EM-pass log_pmf of the heavy entries in CSC order
     clx::DevBuf<uint32_t> giant_idx;                      // [n_giant] heavy entries with total > HEAVY_GIANT_TOTAL
     uint32_t n_giant = 0;
     clx::DevBuf<double> hv_ll, hv_e;                      // [3 * n_heavy] values of the current scoring pass

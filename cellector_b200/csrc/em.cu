@@ -68,17 +68,6 @@ void launch_columns(clx_ctx* c, int G) {
     // sharded over peer memory: the partial sums go into this rank's window, where the slice owners read them
     double* out_ll = c->p2p ? reinterpret_cast<double*>((unsigned char*)c->win + c->win_off_part_ll) : c->loc_ll.p;
     unsigned long long* out_int = c->p2p ? reinterpret_cast<unsigned long long*>((unsigned char*)c->win + c->win_off_part_int) : c->loc_int.p;
-    // k_columns_w (one warp per column, software-pipelined) measured slower than the G-lanes-per-column kernel on
-    // B200 at both bench sizes (C2: 33 vs 28 us, C3 shard: 197 vs 150 us): opt-in until that is understood
-    static const int warp_cols = env_int("CLX_COLUMNS_W", 0);
-    if (warp_cols) {
-        const unsigned grid = std::min<unsigned>((n + COLW_WARPS - 1) / COLW_WARPS, (unsigned)c->sm_count * (unsigned)env_int("CLX_COLW_CTAS", 3));
-        k_columns_w<FUSE><<<grid, COLW_WARPS * 32, 0, c->stream>>>(
-            c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_cell.p, c->hc_ref.p,
-            c->hc_alt.p, c->hv_c.p, out_ll, out_int, c->n_used.p, c->d_stats.p);
-        c->launches++;
-        return;
-    }
 #define CLX_COLS(GG)                                                                                                   \
     k_columns<GG, FUSE><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                          \
         c->csc.p, c->col_ptr.p, n, c->tab.p, c->loci_used.p, c->excl_bits.p, c->hc_col_ptr.p, c->hc_perm.p,            \
@@ -132,13 +121,7 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
     const SelectPlan plan = make_plan(n_real);
     cudaStream_t s = c->stream;
     const uint32_t N = c->n_cells;
-    static const int mode = env_int("CLX_SELECT_MODE", 0);  // 0/1 cooperative kernel, 2 forces the multi-launch path, 3 the one-CTA kernel
-    if (mode == 3 && n_vals <= SELECT_SMALL_MAX && vals == c->norm.p) {  // one CTA, exclusion fused (kept for comparison)
-        k_select_small<<<1, SELECT_SMALL_THREADS, 0, s>>>(vals, (uint32_t)n_vals, plan, c->d_params.p,
-                                                                         c->d_stats.p, c->norm.p, N, c->excl_bits.p);
-        c->launches++;
-        return CLX_OK;
-    }
+    static const int mode = env_int("CLX_SELECT_MODE", 0);  // 0 cooperative kernel, 2 forces the multi-launch path
     // cooperative grid, keys in registers, one launch: as few keys per thread as one CTA per SM allows (1, 4 or 16);
     // 256-thread CTAs for small inputs measured slightly slower (29.8 vs 27.9 us at 10 k keys): opt-in
     const uint64_t cap1 = (uint64_t)SELECT_SMALL_THREADS * (uint64_t)c->sm_count;
@@ -207,8 +190,6 @@ int em_alloc(clx_ctx* c) {
     CLX_CUDA(c, c->post_u8.alloc(3 * N + 1));
     const size_t n_sel = c->world > 1 ? (size_t)c->world * c->max_local_cells : N;
     if (c->world > 1) CLX_CUDA(c, c->norm_all.alloc(n_sel + 1));
-    const size_t n_cta_keys = (size_t)SELECT_SMALL_THREADS * SELECT_R * (size_t)c->sm_count;
-    (void)n_cta_keys;
     CLX_CUDA(c, c->sel_keys.alloc(n_sel + 256));  // key array of the multi-launch path / survivor list
     CLX_CUDA(c, c->sel_hist.alloc(SELECT_COOP_SCRATCH + 8 * SELECT_TARGETS * 256 + 8));
     CLX_CUDA(c, c->sel_state.alloc(sizeof(SelectState) / 8 + 1));
@@ -275,12 +256,11 @@ int enqueue_iteration(clx_ctx* c) {
     auto heavy = [&]() -> int {
         if (!c->n_heavy) return CLX_OK;
         k_heavy_em<<<(unsigned)((c->n_heavy + HEAVY_HB - 1) / HEAVY_HB), TPB, 0, hs>>>(
-            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, c->h2c.p,
-            c->hv_c.p);
+            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
         c->launches++;
         if (c->n_giant) {
             k_heavy_giant<<<c->n_giant, TPB, 0, hs>>>(c->giant_idx.p, c->n_giant, c->h_locus.p, c->h_ref.p, c->h_alt.p, cnts,
-                                                      c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, c->h2c.p, c->hv_c.p);
+                                                      c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
             c->launches++;
         }
         return CLX_OK;

@@ -217,8 +217,7 @@ static __device__ __noinline__ double heavy_ll_k(uint64_t n, uint64_t k, double 
 __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                                        const uint32_t* __restrict__ h_alt, uint32_t n_heavy, EmCounts cnts,
                                                        const double* __restrict__ lnfact, int with_expected,
-                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e,
-                                                       const uint32_t* __restrict__ h2c, double* __restrict__ hv_c) {
+                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e) {
     const double* __restrict__ lng = cnts.lng;
     const uint32_t lng_n = cnts.lng_n;
     const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
@@ -235,7 +234,6 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
         if (!on) {
             hv_ll[h] = 0.0;
             hv_e[h] = 0.0;
-            hv_c[h2c[h]] = 0.0;
         } else {
             lgab = ln_gamma_int(((double)a + alpha) + ((double)(n - a) + beta), lng, lng_n);
         }
@@ -248,7 +246,6 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
             for (uint64_t k = 1; k <= n; ++k) ex = logsumexp2(ex, 2.0 * heavy_ll_k(n, k, alpha, beta, lgab, den, lnfact, lng, lng_n));
         }
         hv_ll[h] = own;
-        hv_c[h2c[h]] = own;
         hv_e[h] = ex;
     }
     // deep entries of this warp, one at a time over all 32 lanes
@@ -275,7 +272,6 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
         if ((int)lane == src) {
             const double own = heavy_ll_k(dn, da, dal, dbe, dlgab, dden, lnfact, lng, lng_n);
             hv_ll[dh] = own;
-            hv_c[h2c[dh]] = own;
             hv_e[dh] = ex;
         }
     }
@@ -349,8 +345,7 @@ __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict_
                                                      const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                                      const uint32_t* __restrict__ h_alt, EmCounts cnts,
                                                      const double* __restrict__ lnfact, int with_expected,
-                                                     double* __restrict__ hv_ll, double* __restrict__ hv_e,
-                                                     const uint32_t* __restrict__ h2c, double* __restrict__ hv_c) {
+                                                     double* __restrict__ hv_ll, double* __restrict__ hv_e) {
     __shared__ double s_m[8], s_s[8];
     const uint32_t h = giant_idx[blockIdx.x];
     double alpha, beta, den;
@@ -361,7 +356,6 @@ __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict_
     if (tid == 0) {
         const double v = log_beta_binomial_pmf_den((double)a, (double)r, alpha, beta, ln_binomial(n, a, lnfact), den);
         hv_ll[h] = v;
-        hv_c[h2c[h]] = v;
     }
     if (!with_expected) {
         if (tid == 0) hv_e[h] = 0.0;
@@ -636,196 +630,6 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
             if (f) atomicAdd(&st->n_loci_filtered, (unsigned long long)f);
             if (u) atomicAdd(&st->n_loci_in_use, (unsigned long long)u);
         }
-    }
-}
-
-// Lean variant of the column pass: ONE WARP PER COLUMN (persistent, warp-strided), one coalesced 8-byte load per
-// entry and lane (a warp load is 256 contiguous bytes), 32-bit indices relative to the column start, the column's
-// memo slots staged in shared memory per warp, majority counts derived from the totals (integers).  Same outputs
-// as k_columns; the old kernel spent ~100 instructions per 32 entries on 64-bit bounds checks.
-constexpr int COLW_WARPS = 8;
-constexpr int COLW_U = 4;
-struct ColAcc {
-    double s_min, s_maj;
-    uint32_t c_min, r_min, a_min, r_all, a_all;
-};
-__device__ __forceinline__ void colw_batch(const uint2 (&q)[COLW_U], uint32_t i0, uint32_t len, uint32_t lane,
-                                           const uint32_t* __restrict__ excl_bits, const double* __restrict__ rec, ColAcc& A) {
-    uint32_t w[COLW_U];
-#pragma unroll
-    for (int u = 0; u < COLW_U; ++u) w[u] = __ldg(excl_bits + (q[u].x >> 5));  // cell 0 for a slot past the end: a valid address
-#pragma unroll
-    for (int u = 0; u < COLW_U; ++u) {
-        const bool valid = i0 + 32u * u + lane < len;
-        const bool ex = valid && ((w[u] >> (q[u].x & 31u)) & 1u);
-        const uint32_t r = q[u].y & 0xFFFFu, a = q[u].y >> 16, n = r + a;
-        const bool light = (n - 1u) < (uint32_t)K_LIGHT;  // a slot past the end has n = 0; zero totals / the heavy marker are not light
-        const double v = light ? rec[((n - 1u) << 2) + a] : 0.0;
-        const uint32_t rl = light ? r : 0u, al = light ? a : 0u;
-        A.c_min += ex ? 1u : 0u;
-        A.s_min += ex ? v : 0.0;
-        A.s_maj += ex ? 0.0 : v;
-        A.r_min += ex ? rl : 0u;
-        A.a_min += ex ? al : 0u;
-        A.r_all += rl;
-        A.a_all += al;
-    }
-}
-// Software pipeline per warp: column pointers are fetched two columns ahead, the first COLW_U x 32 entries, the memo
-// slots and the tail operands (heavy range, in-use flag) one column ahead, so a warp always has a column's worth of
-// loads in flight while it sums the current one.
-template <bool FUSE_FILTER>
-__global__ void __launch_bounds__(COLW_WARPS * 32) k_columns_w(
-    const ColEntry* __restrict__ csc, const uint64_t* __restrict__ col_ptr, uint32_t n_loci, const double* __restrict__ tab,
-    uint8_t* __restrict__ used, const uint32_t* __restrict__ excl_bits, const uint32_t* __restrict__ hc_col_ptr,
-    const uint32_t* __restrict__ hc_cell, const uint32_t* __restrict__ hc_ref, const uint32_t* __restrict__ hc_alt,
-    const double* __restrict__ hv_c, double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int,
-    uint32_t* __restrict__ n_used, DeviceStats* __restrict__ st) {
-    constexpr int U = COLW_U;
-    __shared__ double s_rec[COLW_WARPS][12];
-    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
-    const uint32_t n_warps = gridDim.x * COLW_WARPS;
-    const size_t L = n_loci;
-    uint32_t f_cnt = 0, u_cnt = 0;
-    uint32_t l = blockIdx.x * COLW_WARPS + wib;
-    if (l >= n_loci) return;
-    uint32_t ln = l + n_warps;
-    uint64_t b0 = __ldg(col_ptr + l), e0 = __ldg(col_ptr + l + 1), b1 = 0, e1 = 0;
-    if (ln < n_loci) {
-        b1 = __ldg(col_ptr + ln);
-        e1 = __ldg(col_ptr + ln + 1);
-    }
-    uint2 q[U], qn[U];
-    double recv = 0.0, recn = 0.0;
-    uint32_t tp = 0, tpn = 0;  // lane 0: first heavy entry, lane 1: end of the heavy range, lane 2: in-use flag
-    auto prefetch = [&](uint32_t col, uint64_t begin, uint64_t end, uint2 (&dst)[U], double& rv, uint32_t& t) {
-        const uint32_t len = (uint32_t)(end - begin);
-        const uint2* __restrict__ p = reinterpret_cast<const uint2*>(csc + begin);
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const uint32_t idx = 32u * u + lane;
-            dst[u] = idx < len ? __ldg(p + idx) : make_uint2(0u, 0u);
-        }
-        rv = lane < 12 ? __ldg(tab + (size_t)col * TAB_STRIDE + lane) : 0.0;
-        t = lane < 2 ? __ldg(hc_col_ptr + col + lane) : (lane == 2 ? (uint32_t)used[col] : 0u);
-    };
-    prefetch(l, b0, e0, q, recv, tp);
-    for (;;) {
-        const uint32_t l2 = ln + n_warps;
-        uint64_t b2 = 0, e2 = 0;
-        if (ln < n_loci && l2 < n_loci) {
-            b2 = __ldg(col_ptr + l2);
-            e2 = __ldg(col_ptr + l2 + 1);
-        }
-        if (ln < n_loci) prefetch(ln, b1, e1, qn, recn, tpn);
-        // ---- current column
-        if (lane < 12) s_rec[wib][lane] = recv;
-        __syncwarp();
-        const uint32_t len = (uint32_t)(e0 - b0);
-        const uint2* __restrict__ p = reinterpret_cast<const uint2*>(csc + b0);
-        const uint32_t hb = __shfl_sync(0xffffffffu, tp, 0), he = __shfl_sync(0xffffffffu, tp, 1);
-        const bool on = __shfl_sync(0xffffffffu, tp, 2) != 0;  // entries were scored only if the locus was in use (main.rs:556)
-        // the column's heavy entries (CSC-ordered side arrays), one per lane: loads issued before the light entries are summed
-        uint32_t hcell = 0, href = 0, halt = 0;
-        double hval = 0.0;
-        if (hb + lane < he) {
-            hcell = __ldg(hc_cell + hb + lane);
-            href = __ldg(hc_ref + hb + lane);
-            halt = __ldg(hc_alt + hb + lane);
-            hval = __ldg(hv_c + hb + lane);
-        }
-        ColAcc A = {0.0, 0.0, 0u, 0u, 0u, 0u, 0u};
-        colw_batch(q, 0u, len, lane, excl_bits, s_rec[wib], A);
-        for (uint32_t i0 = 32u * U; i0 < len; i0 += 32u * U) {
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const uint32_t idx = i0 + 32u * u + lane;
-                q[u] = idx < len ? __ldg(p + idx) : make_uint2(0u, 0u);
-            }
-            colw_batch(q, i0, len, lane, excl_bits, s_rec[wib], A);
-        }
-        unsigned long long hR_min = 0, hA_min = 0, hR_all = 0, hA_all = 0;
-        if (he > hb) {  // warp-uniform
-            for (uint32_t base = hb; base < he; base += 32u) {
-                if (base != hb && base + lane < he) {
-                    hcell = __ldg(hc_cell + base + lane);
-                    href = __ldg(hc_ref + base + lane);
-                    halt = __ldg(hc_alt + base + lane);
-                    hval = __ldg(hv_c + base + lane);
-                }
-                if (base + lane < he) {
-                    const bool ex = (__ldg(excl_bits + (hcell >> 5)) >> (hcell & 31u)) & 1u;
-                    A.s_min += ex ? hval : 0.0;
-                    A.s_maj += ex ? 0.0 : hval;
-                    hR_min += ex ? href : 0u;
-                    hA_min += ex ? halt : 0u;
-                    hR_all += href;
-                    hA_all += halt;
-                }
-            }
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                hR_min += __shfl_xor_sync(0xffffffffu, hR_min, off);
-                hA_min += __shfl_xor_sync(0xffffffffu, hA_min, off);
-                hR_all += __shfl_xor_sync(0xffffffffu, hR_all, off);
-                hA_all += __shfl_xor_sync(0xffffffffu, hA_all, off);
-            }
-        }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            A.s_min += __shfl_xor_sync(0xffffffffu, A.s_min, off);
-            A.s_maj += __shfl_xor_sync(0xffffffffu, A.s_maj, off);
-            A.c_min += __shfl_xor_sync(0xffffffffu, A.c_min, off);
-            A.r_min += __shfl_xor_sync(0xffffffffu, A.r_min, off);
-            A.a_min += __shfl_xor_sync(0xffffffffu, A.a_min, off);
-            A.r_all += __shfl_xor_sync(0xffffffffu, A.r_all, off);
-            A.a_all += __shfl_xor_sync(0xffffffffu, A.a_all, off);
-        }
-        bool filtered = false;
-        if (lane == 0) {
-            const double s_min = A.s_min, s_maj = A.s_maj;
-            const uint32_t c_min = A.c_min, c_maj = len - A.c_min;
-            const unsigned long long R_min = A.r_min + hR_min, A_min = A.a_min + hA_min,
-                                     R_maj = (A.r_all - A.r_min) + (hR_all - hR_min), A_maj = (A.a_all - A.a_min) + (hA_all - hA_min);
-            loc_ll[l] = on ? s_min : 0.0;
-            loc_ll[L + l] = on ? s_maj : 0.0;
-            loc_int[0 * L + l] = on ? c_min : 0;
-            loc_int[1 * L + l] = on ? c_maj : 0;
-            loc_int[2 * L + l] = on ? R_min : 0;
-            loc_int[3 * L + l] = on ? A_min : 0;
-            loc_int[4 * L + l] = on ? R_maj : 0;
-            loc_int[5 * L + l] = on ? A_maj : 0;
-            loc_int[6 * L + l] = R_min;  // init_alpha_betas subtracts every stored entry of an excluded cell (main.rs:603-608)
-            loc_int[7 * L + l] = A_min;
-            if (FUSE_FILTER) {  // main.rs:431-451 on this locus
-                const double per_cell = (on && c_min != 0) ? s_min / (double)c_min : 0.0;
-                if (per_cell < -80.0) {
-                    filtered = on;
-                    used[l] = 0;
-                    f_cnt += on ? 1u : 0u;
-                } else {
-                    u_cnt += on ? 1u : 0u;
-                }
-            }
-        }
-        if (FUSE_FILTER) {
-            // a locus switched off now stops counting toward loci_used_per_cell (main.rs:575) of the cells it covers
-            if (__shfl_sync(0xffffffffu, filtered ? 1 : 0, 0))
-                for (uint32_t i = lane; i < len; i += 32u) atomicSub(&n_used[p[i].x], 1u);
-        }
-        __syncwarp();  // s_rec[wib] is rewritten for the next column
-        if (ln >= n_loci) break;
-        l = ln;
-        ln = l2;
-        b0 = b1; e0 = e1; b1 = b2; e1 = e2;
-#pragma unroll
-        for (int u = 0; u < U; ++u) q[u] = qn[u];
-        recv = recn;
-        tp = tpn;
-    }
-    if (FUSE_FILTER && lane == 0) {
-        if (f_cnt) atomicAdd(&st->n_loci_filtered, (unsigned long long)f_cnt);
-        if (u_cnt) atomicAdd(&st->n_loci_in_use, (unsigned long long)u_cnt);
     }
 }
 

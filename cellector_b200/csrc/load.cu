@@ -171,18 +171,6 @@ __global__ void k_lng_build(double* __restrict__ lng, uint32_t n) {
     if (i < n) lng[i] = i == 0 ? INFINITY : ln_gamma((double)i);
 }
 
-// the heavy lists once more in CSC order (the column pass reads them without the permutation hop) + the inverse map
-__global__ void k_heavy_csc(const uint32_t* __restrict__ perm, uint32_t n_heavy, const uint32_t* __restrict__ h_cell,
-                            const uint32_t* __restrict__ h_ref, const uint32_t* __restrict__ h_alt, uint32_t* __restrict__ hc_cell,
-                            uint32_t* __restrict__ hc_ref, uint32_t* __restrict__ hc_alt, uint32_t* __restrict__ h2c) {
-    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n_heavy) return;
-    const uint32_t h = perm[j];
-    hc_cell[j] = h_cell[h];
-    hc_ref[j] = h_ref[h];
-    hc_alt[j] = h_alt[h];
-    h2c[h] = j;
-}
 
 __global__ void k_unpack_counts(const uint32_t* __restrict__ packed, uint64_t n, uint32_t* __restrict__ ref, uint32_t* __restrict__ alt) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
@@ -409,11 +397,6 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     CLX_CUDA(c, c->hv_ll.alloc(3 * (size_t)n_heavy));
     CLX_CUDA(c, c->hv_e.alloc(n_heavy));
     CLX_CUDA(c, hcpos.alloc(n_heavy));
-    CLX_CUDA(c, c->hc_cell.alloc(n_heavy));
-    CLX_CUDA(c, c->hc_ref.alloc(n_heavy));
-    CLX_CUDA(c, c->hc_alt.alloc(n_heavy));
-    CLX_CUDA(c, c->h2c.alloc(n_heavy));
-    CLX_CUDA(c, c->hv_c.alloc(n_heavy));
     if (n_heavy) {
         k_heavy_gather<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hpos.p, n_heavy, csr_src.p, c->csr.p, d_cell.p, d_ref.p,
                                                                d_alt.p, c->h_cell.p, c->h_locus.p, c->h_ref.p, c->h_alt.p);
@@ -423,9 +406,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         CLX_CUDA(c, tmp.alloc(tmp_bytes));
         CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, hcpos.p, n_sel.p, (int)nnz, f2, s));
         k_heavy_perm<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, csc_src.p, hpos.p, n_heavy, c->hc_perm.p);
-        k_heavy_csc<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(c->hc_perm.p, n_heavy, c->h_cell.p, c->h_ref.p, c->h_alt.p, c->hc_cell.p,
-                                                              c->hc_ref.p, c->hc_alt.p, c->h2c.p);
-        c->launches += 5;
+        c->launches += 4;
     }
     // entries too deep for the batched heavy kernel get a CTA each (em_kernels.cuh: k_heavy_giant)
     c->n_giant = 0;

@@ -3,10 +3,10 @@
 //
 // statrs 0.16.0 Data::{median, lower_quartile, upper_quartile} (R-8 quantile, h = (N + 1/3) tau + 1/3) need at
 // most six order statistics.  They are selected exactly on order-preserving u64 keys:
-//   * N <= SELECT_SMALL_MAX : one CTA runs the radix select on keys held in registers and applies the
-//                            exclusion rule — one launch;
-//   * larger N             : MSB-first radix select, 8 passes of 8 bits, all six ranks in flight at once,
-//                            one launch per pass (histogram + last-block digit pick).
+//   * up to 16 keys per thread x 1024 threads x one CTA per SM (2.4 M values): k_select_coop, a cooperative grid
+//     with the keys held in registers, which also applies the exclusion rule — one launch;
+//   * larger N: MSB-first radix select, 8 passes of 8 bits, all six ranks in flight at once, one launch per pass
+//     (histogram + last-block digit pick), then k_exclude.
 #pragma once
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
@@ -17,7 +17,7 @@
 
 namespace clx {
 
-constexpr uint32_t SELECT_SMALL_MAX = 16384;  // one CTA of 1024 threads x 16 keys in registers
+constexpr uint32_t SELECT_SMALL_MAX = 16384;  // keys of one CTA: 1024 threads x at most 16 keys in registers
 constexpr int SELECT_TARGETS = 6;
 
 struct SelectPlan {            // ranks (0-based order statistics) and interpolation data, computed on the host
@@ -49,7 +49,7 @@ __device__ __forceinline__ void finish_stats(const double* x, const SelectPlan& 
     st->threshold = q1 - iqr_multiple * iqr;
 }
 
-// ---- small N: one CTA; every thread keeps SELECT_R keys in registers.  The radix select starts below the bits
+// ---- register-resident select: every thread keeps its keys in registers.  The radix select starts below the bits
 // all keys share (normalized log likelihoods cluster: sign, exponent and leading mantissa bits are common), takes
 // 8 bits per pass with all six ranks in flight (targets that still share a prefix share a histogram) and drops a
 // key as soon as it matches no target prefix, so later passes touch a handful of keys.  The same launch then
@@ -109,217 +109,9 @@ constexpr int SELECT_R = 16;
 constexpr unsigned int SELECT_RANK_CAP = 192;  // finish by direct ranking once this few keys are left
 static_assert(SELECT_SMALL_MAX == SELECT_SMALL_THREADS * SELECT_R, "keys per thread");
 static_assert(SELECT_RANK_CAP <= SELECT_LIST_PAD, "survivor list fits the sort network");
-__global__ void __launch_bounds__(SELECT_SMALL_THREADS) k_select_small(const double* __restrict__ vals, uint32_t n,
-                                                                       SelectPlan plan, const IterParams* __restrict__ prm,
-                                                                       DeviceStats* __restrict__ st,
-                                                                       const double* __restrict__ norm_local,
-                                                                       uint32_t n_cells_local, uint32_t* __restrict__ bits) {
-    __shared__ unsigned int sh[SELECT_TARGETS][256];
-    __shared__ unsigned long long spre[SELECT_TARGETS], srank[SELECT_TARGETS];
-    __shared__ int sgrp[SELECT_TARGETS];
-    __shared__ unsigned long long s_and[32], s_or[32];
-    __shared__ unsigned int scnt[SELECT_TARGETS], s_total, s_nlist;
-    __shared__ int s_nlead, s_leadt[SELECT_TARGETS];
-    __shared__ unsigned long long s_leadpre[SELECT_TARGETS], s_result[SELECT_TARGETS];
-    __shared__ unsigned long long s_list[SELECT_LIST_PAD];
-    __shared__ double sthr;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    unsigned long long key[SELECT_R];
-    unsigned int valid = 0;
-    unsigned long long k_and = ~0ull, k_or = 0ull;
-    // exclusion fused into this launch when the selected values ARE this rank's normalized values (one GPU):
-    // slot j of a warp covers 32 consecutive cells = one word of the excluded bitmap; lane j prefetches word j's
-    // old value now so that its latency hides behind the select
-    const bool fuse_exclude = bits != nullptr && norm_local == vals;
-    unsigned int old_word = 0;
-    if (fuse_exclude && lane < SELECT_R) {
-        const uint32_t i0 = (uint32_t)lane * SELECT_SMALL_THREADS + (uint32_t)(warp << 5);
-        if (i0 < n_cells_local) old_word = bits[i0 >> 5];
-    }
-#pragma unroll
-    for (int j = 0; j < SELECT_R; ++j) {
-        const uint32_t i = (uint32_t)j * SELECT_SMALL_THREADS + tid;
-        key[j] = 0ull;
-        if (i < n) {
-            key[j] = f64_to_key(vals[i]);
-            valid |= 1u << j;
-            k_and &= key[j];
-            k_or |= key[j];
-        }
-    }
-    // bits that differ anywhere: (and ^ or); everything above the highest of them is a common prefix
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        k_and &= __shfl_xor_sync(0xffffffffu, k_and, off);
-        k_or |= __shfl_xor_sync(0xffffffffu, k_or, off);
-    }
-    if (lane == 0) { s_and[warp] = k_and; s_or[warp] = k_or; }
-    if (tid < SELECT_TARGETS) srank[tid] = plan.rank[tid];
-    __syncthreads();
-    k_and = s_and[0]; k_or = s_or[0];
-    for (int w = 1; w < SELECT_SMALL_THREADS / 32; ++w) { k_and &= s_and[w]; k_or |= s_or[w]; }
-    const unsigned long long diff = k_and ^ k_or;
-    int hi_bit = diff ? 64 - __clzll((long long)diff) : 0;  // number of low bits that vary
-    if (tid < SELECT_TARGETS) spre[tid] = hi_bit >= 64 ? 0ull : (k_or >> hi_bit);  // the shared prefix
-    __syncthreads();
-    // scnt[t] = number of keys that still match target t's prefix; s_total = keys matching any target
-    if (tid < SELECT_TARGETS) scnt[tid] = n;
-    if (tid == 0) s_total = n;
-    __syncthreads();
-    while (hi_bit > 0 && s_total > SELECT_RANK_CAP) {
-        const int lo_bit = hi_bit > 8 ? hi_bit - 8 : 0;
-        const unsigned int dmask = (1u << (hi_bit - lo_bit)) - 1u;
-        for (int i = tid; i < SELECT_TARGETS * 256; i += SELECT_SMALL_THREADS) (&sh[0][0])[i] = 0;
-        if (tid < SELECT_TARGETS) {  // distinct prefixes among the targets ("leaders") share one histogram
-            unsigned long long p[SELECT_TARGETS];
-#pragma unroll
-            for (int u = 0; u < SELECT_TARGETS; ++u) p[u] = spre[u];
-            int g = tid;
-#pragma unroll
-            for (int u = SELECT_TARGETS - 1; u >= 0; --u)
-                if (u < tid && p[u] == p[tid]) g = u;
-            sgrp[tid] = g;
-            // position of a leader in the leader list = number of leaders before it
-            int pos = 0, nl = 0;
-#pragma unroll
-            for (int u = 0; u < SELECT_TARGETS; ++u) {
-                bool lead = true;
-#pragma unroll
-                for (int v = 0; v < SELECT_TARGETS; ++v) lead = lead && !(v < u && p[v] == p[u]);
-                pos += (lead && u < tid) ? 1 : 0;
-                nl += lead ? 1 : 0;
-            }
-            if (g == tid) { s_leadt[pos] = tid; s_leadpre[pos] = p[tid]; }
-            if (tid == 0) s_nlead = nl;
-        }
-        __syncthreads();
-        const int nlead = s_nlead;
-        if (valid) {
-            unsigned long long lpre[SELECT_TARGETS];
-            // a leader's histogram row is sh[t] with t its own target index; an impossible prefix disables slot k
-            int lrow[SELECT_TARGETS];
-#pragma unroll
-            for (int k = 0; k < SELECT_TARGETS; ++k) {
-                lpre[k] = k < nlead ? s_leadpre[k] : ~0ull;
-                lrow[k] = k < nlead ? s_leadt[k] : 0;
-            }
-#pragma unroll
-            for (int j = 0; j < SELECT_R; ++j) {
-                if (!((valid >> j) & 1u)) continue;
-                const unsigned long long pk = hi_bit >= 64 ? 0ull : (key[j] >> hi_bit);
-                const unsigned int d = (unsigned int)(key[j] >> lo_bit) & dmask;
-#pragma unroll
-                for (int k = 0; k < SELECT_TARGETS; ++k)
-                    if (pk == lpre[k]) atomicAdd(&sh[lrow[k]][d], 1u);
-            }
-        }
-        __syncthreads();
-        if (warp < SELECT_TARGETS) {  // warp t walks the histogram of its group: 8 bins per lane + warp scan
-            const int t = warp;
-            const unsigned int* h = sh[sgrp[t]];
-            unsigned int c[8], tot = 0;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                c[j] = h[lane * 8 + j];
-                tot += c[j];
-            }
-            unsigned int incl = tot;
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const unsigned int o = __shfl_up_sync(0xffffffffu, incl, off);
-                if (lane >= off) incl += o;
-            }
-            const unsigned long long r = srank[t];
-            const unsigned long long excl = incl - tot;
-            const bool here = r >= excl && r < (unsigned long long)incl;
-            const unsigned int who = __ballot_sync(0xffffffffu, here);
-            const int src = who ? __ffs(who) - 1 : 31;
-            if (lane == src) {
-                unsigned long long rr = r - excl;
-                int j = 0;
-                for (; j < 7; ++j) {
-                    if (rr < c[j]) break;
-                    rr -= c[j];
-                }
-                spre[t] = (spre[t] << (hi_bit - lo_bit)) | (unsigned long long)(lane * 8 + j);
-                srank[t] = rr;
-                scnt[t] = c[j];
-            }
-        }
-        __syncthreads();
-        if (tid == 0) s_total = 0;
-        __syncthreads();
-        if (tid < SELECT_TARGETS) {  // keys left = sum over distinct new prefixes
-            bool first = true;
-#pragma unroll
-            for (int u = 0; u < SELECT_TARGETS; ++u) first = first && !(u < tid && spre[u] == spre[tid]);
-            if (first) atomicAdd(&s_total, scnt[tid]);
-        }
-        // drop the keys that no target can still be
-        if (valid) {
-            unsigned long long pre[SELECT_TARGETS];
-#pragma unroll
-            for (int t = 0; t < SELECT_TARGETS; ++t) pre[t] = spre[t];
-#pragma unroll
-            for (int j = 0; j < SELECT_R; ++j) {
-                if (!((valid >> j) & 1u)) continue;
-                const unsigned long long pk = key[j] >> lo_bit;
-                bool keep = false;
-#pragma unroll
-                for (int t = 0; t < SELECT_TARGETS; ++t) keep = keep || pk == pre[t];
-                if (!keep) valid &= ~(1u << j);
-            }
-        }
-        hi_bit = lo_bit;
-        __syncthreads();
-    }
-    if (hi_bit > 0 && n > 0) {
-        // few keys left: list them in shared memory and rank them directly.  Target t is the key of its prefix
-        // group with exactly srank[t] group members ordered before it (ties broken by list position).
-        if (tid == 0) s_nlist = 0;
-        __syncthreads();
-        if (valid) {
-#pragma unroll
-            for (int j = 0; j < SELECT_R; ++j)
-                if ((valid >> j) & 1u) s_list[atomicAdd(&s_nlist, 1u)] = key[j];
-        }
-        __syncthreads();
-        select_from_list(s_list, s_nlist, hi_bit, spre, srank);
-    }
-    if (tid == 0) {
-        double x[SELECT_TARGETS];
-#pragma unroll
-        for (int t = 0; t < SELECT_TARGETS; ++t) x[t] = n ? key_to_f64(spre[t]) : 0.0;
-        finish_stats(x, plan, prm->iqr_multiple, st);
-        sthr = st->threshold;
-    }
-    __syncthreads();
-    if (fuse_exclude) {
-        const double thr = sthr;
-        unsigned int nn = 0, nr = 0, ne = 0;
-#pragma unroll
-        for (int j = 0; j < SELECT_R; ++j) {
-            const uint32_t i = (uint32_t)j * SELECT_SMALL_THREADS + tid;
-            const bool ex = i < n_cells_local && key_to_f64(key[j]) < thr;  // main.rs:331 on the exact double
-            const unsigned int word = __ballot_sync(0xffffffffu, ex);
-            const unsigned int old = __shfl_sync(0xffffffffu, old_word, j);
-            if (lane == 0 && (uint32_t)j * SELECT_SMALL_THREADS + (uint32_t)(warp << 5) < n_cells_local) {
-                bits[i >> 5] = word;
-                nn += __popc(word & ~old);
-                nr += __popc(old & ~word);
-                ne += __popc(word);
-            }
-        }
-        if (lane == 0) {
-            if (nn) atomicAdd(&st->n_new, (unsigned long long)nn);
-            if (nr) atomicAdd(&st->n_rescued, (unsigned long long)nr);
-            if (ne) atomicAdd(&st->n_excluded, (unsigned long long)ne);
-        }
-    }
-}
 
-// ---- medium N (up to SELECT_SMALL_MAX keys per CTA x one CTA per SM): the same register-resident radix select,
-// spread over a cooperative grid.  Every CTA keeps its keys in registers; per pass the CTA histograms are added
+// ---- up to SELECT_SMALL_MAX keys per CTA x one CTA per SM: a register-resident radix select spread over a
+// cooperative grid (a one-CTA version measured slower even at 10 k values: 33 vs 28 us).  Every CTA keeps its keys in registers; per pass the CTA histograms are added
 // into a global histogram (one region per pass, zeroed by the host), the grid synchronises, and every CTA picks
 // the digits redundantly from the global histogram — one launch for the whole select, ~one grid barrier per
 // pass.  Used when cells are sharded (the gathered values of all ranks are selected on every rank, so all ranks

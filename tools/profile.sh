@@ -14,11 +14,6 @@ import json
 d=json.load(open("gpurun_out/${TAG}_items$v.json")); print("items/SM $v:", d["ms_per_step"], d["phase_us_per_step"])
 PY
 done
-CLX_SELECT_MODE=3 timeout 200 $B > gpurun_out/${TAG}_selsmall.json 2>/dev/null
-python - <<PY
-import json
-d=json.load(open("gpurun_out/${TAG}_selsmall.json")); print("select one-CTA:", d["ms_per_step"], d["phase_us_per_step"])
-PY
 timeout 400 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${TAG}_launches.csv \
   $B --steps 2 --warmup 1 > gpurun_out/${TAG}_ncu1.log 2>&1
 echo "launch list rc=$?"
