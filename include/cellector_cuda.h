@@ -6,6 +6,8 @@
  *
  *   clx_load_coo            replaces load_data::load_cell_data        cellector/src/load_data.rs:134-181
  *                           (+ get_loci_used                           cellector/src/load_data.rs:254-280)
+ *   clx_load_coo_packed     the same replacement, ref and alt of an entry in one word (the two counts
+ *                           load_data.rs:195-196 parses per line pair)
  *   clx_get_locus_ids       replaces the locus_ids vector              cellector/src/load_data.rs:144-147
  *   clx_em_iteration        replaces compute_new_excluded              cellector/src/main.rs:308-347
  *                           (init_alpha_betas :598-611, get_cell_log_likelihoods :541-591,
