@@ -128,7 +128,8 @@ def run_reference(args, rank, world):
     n_s = min(args.cpu_sample_cells, data.n_cells)
     keep = data.cell < n_s
     orc = Oracle()
-    _, nnz_used = orc.load_cell_data(data.locus[keep], data.cell[keep], data.ref[keep], data.alt[keep], data.n_loci, n_s)
+    coo = [a[keep] for a in (data.locus, data.cell, data.ref, data.alt)]
+    _, nnz_used = orc.load_cell_data(*coo, data.n_loci, n_s)
     times = []
     for i in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -149,7 +150,42 @@ def run_reference(args, rank, world):
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "reference = oracle/ C++ restatement of cellector (Rust toolchain absent); the reference is single-threaded (rayon declared, never used), so cores=1"}
+    ctx_all = all_cores_context(coo, data.n_loci, n_s)
+    if ctx_all:
+        line["cpu_baseline"]["all_cores_context"] = ctx_all
     print(json.dumps(line), flush=True)
+
+
+def all_cores_context(coo, n_loci, n_s):
+    """Context only: the oracle port on disjoint contiguous cell slices, one thread per host core (ctypes releases
+    the GIL).  The reference itself is single-threaded."""
+    from tests.oracle import Oracle
+    n_thr = max(1, min(os.cpu_count() or 1, 64))
+    if n_thr < 2 or n_s < 250 * n_thr:  # too few cells per slice: the per-slice locus filter would remove most loci
+        return None
+    cuts = np.linspace(0, n_s, n_thr + 1).astype(np.int64)
+    parts = []
+    for k in range(n_thr):
+        m = (coo[1] >= cuts[k]) & (coo[1] < cuts[k + 1])
+        o = Oracle()
+        _, nz = o.load_cell_data(coo[0][m], coo[1][m] - np.uint32(cuts[k]), coo[2][m], coo[3][m], n_loci, int(cuts[k + 1] - cuts[k]))
+        parts.append((o, nz))
+    best = None
+    for rep in range(3):
+        th = [threading.Thread(target=lambda o=o: o.compute_new_excluded(5.0)) for o, _ in parts]
+        t0 = time.perf_counter()
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        dt = time.perf_counter() - t0
+        if rep > 0:
+            best = dt if best is None else min(best, dt)
+    nz_all = sum(nz for _, nz in parts)
+    for o, _ in parts:
+        o.close()
+    return {"value": nz_all / best, "unit": UNIT, "cores": n_thr,
+            "how": "the oracle port on disjoint cell slices, one thread per host core, per-slice locus filter; not the reference's behaviour (it is single-threaded)"}
 
 
 def cpu_baseline(args, data):
@@ -176,34 +212,9 @@ def cpu_baseline(args, data):
     out = {"value": nnz_used / t, "unit": UNIT, "cores": 1, "kind": "port", "host_cores": os.cpu_count(),
            "sample": f"{len(ts)} EM iterations (mean; faithful cost: expected-LL per entry and the per-entry records) over the "
                      f"first {n_s} cells x all loci of {args.workload} ({nnz_used} scored nonzeros, {t:.2f} s each, {spent:.1f} s timed)"}
-    # context: every host core on its own contiguous cell slice of the same sample (ctypes releases the GIL)
-    n_thr = max(1, min(os.cpu_count() or 1, 64))
-    if n_thr > 1 and n_s >= 4 * n_thr:
-        cuts = np.linspace(0, n_s, n_thr + 1).astype(np.int64)
-        parts = []
-        for k in range(n_thr):
-            m = (coo[1] >= cuts[k]) & (coo[1] < cuts[k + 1])
-            o = Oracle()
-            _, nz = o.load_cell_data(coo[0][m], coo[1][m] - np.uint32(cuts[k]), coo[2][m], coo[3][m], data.n_loci, int(cuts[k + 1] - cuts[k]))
-            parts.append((o, nz))
-        def one(o):
-            o.compute_new_excluded(5.0)
-        best = None
-        for rep in range(3):
-            th = [threading.Thread(target=one, args=(o,)) for o, _ in parts]
-            t0 = time.perf_counter()
-            for x in th:
-                x.start()
-            for x in th:
-                x.join()
-            dt = time.perf_counter() - t0
-            if rep > 0:
-                best = dt if best is None else min(best, dt)
-        nz_all = sum(nz for _, nz in parts)
-        for o, _ in parts:
-            o.close()
-        out["all_cores_context"] = {"value": nz_all / best, "unit": UNIT, "cores": n_thr,
-                                    "how": "the oracle port on disjoint cell slices, one thread per host core, per-slice locus filter; not the reference's behaviour (it is single-threaded)"}
+    ctx_all = all_cores_context(coo, data.n_loci, n_s)
+    if ctx_all:
+        out["all_cores_context"] = ctx_all
     return out
 
 
