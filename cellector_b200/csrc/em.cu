@@ -123,13 +123,11 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
     const uint32_t N = c->n_cells;
     static const int mode = env_int("CLX_SELECT_MODE", 0);  // 0 cooperative kernel, 2 forces the multi-launch path
     // cooperative grid, keys in registers, one launch: as few keys per thread as one CTA per SM allows (1, 4 or 16);
-    // 256-thread CTAs for small inputs measured slightly slower (29.8 vs 27.9 us at 10 k keys): opt-in
+    // 256-thread CTAs for small inputs measured slightly slower (29.8 vs 27.9 us at 10 k keys)
     const uint64_t cap1 = (uint64_t)SELECT_SMALL_THREADS * (uint64_t)c->sm_count;
     if (mode != 2 && n_vals <= 16 * cap1) {
-        static const int small_cta = env_int("CLX_SELECT_CTA256", 0);
-        const bool t256 = small_cta && n_vals <= 256ull * (uint64_t)c->sm_count;
-        const int R = t256 ? 1 : (n_vals <= cap1 ? 1 : (n_vals <= 4 * cap1 ? 4 : 16));
-        const int threads = t256 ? 256 : SELECT_SMALL_THREADS;
+        const int R = n_vals <= cap1 ? 1 : (n_vals <= 4 * cap1 ? 4 : 16);
+        const int threads = SELECT_SMALL_THREADS;
         const uint64_t per_cta = (uint64_t)threads * R;
         // the histogram scratch was zeroed at the head of the iteration (k_tables_em)
         const unsigned grid = (unsigned)std::max<uint64_t>(1, (n_vals + per_cta - 1) / per_cta);
@@ -147,9 +145,9 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
         void* args[] = {(void*)&vals, (void*)&n_vals, (void*)&pl, (void*)&prm, (void*)&st, (void*)&scratch,
                         (void*)&glist, (void*)&norm_local, (void*)&n_local, (void*)&bits, (void*)&win, (void*)&rank,
                         (void*)&world, (void*)&off_counters};
-        const void* fn = t256 ? (const void*)k_select_coop<1, 256>
-                              : (R == 1 ? (const void*)k_select_coop<1, SELECT_SMALL_THREADS>
-                                        : (R == 4 ? (const void*)k_select_coop<4, SELECT_SMALL_THREADS> : (const void*)k_select_coop<16, SELECT_SMALL_THREADS>));
+        const void* fn = R == 1 ? (const void*)k_select_coop<1, SELECT_SMALL_THREADS>
+                                : (R == 4 ? (const void*)k_select_coop<4, SELECT_SMALL_THREADS>
+                                          : (const void*)k_select_coop<16, SELECT_SMALL_THREADS>);
         CLX_CUDA(c, cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(threads), args, 0, s));
         c->launches++;
         return CLX_OK;

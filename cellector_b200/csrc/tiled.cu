@@ -781,26 +781,3 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
 }
 
 }  // namespace clx
-
-// Test hooks: the tiled layout as the kernel sees it (tests decode it on the host and compare with the matrix).
-extern "C" int clx_debug_tiled_sizes(clx_ctx* c, uint64_t* out8) {
-    if (!c || !out8) return CLX_ERR_ARG;
-    out8[0] = c->tiled_ready ? 1 : 0;
-    out8[1] = c->tl_stream_len;
-    out8[2] = c->tl_pk_d.n;
-    out8[3] = c->tl_pk_base.n;
-    out8[4] = c->tl_n_items;
-    out8[5] = c->tl_NB;
-    out8[6] = c->tl_nT;
-    out8[7] = c->tl_n_light;
-    return CLX_OK;
-}
-extern "C" int clx_debug_tiled_copy(clx_ctx* c, uint32_t* stream, uint32_t* pk_d, uint32_t* pk_base, uint32_t* item_q) {
-    if (!c || !c->tiled_ready) return CLX_ERR_STATE;
-    cudaStreamSynchronize(c->stream);
-    if (stream) cudaMemcpy(stream, c->tl_stream.p, c->tl_stream_len * 4, cudaMemcpyDeviceToHost);
-    if (pk_d) cudaMemcpy(pk_d, c->tl_pk_d.p, c->tl_pk_d.n * 8, cudaMemcpyDeviceToHost);
-    if (pk_base) cudaMemcpy(pk_base, c->tl_pk_base.p, c->tl_pk_base.n * 4, cudaMemcpyDeviceToHost);
-    if (item_q) cudaMemcpy(item_q, c->tl_item_q.p, (size_t)c->tl_n_items * 16, cudaMemcpyDeviceToHost);
-    return cudaGetLastError() == cudaSuccess ? CLX_OK : CLX_ERR_CUDA;
-}
