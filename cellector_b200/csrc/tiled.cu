@@ -591,6 +591,8 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         } else {
             nb = nb_even;
         }
+        const char* env_nb = getenv("CLX_TILED_NB");  // experiments: force the cell-block size (tools/tiled_model.py)
+        if (env_nb && *env_nb) nb = std::min<uint32_t>(NB_MAX, std::max<uint32_t>(32u, ((uint32_t)atoi(env_nb) + 31u) / 32u * 32u));
         c->tl_NB = nb;
         c->tl_Pc = N ? (N + c->tl_NB - 1) / c->tl_NB : 1;
     }
