@@ -48,11 +48,20 @@ def model(locus, cell, total, n_cells, L, NB):
     batches = int(np.ceil(group_iters / BATCH_ITERS).sum())
     stream_bytes = 64 * int(group_iters.sum()) + 32 * n_groups + 16 * batches
     n_sub_nonempty = int(first.sum())
+    # what run packing could reach: a sub-unit's runs spread over 32 lane slots, several short runs per slot, one extra
+    # slot entry per additional run (the in-line cell index): iterations = max(longest run, ceil(slots needed / 32))
+    su_id = np.cumsum(first) - 1
+    su_entries = np.bincount(su_id, weights=cnt_s).astype(np.int64)
+    su_runs = np.bincount(su_id).astype(np.int64)
+    su_longest = cnt_s[first]
+    packed_iters = np.maximum(su_longest, -(-(su_entries + np.maximum(su_runs - 32, 0)) // 32))
+    packed_lane_iters = int(packed_iters.sum()) * 32
     return {"NB": NB, "cell_blocks": int((n_cells + NB - 1) // NB), "tiles": int(nT), "light_entries": int(light.sum()),
             "runs": int(len(uk)), "mean_run": float(cnt.mean()), "groups": n_groups,
             "lane_iterations": lane_iters, "padding_frac": 1.0 - light.sum() / lane_iters,
             "stream_MB": stream_bytes / 1e6, "bytes_per_entry": stream_bytes / light.sum(),
-            "table_MB_read": (n_cells + NB - 1) // NB * nT * TILE_L * 104 / 1e6, "nonempty_sub_units": n_sub_nonempty}
+            "table_MB_read": (n_cells + NB - 1) // NB * nT * TILE_L * 104 / 1e6, "nonempty_sub_units": n_sub_nonempty,
+            "packed_lane_iterations": packed_lane_iters, "packed_padding_frac": 1.0 - light.sum() / packed_lane_iters}
 
 
 def main():
