@@ -56,12 +56,20 @@ def model(locus, cell, total, n_cells, L, NB):
     su_longest = cnt_s[first]
     packed_iters = np.maximum(su_longest, -(-(su_entries + np.maximum(su_runs - 32, 0)) // 32))
     packed_lane_iters = int(packed_iters.sum()) * 32
+    # a packing the device builder can do by formula: sorted runs dealt to the lanes boustrophedon (0..31, 31..0, ...);
+    # a lane's load = its entries + one slot per extra run; the sub-unit runs for the heaviest lane
+    rnd, idx = pos // 32, pos % 32
+    lane = np.where(rnd % 2 == 0, idx, 31 - idx)
+    slot = su_id * 32 + lane
+    load = np.bincount(slot, weights=cnt_s + (rnd > 0), minlength=int(su_id.max() + 1) * 32).reshape(-1, 32)
+    snake_lane_iters = int(load.max(axis=1).sum()) * 32
     return {"NB": NB, "cell_blocks": int((n_cells + NB - 1) // NB), "tiles": int(nT), "light_entries": int(light.sum()),
             "runs": int(len(uk)), "mean_run": float(cnt.mean()), "groups": n_groups,
             "lane_iterations": lane_iters, "padding_frac": 1.0 - light.sum() / lane_iters,
             "stream_MB": stream_bytes / 1e6, "bytes_per_entry": stream_bytes / light.sum(),
             "table_MB_read": (n_cells + NB - 1) // NB * nT * TILE_L * 104 / 1e6, "nonempty_sub_units": n_sub_nonempty,
-            "packed_lane_iterations": packed_lane_iters, "packed_padding_frac": 1.0 - light.sum() / packed_lane_iters}
+            "packed_lane_iterations": packed_lane_iters, "packed_padding_frac": 1.0 - light.sum() / packed_lane_iters,
+            "snake_lane_iterations": snake_lane_iters, "snake_padding_frac": 1.0 - light.sum() / snake_lane_iters}
 
 
 def main():
