@@ -1,5 +1,7 @@
 """GPU parity tests proper: every call goes through the C ABI of libcellector_cuda.so and is checked against
 the CPU oracle on the same seeded input (sizes the oracle finishes in seconds)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -204,3 +206,16 @@ def test_gpu_against_committed_golden(libs):
         p = gpu.calculate_posteriors()
         assert np.bincount(p["label"], minlength=4).tolist() == g["label_counts"]
         assert float(p["ll_minor"].sum()) == pytest.approx(g["ll_minor_sum"], rel=1e-9)
+
+
+@pytest.mark.skipif(os.environ.get("CLX_RUN_DENSE") != "1",
+                    reason="written after the round's GPU minutes were spent: run once with CLX_RUN_DENSE=1, then drop this guard")
+def test_parity_dense_tiles(libs, monkeypatch):
+    """Nearly dense matrix in ONE cell block of 3072 cells: runs of ~440 entries per cell and tile, three groups of
+    ~30 batches per warp and tile, i.e. ~90 packets per warp and work item — the descriptor-window refills of
+    k_score_tiled (windows of 32 packets) and many-batch groups, which the sparse cases never reach."""
+    monkeypatch.setenv("CLX_TILED_NB", "3072")
+    gpu, orc = _pair(libs)
+    cfg = synth.SynthConfig(n_cells=3072, n_loci=1536, density=2.0, minority_frac=0.05, seed=13)
+    with gpu, orc:
+        run_parity(gpu, orc, synth.generate(cfg))
