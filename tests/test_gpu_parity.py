@@ -208,8 +208,6 @@ def test_gpu_against_committed_golden(libs):
         assert float(p["ll_minor"].sum()) == pytest.approx(g["ll_minor_sum"], rel=1e-9)
 
 
-@pytest.mark.skipif(os.environ.get("CLX_RUN_DENSE") != "1",
-                    reason="written after the round's GPU minutes were spent: run once with CLX_RUN_DENSE=1, then drop this guard")
 def test_parity_dense_tiles(libs, monkeypatch):
     """Nearly dense matrix in ONE cell block of 3072 cells: runs of ~440 entries per cell and tile, three groups of
     ~30 batches per warp and tile, i.e. ~90 packets per warp and work item — the descriptor-window refills of
