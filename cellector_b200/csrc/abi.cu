@@ -115,6 +115,13 @@ __global__ void k_flush_read(const uint4* __restrict__ p, size_t n, unsigned int
 
 using namespace clx;
 
+// Every entry point that takes a context binds the calling thread to the context's device and allocation stream
+// first: a context may be driven from any host thread, and several contexts (one per device) may live in one process.
+static inline void bind_ctx(clx_ctx* c) {
+    cudaSetDevice(c->device);
+    alloc_stream() = c->stream;
+}
+
 extern "C" {
 
 int clx_create(clx_ctx** out, int device, unsigned flags) {
@@ -217,7 +224,7 @@ int clx_nccl_unique_id(void* out128) { return out128 ? comm_unique_id(out128) : 
 
 int clx_comm_init(clx_ctx* c, int rank, int world, const void* id) {
     if (!c) return CLX_ERR_ARG;
-    alloc_stream() = c->stream;
+    bind_ctx(c);
     return comm_init(c, rank, world, id);
 }
 
@@ -225,8 +232,7 @@ int clx_load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, 
                  const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt,
                  uint32_t* n_loci_used, uint64_t* nnz_used) {
     if (!c) return CLX_ERR_ARG;
-    cudaSetDevice(c->device);
-    alloc_stream() = c->stream;
+    bind_ctx(c);
     CLX_TRY(load_coo(c, nnz0, n_loci0, n_cells, locus, cell, ref, alt, min_ref, min_alt));
     if (n_loci_used) *n_loci_used = c->n_loci;
     if (nnz_used) *nnz_used = c->nnz;
@@ -237,8 +243,7 @@ int clx_load_coo_packed(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_
                         const uint32_t* cell, const uint32_t* ref_alt, uint32_t min_ref, uint32_t min_alt,
                         uint32_t* n_loci_used, uint64_t* nnz_used) {
     if (!c) return CLX_ERR_ARG;
-    cudaSetDevice(c->device);
-    alloc_stream() = c->stream;
+    bind_ctx(c);
     CLX_TRY(load_coo(c, nnz0, n_loci0, n_cells, locus, cell, ref_alt, nullptr, min_ref, min_alt));
     if (n_loci_used) *n_loci_used = c->n_loci;
     if (nnz_used) *nnz_used = c->nnz;
@@ -247,6 +252,7 @@ int clx_load_coo_packed(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_
 
 int clx_get_locus_ids(clx_ctx* c, uint32_t* ids) {
     if (!c || !c->loaded) return c ? fail(c, CLX_ERR_STATE, "not loaded") : CLX_ERR_ARG;
+    bind_ctx(c);
     CLX_TRY(d2h(c, ids, c->locus_ids.p, c->n_loci));
     CLX_CUDA(c, cudaStreamSynchronize(c->stream));
     return CLX_OK;
@@ -254,17 +260,20 @@ int clx_get_locus_ids(clx_ctx* c, uint32_t* ids) {
 
 int clx_reset(clx_ctx* c) {
     if (!c || !c->loaded) return c ? fail(c, CLX_ERR_STATE, "not loaded") : CLX_ERR_ARG;
+    bind_ctx(c);
     return em_reset(c);
 }
 
 int clx_em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
     if (!c) return CLX_ERR_ARG;
+    bind_ctx(c);
     return em_iteration(c, iqr_multiple, out);
 }
 
 int clx_get_cell_vectors(clx_ctx* c, double* ll, double* expected_ll, uint32_t* n_loci, double* norm, uint8_t* excluded) {
     if (!c || !c->loaded) return c ? fail(c, CLX_ERR_STATE, "not loaded") : CLX_ERR_ARG;
     if (!c->have_iteration) return fail(c, CLX_ERR_STATE, "no iteration run yet");
+    bind_ctx(c);
     const uint32_t N = c->n_cells;
     CLX_TRY(d2h(c, ll, c->ll.p, N));
     CLX_TRY(d2h(c, expected_ll, c->ell.p, N));
@@ -281,7 +290,7 @@ int clx_get_cell_vectors(clx_ctx* c, double* ll, double* expected_ll, uint32_t* 
 
 int clx_get_locus_vectors(clx_ctx* c, const clx_locus_arrays* o) {
     if (!c || !o) return CLX_ERR_ARG;
-    alloc_stream() = c->stream;
+    bind_ctx(c);
     if (!c->loaded || !c->have_iteration) return fail(c, CLX_ERR_STATE, "no iteration run yet");
     const size_t L = c->n_loci;
     CLX_TRY(d2h(c, o->ll_minority, c->loc_ll.p, L));
@@ -308,12 +317,13 @@ int clx_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_use
                    double* doublet_posterior, double* ll_major, double* ll_minor, uint8_t* label, uint8_t* anomaly,
                    uint8_t* qual) {
     if (!c) return CLX_ERR_ARG;
+    bind_ctx(c);
     CLX_TRY(em_posteriors(c, posterior_threshold, min_loci_used));
     const size_t N = c->n_cells;
     CLX_TRY(d2h(c, posterior, c->post.p, N));
     CLX_TRY(d2h(c, doublet_posterior, c->post.p + N, N));
-    CLX_TRY(d2h(c, ll_minor, c->ll.p, N));
-    CLX_TRY(d2h(c, ll_major, c->ll.p + N, N));
+    CLX_TRY(d2h(c, ll_minor, c->post_ll.p, N));
+    CLX_TRY(d2h(c, ll_major, c->post_ll.p + N, N));
     CLX_TRY(d2h(c, label, c->post_u8.p, N));
     CLX_TRY(d2h(c, anomaly, c->post_u8.p + N, N));
     CLX_TRY(d2h(c, qual, c->post_u8.p + 2 * N, N));
@@ -324,7 +334,7 @@ int clx_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_use
 int clx_final_locus_counts(clx_ctx* c, uint64_t* minority_ref_alt, uint64_t* majority_ref_alt) {
     if (!c || !minority_ref_alt || !majority_ref_alt) return CLX_ERR_ARG;
     if (!c->loaded) return fail(c, CLX_ERR_STATE, "not loaded");
-    alloc_stream() = c->stream;
+    bind_ctx(c);
     const size_t n = 2 * (size_t)c->n_loci0;
     clx::DevBuf<unsigned long long> mn, mj;
     CLX_CUDA(c, mn.alloc(n + 1));
@@ -359,6 +369,7 @@ int clx_get_phase_ms(clx_ctx* c, int phase, double* total_ms, uint64_t* launches
 }
 int clx_set_profiling(clx_ctx* c, int on) {
     if (!c) return CLX_ERR_ARG;
+    bind_ctx(c);
     if (c->stream) cudaStreamSynchronize(c->stream);
     phase_resolve(c);
     em_drop_graph(c);  // the events are nodes of the captured iteration
@@ -389,7 +400,7 @@ int clx_launch_count(clx_ctx* c, uint64_t* launches) {
 int clx_flush_l2(clx_ctx* c) {
     if (!c) return CLX_ERR_ARG;
     const size_t bytes = 512ull << 20;  // 4x the 126 MB L2
-    alloc_stream() = c->stream;
+    bind_ctx(c);
     if (!c->flush_buf.p) CLX_CUDA(c, c->flush_buf.alloc(bytes));
     static uint32_t v = 0;
     k_flush<<<c->sm_count * 8, 256, 0, c->stream>>>((uint4*)c->flush_buf.p, bytes / 16, ++v);

@@ -123,21 +123,21 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> giant_idx;                      // [n_giant] heavy entries with total > HEAVY_GIANT_TOTAL
     uint32_t n_giant = 0;
     clx::DevBuf<double> hv_ll, hv_e;                      // [3 * n_heavy] values of the current scoring pass
-    // --- tiled scoring layout (tiled.cu): light entries (total 1..3) packed to 4 bytes, ordered by
-    //     runs (one cell x one locus tile) inside packets; one work item = one cell block x a range of locus tiles
+    // --- run-stream scoring layout (tiled.cu): light entries (total 1..3) as 2-byte words, ordered by runs (one cell x
+    //     one locus tile) in length-sorted groups of 32; one work item = one cell block x a range of locus tiles
     bool tiled_ready = false;
-    uint32_t tl_NB = 0, tl_Pc = 0, tl_nT = 0, tl_n_items = 0, tl_n_units = 0;
-    uint64_t tl_n_light = 0, tl_stream_len = 0;       // light entries; stream length incl. slice padding
-    clx::DevBuf<uint32_t> tl_stream;                  // [tl_stream_len] packets of runs (tiled.cu), 4-byte words
-    clx::DevBuf<uint2> tl_pk_d;                       // [n_packets] packet descriptors {start, size}, in quads (16 B)
-    clx::DevBuf<uint32_t> tl_pk_base;                 // [n_sub + 1] first packet of every (cell block, warp, tile) sub-unit
+    uint32_t tl_NB = 0, tl_W = 0, tl_Pc = 0, tl_nT = 0, tl_n_items = 0, tl_n_units = 0;
+    uint64_t tl_n_light = 0, tl_stream_chunks = 0;    // light entries; stream length in 512-byte warp chunks
+    uint64_t tl_stream_steps = 0;                     // lookup steps x 32 lanes of one pass (padding included)
+    clx::DevBuf<uint4> tl_stream;                     // [tl_stream_chunks][32] one 16-byte piece (8 words) per lane
     clx::DevBuf<uint4> tl_item_q;                     // [n_items] work queue, largest first: cell block, first tile, n tiles, item id
-    clx::DevBuf<uint2> tl_item_pk;                    // [n_items][TL_WARPS] per queue slot and warp: first packet, n packets
-    uint32_t tl_grid = 0;                             // CTAs of k_score_tiled (the first tl_grid queue slots are taken statically)
+    clx::DevBuf<uint2> tl_item_rng;                   // [n_items][W] per queue slot and warp: first chunk, end chunk
+    uint32_t tl_grid = 0;                             // CTAs of k_score_runs (the first tl_grid queue slots are taken statically)
     clx::DevBuf<uint32_t> tl_cb_item;                 // [Pc + 1] first item of every cell block
     clx::DevBuf<uint32_t> tl_counter;                 // [1] work-queue cursor (k_score_finish re-arms it)
-    clx::DevBuf<double> tl_part;                      // [n_items][NB][2] per-item partial (log_pmf, expected) sums
-    clx::DevBuf<double> tab13;                        // [3][nT * TILE_L][13] compact memo records for the tiled kernel
+    clx::DevBuf<double> tl_part;                      // [n_items][NB][2] per-item partial sums of the two slot halves
+    clx::DevBuf<double> tab16;                        // [2][nT * TILE_L][TAB_SLOTS][2] staged tables (pass 0 / pass 1)
+    bool tl_attr_set = false;                         // dynamic shared-memory limit set on this context's device
     clx::DevBuf<uint32_t> n_used, row_len;            // [n_cells] loci_used_per_cell (main.rs:575) / stored row length
     // retained COO for clx_final_locus_counts
     clx::DevBuf<uint32_t> coo_locus, coo_cell, coo_ref, coo_alt;
@@ -156,7 +156,8 @@ struct clx_ctx {
     clx::DevBuf<uint8_t> loci_used;                   // [n_loci]
     clx::DevBuf<unsigned long long> min_cnt;          // [2 * n_loci] minority (ref, alt) over all stored entries
     clx::DevBuf<double> tab;                          // [3][n_loci][16] memo tables (slot 0 = EM, 0..2 = posteriors)
-    clx::DevBuf<double> ll, ell, norm;                // [n_cells] (+ ll for 3 tables in the posterior pass)
+    clx::DevBuf<double> ll, ell, norm;                // [n_cells] outputs of the last EM iteration
+    clx::DevBuf<double> post_ll;                      // [3 * n_cells] posterior pass: minority | majority | doublet log likelihoods
     clx::DevBuf<uint32_t> nloci;                      // [n_cells]
     clx::DevBuf<double> norm_all;                     // [world * max_local] gathered normalized values (world > 1)
     clx::DevBuf<uint64_t> sel_keys;                   // select scratch
@@ -244,7 +245,8 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
              const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt);
 // tiled.cu
 int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry);  // CSR-order cell id of every entry
-int score_tiled(clx_ctx* c, int table, bool with_e, bool em_outputs);
+enum ScoreMode { SCORE_EM = 0, SCORE_POST_AB = 1, SCORE_POST_C = 2 };
+int score_tiled(clx_ctx* c, ScoreMode mode);
 // em.cu
 int em_alloc(clx_ctx* c);
 int em_reset(clx_ctx* c);

@@ -50,7 +50,7 @@ void launch_score_rows(clx_ctx* c, int G) {
 #define CLX_SCORE(GG)                                                                                                  \
     k_score_rows<GG, NT, WITH_E><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                 \
         c->csr.p, c->row_ptr.p, n, c->tab.p, c->n_loci, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p, (uint32_t)c->n_heavy,   \
-        c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag)
+        NT == 1 ? c->ll.p : c->post_ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag)
     switch (G) {
         case 4: CLX_SCORE(4); break;
         case 8: CLX_SCORE(8); break;
@@ -177,7 +177,8 @@ int em_alloc(clx_ctx* c) {
     CLX_CUDA(c, c->excl_bits.alloc(words));
     CLX_CUDA(c, c->loci_used.alloc(L + 1));
     CLX_CUDA(c, c->tab.alloc(3 * L * TAB_STRIDE + TAB_STRIDE));
-    CLX_CUDA(c, c->ll.alloc(3 * N + 1));
+    CLX_CUDA(c, c->ll.alloc(N + 1));
+    CLX_CUDA(c, c->post_ll.alloc(3 * N + 1));
     CLX_CUDA(c, c->ell.alloc(N + 1));
     const size_t norm_n = std::max<size_t>(N, c->max_local_cells) + 1;
     CLX_CUDA(c, c->norm.alloc(norm_n));
@@ -202,9 +203,9 @@ int em_alloc(clx_ctx* c) {
     c->col_G = env_int("CLX_COL_G", pick_group(L ? (double)c->nnz / L : 0.0));
     // roofline accounting of the gather scoring kernel: packed entries + row pointers + outputs + table
     c->score_bytes = 8ull * c->nnz + 8ull * (N + 1) + 20ull * N + 128ull * L;
-    // tiled kernel: the packet stream (2-byte entries + 4-byte run headers) + one read of the 104-byte compact
-    // records + 16 B of sums per cell
-    if (use_tiled(c)) c->score_bytes = 4ull * c->tl_stream_len + 104ull * L + 16ull * N;
+    // run-stream kernel: the stream (512-byte chunks of 2-byte words) + one read of the 144-byte slot records per
+    // cell block + 16 B of partial sums per cell and work item
+    if (use_tiled(c)) c->score_bytes = 512ull * c->tl_stream_chunks + 144ull * L * c->tl_Pc + 16ull * c->tl_n_items * c->tl_NB;
     return em_reset(c);
 }
 
@@ -270,7 +271,7 @@ int enqueue_iteration(clx_ctx* c) {
     phase_begin(c, CLX_PHASE_TABLES);
     if (L) {
         k_tables_em<<<(unsigned)((3ull * L + TPB - 1) / TPB), TPB, 0, s>>>(cnts, L, make_lbc(c), with_e, c->tab.p,
-                                                                           c->tiled_ready ? c->tab13.p : nullptr, c->d_stats.p,
+                                                                           c->tiled_ready ? c->tab16.p : nullptr, c->d_stats.p,
                                                                            c->sel_hist.p, (uint32_t)c->sel_hist.n);
         c->launches++;
     } else {
@@ -287,7 +288,7 @@ int enqueue_iteration(clx_ctx* c) {
     // 2b. the per-cell scoring pass (main.rs:312)
     phase_begin(c, CLX_PHASE_SCORE);
     if (use_tiled(c)) {
-        CLX_TRY(score_tiled(c, 0, with_e != 0, true));
+        CLX_TRY(score_tiled(c, SCORE_EM));
     } else {
         if (with_e) launch_score_rows<1, true>(c, c->score_G);
         else launch_score_rows<1, false>(c, c->score_G);
@@ -449,7 +450,7 @@ int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used
     if (L) {
         k_tables<1><<<3 * ((L + TAB_LPB - 1) / TAB_LPB), TPB, 0, s>>>(
             c->locus_tot.p, c->loc_int.p + 6 * (size_t)L, c->loc_int.p + 7 * (size_t)L, L, make_lbc(c), mf_unclamped, mf, 0,
-            nullptr, c->tab.p, c->tiled_ready ? c->tab13.p : nullptr, c->tl_nT * TILE_L, nullptr, c->lng.p, c->lng_n);
+            nullptr, c->tab.p, c->tiled_ready ? c->tab16.p : nullptr, c->tl_nT * TILE_L, nullptr, c->lng.p, c->lng_n);
         c->launches++;
     }
     phase_end(c, CLX_PHASE_TABLES);
@@ -463,13 +464,15 @@ int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used
     // get_loci_used_for_posterior_calc pushes true on both branches (main.rs:301-303): every locus is scored
     phase_begin(c, CLX_PHASE_SCORE);
     if (use_tiled(c)) {
-        for (int t = 0; t < 3; ++t) CLX_TRY(score_tiled(c, t, false, false));
+        // two passes over the run stream instead of three: {minority, majority} share the 16-byte slots of pass 0
+        CLX_TRY(score_tiled(c, SCORE_POST_AB));
+        CLX_TRY(score_tiled(c, SCORE_POST_C));
     } else {
         launch_score_rows<3, false>(c, c->score_G);
     }
     phase_end(c, CLX_PHASE_SCORE);
     if (N) {
-        k_posterior<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->ll.p, N, c->row_ptr.p, c->excl_bits.p, pp, c->post.p, c->post_u8.p);
+        k_posterior<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->post_ll.p, N, c->row_ptr.p, c->excl_bits.p, pp, c->post.p, c->post_u8.p);
         c->launches++;
     }
     CLX_CUDA(c, cudaStreamSynchronize(s));

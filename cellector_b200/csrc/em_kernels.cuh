@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(256) k_tables(const unsigned long long* __rest
                                                 const unsigned long long* __restrict__ raw_min_alt, uint32_t n_loci,
                                                 Lbc10 lbc, double mf, double mf_clamped, int with_expected,
                                                 const uint8_t* __restrict__ used, double* __restrict__ tab,
-                                                double* __restrict__ tab13, uint32_t n_loci_pad,
+                                                double* __restrict__ tab16, uint32_t n_loci_pad,
                                                 DeviceStats* __restrict__ st_clear, const double* __restrict__ lng,
                                                 uint32_t lng_n) {
     static_assert(K_LIGHT == 3, "task layout below is for K_LIGHT == 3");
@@ -150,18 +150,23 @@ __global__ void __launch_bounds__(256) k_tables(const unsigned long long* __rest
     const uint32_t n_here = n_loci - l0 < (uint32_t)TAB_LPB ? n_loci - l0 : (uint32_t)TAB_LPB;
     double* dst = tab + ((size_t)t * n_loci + l0) * TAB_STRIDE;
     for (uint32_t i = tid; i < n_here * TAB_STRIDE; i += blockDim.x) dst[i] = (&s_rec[0][0])[i];
-    // compact 13-double records for the tiled scoring kernel (numerics.cuh): zeros for a switched-off locus
-    if (tab13 != nullptr) {
-        double* d13 = tab13 + ((size_t)t * n_loci_pad + l0) * TAB13;
-        for (uint32_t i = tid; i < n_here * TAB13; i += blockDim.x) {
-            const uint32_t ll = i / TAB13, p = i % TAB13;
-            double v = 0.0;
-            if (s_on[ll] && p < 12) {
-                // p < 9: T slot p(a, n) = n(n+1)/2 - 1 + a;  9..11: E(n = p - 8)
-                const int n = p < 2 ? 1 : (p < 5 ? 2 : (p < 9 ? 3 : (int)p - 8));
-                v = p < 9 ? s_rec[ll][tab_idx_T((int)p - (n * (n + 1)) / 2 + 1, n)] : s_rec[ll][tab_idx_E(n)];
+    // 16-byte slots of the run-stream scoring kernel (numerics.cuh).  MODE 0: {T, E(n)}, zeros for a switched-off
+    // locus.  MODE 1 (posterior pass): table 0 / 1 are the two halves of pass 0, table 2 is the first half of pass 1
+    // (its second half stays 0.0 from the allocation).
+    if (tab16 != nullptr) {
+        const uint32_t pass = (MODE == 1 && t == 2) ? 1u : 0u, half = (MODE == 1 && t == 1) ? 1u : 0u;
+        double* d16 = tab16 + (((size_t)pass * n_loci_pad + l0) * TAB_SLOTS) * 2;
+        for (uint32_t i = tid; i < n_here * TAB_SLOTS; i += blockDim.x) {
+            const uint32_t ll = i / TAB_SLOTS, p = i % TAB_SLOTS;
+            const int n = p < 2 ? 1 : (p < 5 ? 2 : 3);
+            const bool on = s_on[ll] != 0;
+            const double v = on ? s_rec[ll][tab_idx_T((int)p - (n * (n + 1)) / 2 + 1, n)] : 0.0;
+            if (MODE == 0) {
+                d16[2 * i] = v;
+                d16[2 * i + 1] = on ? s_rec[ll][tab_idx_E(n)] : 0.0;
+            } else {
+                d16[2 * i + half] = v;
             }
-            d13[i] = v;
         }
     }
 }
@@ -283,7 +288,7 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
 // phases.  Expressions are those of k_tables<0> / build_locus_table, operation for operation.  Thread 0.. of block
 // 0 also clears the per-iteration DeviceStats.
 __global__ void __launch_bounds__(256) k_tables_em(EmCounts cnts, uint32_t n_loci, Lbc10 lbc, int with_expected,
-                                                   double* __restrict__ tab, double* __restrict__ tab13,
+                                                   double* __restrict__ tab, double* __restrict__ tab16,
                                                    DeviceStats* __restrict__ st_clear, unsigned int* __restrict__ zero_buf,
                                                    uint32_t zero_words) {
     __shared__ double s_lbc[10];
@@ -301,13 +306,12 @@ __global__ void __launch_bounds__(256) k_tables_em(EmCounts cnts, uint32_t n_loc
     em_alpha_beta(cnts, l, &alpha, &beta, &den);
     const bool on = den == den;
     double* rec = tab + (size_t)l * TAB_STRIDE;
-    double* r13 = tab13 != nullptr ? tab13 + (size_t)l * TAB13 : nullptr;
+    double* r16 = tab16 != nullptr ? tab16 + (size_t)l * TAB_SLOTS * 2 : nullptr;  // {T(a | n), E(n)} slots (numerics.cuh)
     if (n == 1) {
         rec[3] = on ? 0.0 : quiet_nan();
         rec[TAB_DEN] = den;
         rec[TAB_ALPHA] = alpha;
         rec[TAB_BETA] = beta;
-        if (r13) r13[12] = 0.0;
     }
     // rolled loops on purpose (small code: the kernel runs for microseconds and instruction fetch showed up first)
     double pm0 = 0.0, pm1 = 0.0, pm2 = 0.0, pm3 = 0.0;
@@ -334,10 +338,9 @@ __global__ void __launch_bounds__(256) k_tables_em(EmCounts cnts, uint32_t n_loc
     for (int a = 0; a <= n; ++a) {
         const double v = a == 0 ? pm0 : (a == 1 ? pm1 : (a == 2 ? pm2 : pm3));
         rec[tab_idx_T(a, n)] = on ? v : quiet_nan();
-        if (r13) r13[tab13_T(a, n)] = on ? v : 0.0;
+        if (r16) reinterpret_cast<double2*>(r16)[tab_slot(a, n)] = on ? make_double2(v, e) : make_double2(0.0, 0.0);
     }
     rec[tab_idx_E(n)] = e;
-    if (r13) r13[tab13_E(n)] = on ? e : 0.0;
 }
 
 // One CTA per giant entry (total > HEAVY_GIANT): streaming max / sum logsumexp over k = 0..n in fixed chunks.

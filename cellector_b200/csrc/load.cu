@@ -192,7 +192,8 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
              const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt) {
     cudaStream_t s = c->stream;
     c->loaded = false;
-    if (nnz0 >= 0xFFFFFFFFull) return fail(c, CLX_ERR_ARG, "more than 2^32-1 nonzeros per GPU: shard the cells over more ranks");
+    // every cub call below takes a 32-bit signed item count
+    if (nnz0 >= 0x7FFFFFFFull) return fail(c, CLX_ERR_ARG, "more than 2^31-2 nonzeros per GPU: shard the cells over more ranks");
     if (nnz0 > 0 && (!locus || !cell || !ref)) return fail(c, CLX_ERR_ARG, "null COO array");
     c->n_cells = n_cells;
     c->n_loci0 = n_loci0;

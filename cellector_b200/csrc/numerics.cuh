@@ -35,14 +35,15 @@ CLX_HD int tab_idx_E(int n) { return n == 1 ? 2 : (n == 2 ? 7 : 12); }
 // index of ln C(n, a) in the 10-entry constant block for n <= 3
 CLX_HD int lbc_idx(int a, int n) { return (n * (n + 1)) / 2 + a; }
 
-// Compact record of the tiled scoring kernel: 13 doubles (odd stride: spreads shared-memory banks)
-//   [0..1] T(.|1)  [2..4] T(.|2)  [5..8] T(.|3)  [9..11] E(1..3)  [12] 0.0
-// slot p(a, n) = n(n+1)/2 - 1 + a; every slot of a switched-off locus is 0.0 (loci_used_per_cell is kept separately).
-constexpr int TAB13 = 13;
-constexpr int TILE_L = 512;   // loci per table tile (53,248 bytes in shared memory)
-constexpr int TL_WARPS = 32;  // warps per CTA of the tiled kernel; a cell belongs to warp (cell_local % TL_WARPS)
-CLX_HD int tab13_T(int a, int n) { return (n * (n + 1)) / 2 - 1 + a; }
-CLX_HD int tab13_E(int n) { return 8 + n; }
+// Staged table tile of the run-stream scoring kernel (tiled.cu): per locus TAB_SLOTS 16-byte slots {T(a | n), E(n)},
+// slot p(a, n) = n(n+1)/2 - 1 + a — one LDS.128 per nonzero fetches both the log-pmf and the expected value of its
+// total.  Every slot of a switched-off locus is {0.0, 0.0} (loci_used_per_cell is kept separately); slot TILE_SLOTS
+// of a staged tile is the all-zero slot padding entries point at.  In the posterior pass the same slots carry
+// {T_minority, T_majority} (pass 0) and {T_doublet, 0} (pass 1).
+constexpr int TILE_L = 512;                          // loci per table tile
+constexpr int TAB_SLOTS = 9;                         // (a | n) pairs with n <= K_LIGHT
+constexpr int TILE_SLOTS = TILE_L * TAB_SLOTS;       // 4608 slots = 73,728 bytes of shared memory per tile
+CLX_HD int tab_slot(int a, int n) { return (n * (n + 1)) / 2 - 1 + a; }
 
 struct Lanczos {
     // statrs GAMMA_DK / GAMMA_R / constants

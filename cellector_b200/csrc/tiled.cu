@@ -1,30 +1,35 @@
-// tiled.cu — the tiled per-cell scoring path (get_cell_log_likelihoods, cellector/src/main.rs:541-591).
+// tiled.cu — the per-cell scoring path (get_cell_log_likelihoods, cellector/src/main.rs:541-591) as a run-stream
+// kernel over shared-memory table tiles.
 //
-// Why: a memo-table gather served by L1/L2 costs one L1 wavefront per nonzero (measured: the gather kernel is
-// bound at ~1 distinct line per SM-cycle, ~25 % of the HBM roofline).  Here the per-locus memo records are staged
-// in SHARED memory by TMA bulk copies (cp.async.bulk + mbarrier), tile by tile, and the nonzeros are re-laid out
-// so that every CTA streams exactly the entries that hit the tile it holds:
+// Why this shape: a memo-table gather served by L1/L2 costs one L1 wavefront per nonzero (measured in round 1: the
+// gather kernel k_score_rows stops at ~20 % of the HBM roofline), so the per-locus memo slots are staged in SHARED
+// memory by TMA bulk copies (cp.async.bulk + mbarrier), tile by tile, and the nonzeros are re-laid out so that every
+// CTA streams exactly the entries that hit the tile it holds.  The kernel is then bound by shared-memory wavefronts
+// (one random 16-byte lookup per nonzero), and the layout below is built to spend them on nothing else:
 //
-//   * only "light" entries (total 1..3) are kept: zero-total entries contribute exactly 0.0 and heavy entries
-//     come from the heavy lists; loci_used_per_cell (main.rs:575) is kept as a counter array instead (n_used);
-//   * a RUN = the entries of one cell inside one locus tile (TILE_L loci), in file order; an entry is 2 bytes:
-//     locus_local << 6 | (total - 1) << 4 | slot, slot = index of T(alt | total) in the 13-double compact record
-//     of numerics.cuh (E(total) sits at 9 + total - 1);
-//   * a cell belongs to ONE warp of the CTA for the whole pass (cell_local % TL_WARPS), so the read-modify-writes of
-//     its shared-memory accumulator never race: no atomics, and no CTA barrier between tiles;
-//   * the runs of one (cell block, tile, warp) SUB-UNIT are ordered by length and taken 32 at a time: a GROUP.  A
-//     group is stored TRANSPOSED — entry j of lane l at j * 32 + l, shorter runs padded with a null entry that
-//     points at an all-zero record — so one lane sums one run with conflict-free 64-byte warp loads, no per-lane
-//     trip counts, no shuffles; runs of a group have similar lengths, so padding is small (~2.6 B per nonzero);
-//   * groups are cut into BATCHES of at most BATCH_ITERS iterations ([16 B header][32 one-byte cell indices if first][entries])
-//     and batches are packed into PACKETS of at most STAGE_BYTES — one TMA bulk copy each into the warp's ring;
-//   * sub-units are numbered warp-major ((cell block, warp), then tile): the packets one warp consumes over the
-//     consecutive tiles of a work item are ONE consecutive range of the descriptor list {start, size}, which the
-//     warp reads 32 at a time with one coalesced load and hands round by shuffle (no dependent global load sits
-//     between two packets); a packet's header names its tile, and that is how the warp learns a tile has ended;
-//   * a work ITEM = one cell block x a range of consecutive tiles; the CTA keeps the block's accumulators in
-//     shared memory across the range and writes one partial per cell at the end; k_score_finish adds the
-//     partials of a cell block in item order (fixed order: deterministic), appends the heavy values and normalises.
+//   * only "light" entries (total 1..3) are kept: zero-total entries contribute exactly 0.0 and heavy entries come
+//     from the heavy lists; loci_used_per_cell (main.rs:575) is kept as a counter array instead (n_used);
+//   * a table slot is 16 bytes {T(alt | total), E(total)} (numerics.cuh): ONE LDS.128 per nonzero fetches the log-pmf
+//     and the expected log-likelihood term;
+//   * a RUN = the entries of one cell inside one locus tile (TILE_L loci); an entry is one 16-bit word: the slot
+//     index inside the staged tile (locus_local * 9 + slot(alt, total));
+//   * a cell belongs to ONE warp of the CTA for the whole pass (cell_local % W): its shared-memory accumulator is
+//     updated with plain read-modify-writes, no atomics, and there is no CTA barrier between tiles;
+//   * the runs of one (cell block, warp, tile) SUB-UNIT are ordered by length and taken 32 at a time: a GROUP.  Lane l
+//     sums run l of the group in registers; the group runs for its longest run (shorter runs are padded with the
+//     all-zero slot) and ends with ONE warp-wide accumulator update.  With W = 16 and 4096-cell blocks a sub-unit
+//     pools 256 runs, so the runs of a group have almost equal lengths (~17 % padded lookups at 5 entries per run);
+//   * inside a group the runs are dealt to lanes so that the 8 lanes of a quarter warp own accumulator slots in
+//     distinct 16-byte bank groups (the update is two conflict-free 128-bit shared-memory instructions);
+//   * the words of a lane are consecutive in its own 16-byte pieces: chunk c of a warp is 32 x 16 bytes, read with
+//     one coalesced LDG.128 per lane, three chunks ahead of the one being summed (registers, no staging ring);
+//     control is in-band and warp-uniform: a HEADER word opens a group (accumulator index of the lane's cell, "this
+//     sub-unit starts the next tile", "nothing follows"), the last entry word of a group carries a flag;
+//   * sub-units are numbered warp-major ((cell block, warp), then tile) and start on chunk boundaries, so the words a
+//     warp consumes over the consecutive tiles of a work item are ONE range of chunks;
+//   * a work ITEM = one cell block x a range of consecutive tiles; the CTA keeps the block's accumulators in shared
+//     memory across the range and writes one partial per cell at the end; k_score_finish adds the partials of a
+//     cell block in item order (fixed order: deterministic), appends the heavy values and normalises.
 #include <cub/cub.cuh>
 #include <stdio.h>
 
@@ -38,14 +43,20 @@ namespace clx {
 namespace {
 
 constexpr int TPB = 256;
-constexpr uint32_t NB_MAX = 3072;        // cells per block: 16 B of accumulators each = 48 KB of shared memory
-constexpr uint32_t NB_MIN = 256;
-constexpr int RING_STAGES = 2;           // packets per warp: one being summed, one in flight
-constexpr uint32_t STAGE_BYTES = 1024;
-constexpr uint32_t BATCH_ITERS = 15;     // 16 + 16 + 32 + 64 * 15 = 1024 <= STAGE_BYTES
-constexpr uint32_t NULL_ENTRY = (uint32_t)TILE_L << 6;  // record TILE_L of a staged tile is all zeros
-static_assert(16 + 16 + 32 + 64 * BATCH_ITERS <= STAGE_BYTES, "a packet holds at least one full batch");
-static_assert(TL_WARPS == 32, "one CTA of 1024 threads");
+constexpr uint32_t NB_MAX = 4096;        // cells per block: 16 B of accumulators each = 64 KB of shared memory
+constexpr uint32_t W_MAX = 16;           // warps per CTA
+constexpr uint32_t CHUNK_WORDS = 8;      // 16-bit words per lane and chunk (one LDG.128)
+constexpr int PF = 3;                    // chunks in flight per lane ahead of the one being summed
+// word encoding (all flags are identical in the 32 lanes of a chunk position, except WD_IDLE)
+constexpr uint32_t WD_HEADER = 0x8000u;   // header word: opens a group (or is a no-op)
+constexpr uint32_t WD_NEWTILE = 0x4000u;  // header: this sub-unit belongs to the next tile of the item
+constexpr uint32_t WD_NOP = 0x2000u;      // header: no group follows (empty sub-unit / chunk padding)
+constexpr uint32_t WD_IDLE = 0x1000u;     // header: this lane has no run in the group
+constexpr uint32_t WD_QMASK = 0x01FFu;    // header: index of the lane's cell among the warp's cells
+constexpr uint32_t WD_LAST = 0x4000u;     // entry word: last step of the group
+constexpr uint32_t WD_SLOT = 0x1FFFu;     // entry word: slot inside the staged tile
+constexpr uint32_t NULL_SLOT = (uint32_t)TILE_SLOTS;
+static_assert(TILE_SLOTS < 0x1FFF, "slot index fits 13 bits");
 
 inline unsigned grid_for(uint64_t n, int tpb = TPB, unsigned cap = 148u * 16u) {
     uint64_t g = (n + tpb - 1) / tpb;
@@ -70,7 +81,7 @@ __global__ void k_tile_keys(const RowEntry* __restrict__ csr, const uint32_t* __
         if (n >= 1 && n <= (uint32_t)K_LIGHT) {
             const uint32_t cb = c / NB, cl = c % NB, t = e.locus / TILE_L, ll = e.locus % TILE_L;
             k = (((unsigned long long)cb * nT + t) << 12) | cl;
-            v = (uint16_t)((ll << 6) | ((n - 1u) << 4) | (uint32_t)tab13_T((int)e.alt, (int)n));
+            v = (uint16_t)(ll * (uint32_t)TAB_SLOTS + (uint32_t)tab_slot((int)e.alt, (int)n));
             ++mine;
         }
         keys[i] = k;
@@ -95,23 +106,21 @@ __device__ __forceinline__ uint64_t lower_bound_dev(const T* __restrict__ a, uin
 }
 
 // Sub-unit = the runs of one warp in one (cell block, tile) unit.  Sub-units are numbered warp-major,
-// su = (cell block * TL_WARPS + warp) * nT + tile, so that the packets a warp consumes over consecutive tiles of a
-// work item are consecutive in the packet list and in the stream.
-__device__ __forceinline__ unsigned long long sub_unit_of(unsigned long long unit, uint32_t w, uint32_t nT) {
+// su = (cell block * W + warp) * nT + tile, so that the chunks a warp consumes over consecutive tiles of a work item
+// are consecutive in the stream.
+__device__ __forceinline__ unsigned long long sub_unit_of(unsigned long long unit, uint32_t w, uint32_t nT, uint32_t W) {
     const unsigned long long cb = unit / nT, t = unit % nT;
-    return (cb * TL_WARPS + w) * nT + t;
+    return (cb * W + w) * nT + t;
 }
-// runs (unique keys + counts, from cub::DeviceRunLengthEncode) -> sort key (sub-unit << 16 | 0xFFFF - count): longest
-// first inside a sub-unit
+// runs (unique keys + counts, from cub::DeviceRunLengthEncode) -> sort key (sub-unit << 16 | 0xFFFF - min(count, 0xFFFF)):
+// longest first inside a sub-unit.  The order only decides how much padding a group carries, never the result.
 __global__ void k_run_keys(const unsigned long long* __restrict__ ukeys, const int* __restrict__ counts, uint32_t n_runs,
-                           uint32_t nT, unsigned long long* __restrict__ key2, uint32_t* __restrict__ idx,
-                           unsigned int* __restrict__ too_long) {
+                           uint32_t nT, uint32_t W, unsigned long long* __restrict__ key2, uint32_t* __restrict__ idx) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_runs) return;
     const uint32_t cnt = (uint32_t)counts[r];
-    if (cnt > 0xFFFFu) atomicOr(too_long, 1u);
     const unsigned long long unit = ukeys[r] >> 12, cl = ukeys[r] & 0xFFFull;
-    key2[r] = (sub_unit_of(unit, (uint32_t)(cl % TL_WARPS), nT) << 16) | (unsigned long long)(0xFFFFu - (cnt > 0xFFFFu ? 0xFFFFu : cnt));
+    key2[r] = (sub_unit_of(unit, (uint32_t)(cl % W), nT, W) << 16) | (unsigned long long)(0xFFFFu - (cnt > 0xFFFFu ? 0xFFFFu : cnt));
     idx[r] = r;
 }
 // first sorted run of every sub-unit, su in [0, n_sub]
@@ -120,109 +129,134 @@ __global__ void k_sub_runs(const unsigned long long* __restrict__ key2_sorted, u
     const uint64_t su = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     if (su <= n_sub) sub_run[su] = (uint32_t)lower_bound_dev<unsigned long long>(key2_sorted, 0, n_runs, su << 16);
 }
-// cost of every unit for the work-item partition: the stream bytes (in quads) of its 32 sub-units — padded groups
-// included, so a ragged cell block whose groups are mostly padding is not mistaken for cheap work
-__global__ void k_unit_cost(const uint32_t* __restrict__ n_quads, uint32_t n_units, uint32_t nT,
+
+__device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, off));
+    return v;
+}
+
+// one warp per sub-unit: words per lane = sum over groups of (1 header + longest run), at least the one header an
+// empty sub-unit needs; rounded up to whole chunks.  steps = lookup steps (padding included) of the sub-unit.
+__global__ void k_sub_count(const uint32_t* __restrict__ sub_run, const uint32_t* __restrict__ idx_sorted,
+                            const int* __restrict__ counts, uint64_t n_sub, uint32_t* __restrict__ n_chunks,
+                            unsigned long long* __restrict__ total_steps) {
+    const uint64_t su = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    if (su > n_sub) return;
+    if (su == n_sub) {
+        if (lane == 0) n_chunks[su] = 0;
+        return;
+    }
+    const uint32_t r0 = sub_run[su], r1 = sub_run[su + 1];
+    uint64_t words = 0, steps = 0;
+    for (uint32_t g0 = r0; g0 < r1; g0 += 32) {
+        const uint32_t M = warp_max_u32(g0 + lane < r1 ? (uint32_t)counts[idx_sorted[g0 + lane]] : 0u);
+        words += 1u + M;
+        steps += M;
+    }
+    if (words == 0) words = 1;
+    if (lane == 0) {
+        n_chunks[su] = (uint32_t)((words + CHUNK_WORDS - 1) / CHUNK_WORDS);
+        if (steps) atomicAdd(total_steps, (unsigned long long)steps);
+    }
+}
+// cost of every unit for the work-item partition: the chunks of its W sub-units
+__global__ void k_unit_cost(const uint32_t* __restrict__ n_chunks, uint32_t n_units, uint32_t nT, uint32_t W,
                             unsigned long long* __restrict__ unit_cost) {
     const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
     if (u >= n_units) return;
     unsigned long long sum = 0;
-    for (uint32_t w = 0; w < (uint32_t)TL_WARPS; ++w) sum += n_quads[sub_unit_of(u, w, nT)];
+    for (uint32_t w = 0; w < W; ++w) sum += n_chunks[sub_unit_of(u, w, nT, W)];
     unit_cost[u] = sum;
 }
 
-// The packets of one sub-unit, generated in order; F is called once per batch with
-//   (packet index within the sub-unit, byte offset of the batch inside the sub-unit's stream, group, batch, m, first, last)
-// and P once per packet with (packet index, start offset, size, n_batches).  Offsets are multiples of 16.
-template <typename F, typename P>
-__device__ __forceinline__ void walk_sub_unit(const uint32_t* __restrict__ idx_sorted, const int* __restrict__ counts,
-                                              uint32_t r0, uint32_t r1, F&& on_batch, P&& on_packet) {
-    uint32_t pk = 0, pk_start = 0, pk_bytes = 0, pk_batches = 0;  // current packet (bytes includes its 16-byte header)
-    for (uint32_t g0 = r0; g0 < r1; g0 += 32) {
-        const uint32_t M = (uint32_t)counts[idx_sorted[g0]];  // longest run of the group
-        for (uint32_t j0 = 0; j0 < M; j0 += BATCH_ITERS) {
-            const uint32_t m = min(BATCH_ITERS, M - j0);
-            const bool first = j0 == 0, last = j0 + m >= M;
-            const uint32_t bytes = 16u + (first ? 32u : 0u) + 64u * m;
-            if (pk_batches && pk_bytes + bytes > STAGE_BYTES) {
-                on_packet(pk, pk_start, pk_bytes, pk_batches);
-                pk_start += pk_bytes;
-                ++pk;
-                pk_bytes = 0;
-                pk_batches = 0;
-            }
-            if (!pk_batches) pk_bytes = 16u;
-            on_batch(pk, pk_start + pk_bytes, g0, j0, m, first, last);
-            pk_bytes += bytes;
-            ++pk_batches;
+// one warp per sub-unit writes its chunks.  Lanes emit in lock step; a lane collects 8 words and stores one uint4.
+struct WordSink {
+    uint4* dst;  // this lane's piece of the current chunk
+    unsigned long long lo, hi;
+    uint32_t pos;
+    __device__ __forceinline__ void put(uint32_t w16) {
+        if (pos < 4) lo |= (unsigned long long)w16 << (16 * pos);
+        else hi |= (unsigned long long)w16 << (16 * (pos - 4));
+        if (++pos == CHUNK_WORDS) {
+            *dst = make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+            dst += 32;
+            lo = hi = 0;
+            pos = 0;
         }
     }
-    if (pk_batches) on_packet(pk, pk_start, pk_bytes, pk_batches);
-}
+};
 
-__global__ void k_sub_count(const uint32_t* __restrict__ sub_run, const uint32_t* __restrict__ idx_sorted,
-                            const int* __restrict__ counts, uint64_t n_sub, uint32_t* __restrict__ n_pk,
-                            uint32_t* __restrict__ n_quads) {
-    const uint64_t su = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-    if (su > n_sub) return;
-    uint32_t packets = 0, bytes = 0;
-    if (su < n_sub)
-        walk_sub_unit(idx_sorted, counts, sub_run[su], sub_run[su + 1],
-                      [](uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, bool, bool) {},
-                      [&](uint32_t, uint32_t, uint32_t sz, uint32_t) { ++packets; bytes += sz; });
-    n_pk[su] = packets;
-    n_quads[su] = bytes >> 4;
-}
-
-// one warp per sub-unit writes its packets: packet header {n_batches, tile}, batch header {m | first << 8 | last << 9},
-// the 32 cell ids of a first batch, and the transposed entries; and the packet's descriptor {start quad, size in quads}
-__global__ void k_sub_fill(const uint32_t* __restrict__ sub_run, const uint32_t* __restrict__ pk_base,
-                           const uint32_t* __restrict__ q_base, const uint32_t* __restrict__ idx_sorted,
-                           const unsigned long long* __restrict__ ukeys, const int* __restrict__ counts,
-                           const unsigned long long* __restrict__ run_start, const uint16_t* __restrict__ vals_sorted,
-                           uint64_t n_sub, uint32_t nT, uint2* __restrict__ pk_d, uint32_t* __restrict__ stream) {
+__global__ void __launch_bounds__(TPB) k_sub_fill(const uint32_t* __restrict__ sub_run, const uint32_t* __restrict__ chunk_off,
+                                                  const uint32_t* __restrict__ idx_sorted, const unsigned long long* __restrict__ ukeys,
+                                                  const int* __restrict__ counts, const unsigned long long* __restrict__ run_start,
+                                                  const uint16_t* __restrict__ vals_sorted, uint64_t n_sub, uint32_t W,
+                                                  uint4* __restrict__ stream) {
+    __shared__ uint32_t s_cnt[TPB / 32][32], s_q[TPB / 32][32];
+    __shared__ unsigned long long s_src[TPB / 32][32];
     const uint64_t su = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
-    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     if (su >= n_sub) return;
     const uint32_t r0 = sub_run[su], r1 = sub_run[su + 1];
-    unsigned char* base = reinterpret_cast<unsigned char*>(stream) + (size_t)q_base[su] * 16;
-    const uint32_t pkb = pk_base[su], qb = q_base[su];
-    walk_sub_unit(
-        idx_sorted, counts, r0, r1,
-        [&](uint32_t, uint32_t off, uint32_t g0, uint32_t j0, uint32_t m, bool first, bool last) {
-            uint32_t* hdr = reinterpret_cast<uint32_t*>(base + off);
-            if (lane < 4) hdr[lane] = lane == 0 ? (m | (first ? 0x100u : 0u) | (last ? 0x200u : 0u)) : 0u;
-            const uint32_t r = g0 + lane;
-            uint32_t cnt = 0;
-            unsigned long long src = 0;
-            uint32_t cell = 0xFFFFu;
-            if (r < r1) {
-                const uint32_t rid = idx_sorted[r];
-                cnt = (uint32_t)counts[rid];
-                src = run_start[rid];
-                cell = (uint32_t)(ukeys[rid] & 0xFFFull);
+    WordSink sink;
+    sink.dst = stream + (size_t)chunk_off[su] * 32 + lane;
+    sink.lo = sink.hi = 0;
+    sink.pos = 0;
+    if (r0 == r1) sink.put(WD_HEADER | WD_NEWTILE | WD_NOP);
+    for (uint32_t g0 = r0; g0 < r1; g0 += 32) {
+        const uint32_t r = g0 + lane;
+        uint32_t cnt = 0, q = 0;
+        unsigned long long src = 0;
+        bool has = r < r1;
+        if (has) {
+            const uint32_t rid = idx_sorted[r];
+            cnt = (uint32_t)counts[rid];
+            src = run_start[rid];
+            q = (uint32_t)(ukeys[rid] & 0xFFFull) / W;  // accumulator slot of the cell = warp * Q + q, Q a multiple of 8
+        }
+        const uint32_t M = warp_max_u32(cnt);
+        // deal the runs to lanes so that a quarter warp's accumulator slots fall in distinct 16-byte bank groups: rank
+        // the runs by (q mod 8, lane) and give rank k to lane (k mod 4) * 8 + k / 4; idle lanes keep what is left
+        {
+            const uint32_t res = q & 7u;
+            uint32_t rank = 0;
+#pragma unroll
+            for (uint32_t v = 0; v < 8; ++v) {
+                const uint32_t m = __ballot_sync(0xffffffffu, has && res == v);
+                if (has && v < res) rank += __popc(m);
+                if (has && v == res) rank += __popc(m & ((1u << lane) - 1u));
             }
-            uint16_t* p16 = reinterpret_cast<uint16_t*>(base + off + 16);
-            if (first) {
-                // the run's cell as q = cell_local / 32 (cell_local % 32 is the owning warp): one byte, 0xFF = no run
-                reinterpret_cast<uint8_t*>(p16)[lane] = cell == 0xFFFFu ? (uint8_t)0xFF : (uint8_t)(cell >> 5);
-                p16 += 16;
-            }
-            for (uint32_t j = 0; j < m; ++j) {
-                const uint32_t jj = j0 + j;
-                p16[j * 32 + lane] = jj < cnt ? vals_sorted[src + jj] : (uint16_t)NULL_ENTRY;
-            }
-        },
-        [&](uint32_t pk, uint32_t start, uint32_t sz, uint32_t nb) {
-            if (lane == 0) {
-                pk_d[pkb + pk] = make_uint2(qb + (start >> 4), sz >> 4);
-                uint32_t* ph = reinterpret_cast<uint32_t*>(base + start);
-                ph[0] = nb;
-                ph[1] = (uint32_t)(su % nT);  // the locus tile this packet indexes
-                ph[2] = 0;
-                ph[3] = 0;
-            }
-        });
+            const uint32_t m_has = __ballot_sync(0xffffffffu, has);
+            if (!has) rank = __popc(m_has) + __popc(~m_has & ((1u << lane) - 1u));
+            const uint32_t tgt = (rank & 3u) * 8u + (rank >> 2);
+            s_cnt[wib][tgt] = has ? cnt : 0u;
+            s_q[wib][tgt] = has ? q : 0xFFFFFFFFu;
+            s_src[wib][tgt] = src;
+            __syncwarp();
+            cnt = s_cnt[wib][lane];
+            q = s_q[wib][lane];
+            src = s_src[wib][lane];
+            has = q != 0xFFFFFFFFu;
+            __syncwarp();
+        }
+        sink.put(WD_HEADER | (g0 == r0 ? WD_NEWTILE : 0u) | (has ? (q & WD_QMASK) : WD_IDLE));
+        for (uint32_t j = 0; j < M; ++j) {
+            const uint32_t slot = j < cnt ? (uint32_t)vals_sorted[src + j] : NULL_SLOT;
+            sink.put(slot | (j + 1 == M ? WD_LAST : 0u));
+        }
+    }
+    while (sink.pos != 0) sink.put(WD_HEADER | WD_NOP);
+}
+
+// per queue slot and warp: the warp's chunk range over the item's tiles (one consecutive range, see sub_unit_of)
+__global__ void k_item_rng(const uint4* __restrict__ item_q, uint32_t n_items, const uint32_t* __restrict__ chunk_off, uint32_t nT,
+                           uint32_t W, uint2* __restrict__ item_rng) {
+    const uint32_t q = blockIdx.x, w = threadIdx.x;
+    if (q >= n_items || w >= W) return;
+    const uint4 it = item_q[q];
+    const size_t su0 = ((size_t)it.x * W + w) * nT + it.y;
+    item_rng[(size_t)q * W + w] = make_uint2(chunk_off[su0], chunk_off[su0 + it.z]);
 }
 
 }  // namespace
@@ -253,219 +287,171 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
             : "memory");
     } while (!ok);
 }
-
-constexpr size_t TL_TAB_BYTES = (size_t)TILE_L * TAB13 * 8;                             // bytes one table bulk copy moves
-constexpr size_t TL_TAB_BUF = (((size_t)(TILE_L + 1) * TAB13 * 8) + 127) / 128 * 128;   // + the all-zero record
-constexpr size_t TL_ACC_BYTES = (size_t)NB_MAX * 16;
-constexpr size_t TL_RING_BYTES = (size_t)TL_WARPS * RING_STAGES * STAGE_BYTES;
-constexpr size_t TL_SMEM = 2 * TL_TAB_BUF + TL_ACC_BYTES + TL_RING_BYTES + (2 + TL_WARPS * RING_STAGES) * 8 + 16;
-static_assert(TL_SMEM <= 227 * 1024, "shared memory budget of the tiled kernel");
-
-// Per-lane state of the run a lane is summing (a group may span several batches and packets).
-struct RunState {
-    double sT, sE;
-    uint32_t cell;
-};
-
-// One packet = n batches.  In a batch, lane l reads entry j at j * 32 + l (one conflict-free 64-byte warp load),
-// looks T and E up in the staged table tile and adds them to its run's sums, in file order; the last batch of a
-// group adds the run to the cell's accumulator (this warp owns the cell: plain read-modify-write).
-// Accumulator slot of a cell: the cells of one warp are cell_local = 32 q + w, and a group touches 32 of them at
-// once, so slot = w * Q + q puts them in neighbouring 16-byte slots (slot = cell_local would put all 32 in the
-// same banks: an 8-way conflict on every read-modify-write).
-__device__ __forceinline__ uint32_t acc_slot(uint32_t cell_local, uint32_t Q) { return (cell_local & 31u) * Q + (cell_local >> 5); }
-
-template <bool WITH_E>
-__device__ __forceinline__ void tiled_packet(const unsigned char* __restrict__ pk, const double* __restrict__ tab,
-                                             double2* __restrict__ acc, int lane, int w, RunState& st, uint32_t Q) {
-    const uint32_t nb = *reinterpret_cast<const uint32_t*>(pk);
-    const unsigned char* p = pk + 16;
-    for (uint32_t b = 0; b < nb; ++b) {
-        const uint32_t hdr = *reinterpret_cast<const uint32_t*>(p);
-        const uint32_t m = hdr & 0xFFu;
-        const uint16_t* e = reinterpret_cast<const uint16_t*>(p + 16);
-        if (hdr & 0x100u) {  // first batch of a group: 32 one-byte cell indices
-            const uint32_t q = reinterpret_cast<const uint8_t*>(e)[lane];
-            st.cell = q == 0xFFu ? 0xFFFFu : (uint32_t)w * Q + q;  // accumulator slot (acc_slot of cell 32 q + w)
-            st.sT = 0.0;
-            st.sE = 0.0;
-            e += 16;
-        }
-        double sT = st.sT, sE = st.sE;
-#pragma unroll 4
-        for (uint32_t j = 0; j < m; ++j) {
-            const uint32_t v = e[j * 32 + lane];
-            const double* rec = tab + (v >> 6) * TAB13;
-            sT += rec[v & 15u];
-            if (WITH_E) sE += rec[9 + ((v >> 4) & 3u)];
-        }
-        st.sT = sT;
-        st.sE = sE;
-#ifdef CLX_TILED_DEBUG
-        if (nb > 64 || m == 0 || m > BATCH_ITERS || ((hdr & 0x200u) && st.cell != 0xFFFFu && st.cell >= 32u * Q))
-            printf("bad batch: blk %d w %d lane %d nb %u b %u hdr %x cell %u\n", blockIdx.x, threadIdx.x >> 5, lane, nb, b, hdr, st.cell);
-#endif
-        if ((hdr & 0x200u) && st.cell != 0xFFFFu) {  // last batch of the group
-            double2 a = acc[st.cell];
-            a.x += sT;
-            a.y += sE;
-            acc[st.cell] = a;
-        }
-        p += 16u + ((hdr & 0x100u) ? 32u : 0u) + 64u * m;
-    }
+// streaming 128-bit load of the run stream: read once, keep it out of L1
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+    return v;
 }
 
-// per queue slot and warp: the warp's packet range over the item's tiles (one consecutive range, see sub_unit_of)
-__global__ void k_item_pk(const uint4* __restrict__ item_q, uint32_t n_items, const uint32_t* __restrict__ pk_base, uint32_t nT,
-                          uint2* __restrict__ item_pk) {
-    const uint32_t q = blockIdx.x, w = threadIdx.x;
-    if (q >= n_items || w >= (uint32_t)TL_WARPS) return;
-    const uint4 it = item_q[q];
-    const size_t su0 = ((size_t)it.x * TL_WARPS + w) * nT + it.y;
-    const uint32_t P0 = pk_base[su0];
-    item_pk[(size_t)q * TL_WARPS + w] = make_uint2(P0, pk_base[su0 + it.z] - P0);
+constexpr size_t TB_BYTES = (size_t)TILE_SLOTS * 16;                              // bytes one table bulk copy moves
+constexpr size_t TB_BUF = (((size_t)(TILE_SLOTS + 1) * 16) + 127) / 128 * 128;    // + the all-zero slot
+constexpr size_t TL_ACC_BYTES = (size_t)NB_MAX * 16;
+constexpr size_t TL_SMEM = 2 * TB_BUF + TL_ACC_BYTES + 64;
+static_assert(TL_SMEM <= 227 * 1024, "shared memory budget of the scoring kernel");
+constexpr uint32_t NOP_PAIR = (WD_HEADER | WD_NOP) | ((WD_HEADER | WD_NOP) << 16);
+
+// Table buffers: tile g of a CTA (counted over all its items) lives in buffer g & 1; tab_full[b] is the mbarrier its
+// bulk copy completes on (parity (g >> 1) & 1), tab_done[b] counts the warps that have finished with the buffer.
+// Handing a buffer over needs no CTA barrier: the last warp to leave tile k starts the copy of tile k + 2 into it
+// (cells never change warps, so accumulators need no barrier either, and warps drift by at most two tiles).
+// Both are out of line: they run once per warp and tile, and inlined at each of the 24 word positions of the
+// unrolled loop they made the kernel 50 KB of code.
+__device__ __noinline__ void leave_tile(unsigned char* smem, uint32_t k, uint32_t g_tile, uint32_t t0, uint32_t ntile, uint32_t nw,
+                                        const double* tab16) {
+    uint64_t* tab_full = reinterpret_cast<uint64_t*>(smem + 2 * TB_BUF + TL_ACC_BYTES);
+    unsigned int* tab_done = reinterpret_cast<unsigned int*>(tab_full + 2);
+    const uint32_t g = g_tile + k;
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) {
+        const unsigned int done = atomicAdd(&tab_done[g & 1], 1u);
+        if (done == nw - 1) {
+            tab_done[g & 1] = 0;
+            if (k + 2 < ntile) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_expect_tx(&tab_full[g & 1], (uint32_t)TB_BYTES);
+                bulk_g2s(smem + (size_t)(g & 1) * TB_BUF, tab16 + (size_t)(t0 + k + 2) * TILE_SLOTS * 2, (uint32_t)TB_BYTES, &tab_full[g & 1]);
+            }
+        }
+    }
+}
+// leaves tile k (if any), waits for tile k + 1; returns the byte offset of its buffer in shared memory
+__device__ __noinline__ uint32_t enter_tile(unsigned char* smem, int k, uint32_t g_tile, uint32_t t0, uint32_t ntile, uint32_t nw,
+                                            const double* tab16) {
+    if (k >= 0) leave_tile(smem, (uint32_t)k, g_tile, t0, ntile, nw, tab16);
+    uint64_t* tab_full = reinterpret_cast<uint64_t*>(smem + 2 * TB_BUF + TL_ACC_BYTES);
+    const uint32_t g = g_tile + (uint32_t)(k + 1);
+    mbar_wait(&tab_full[g & 1], (g >> 1) & 1u);
+    return (g & 1) * (uint32_t)TB_BUF;
 }
 
 // Work queue: CTA b takes queue slot b first, later slots come from an atomic cursor that starts at gridDim.x; the
-// cursor for the NEXT item is fetched while the current one is being scored, so no item waits for the atomic.  The
-// start of an item costs two dependent global loads (slot record + packet range, then the descriptor window) before
-// the first bulk copy goes out.
-template <bool WITH_E>
-__global__ void __launch_bounds__(TL_WARPS * 32, 1)
-    k_score_tiled(const uint32_t* __restrict__ stream, const uint2* __restrict__ pk_d, const uint4* __restrict__ item_q,
-                  const uint2* __restrict__ item_pk, uint32_t n_items, uint32_t* __restrict__ counter,
-                  const double* __restrict__ tab13, uint32_t NB, double* __restrict__ part) {
+// cursor for the NEXT item is fetched while the current one is being scored, so no item waits for the atomic.
+__global__ void __launch_bounds__(W_MAX * 32, 1)
+    k_score_runs(const uint4* __restrict__ stream, const uint4* __restrict__ item_q, const uint2* __restrict__ item_rng,
+                 uint32_t n_items, uint32_t* __restrict__ counter, const double* __restrict__ tab16, uint32_t NB,
+                 double* __restrict__ part) {
     extern __shared__ __align__(128) unsigned char smem[];
-    double2* acc = reinterpret_cast<double2*>(smem + 2 * TL_TAB_BUF);
-    unsigned char* ring = smem + 2 * TL_TAB_BUF + TL_ACC_BYTES;
-    uint64_t* tab_full = reinterpret_cast<uint64_t*>(smem + 2 * TL_TAB_BUF + TL_ACC_BYTES + TL_RING_BYTES);
-    uint64_t* ring_full = tab_full + 2;
-    unsigned int* tab_done = reinterpret_cast<unsigned int*>(ring_full + TL_WARPS * RING_STAGES);  // [2] warps done with a buffer
+    double2* acc = reinterpret_cast<double2*>(smem + 2 * TB_BUF);
+    uint64_t* tab_full = reinterpret_cast<uint64_t*>(smem + 2 * TB_BUF + TL_ACC_BYTES);
+    unsigned int* tab_done = reinterpret_cast<unsigned int*>(tab_full + 2);  // [2] warps done with a buffer
+    uint32_t* s_next = reinterpret_cast<uint32_t*>(tab_done + 2);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const uint32_t Q = (NB + 31u) / 32u;
+    const uint32_t nw = blockDim.x >> 5;
+    const uint32_t Q = NB / nw;  // cells per warp (NB is a multiple of 8 * nw)
     if (tid == 0) {
         mbar_init(&tab_full[0], 1);
         mbar_init(&tab_full[1], 1);
-        for (int i = 0; i < TL_WARPS * RING_STAGES; ++i) mbar_init(&ring_full[i], 1);
         tab_done[0] = 0;
         tab_done[1] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (tid < 2 * TAB13) {  // the all-zero record behind each table buffer (null entries point at it)
-        double* z = reinterpret_cast<double*>(smem + (size_t)(tid / TAB13) * TL_TAB_BUF) + (size_t)TILE_L * TAB13;
-        z[tid % TAB13] = 0.0;
-    }
-    for (uint32_t i = tid; i < 32u * Q; i += blockDim.x) acc[i] = make_double2(0.0, 0.0);
+    if (tid < 2)  // the all-zero slot behind each table buffer (padding entries point at it)
+        reinterpret_cast<double2*>(smem + (size_t)tid * TB_BUF)[TILE_SLOTS] = make_double2(0.0, 0.0);
+    for (uint32_t i = tid; i < NB; i += blockDim.x) acc[i] = make_double2(0.0, 0.0);
     __syncthreads();
     uint32_t g_tile = 0;  // tiles consumed by this CTA so far (buffer = g & 1, parity = (g >> 1) & 1)
-    uint32_t cons_c = 0;  // packets consumed by this warp so far (stage = c % STAGES, parity = (c / STAGES) & 1)
-    unsigned char* my_ring = ring + (size_t)w * RING_STAGES * STAGE_BYTES;
-    uint64_t* my_bar = ring_full + w * RING_STAGES;
-    RunState st;
-    st.sT = 0.0;
-    st.sE = 0.0;
-    st.cell = 0xFFFFu;
-    __shared__ uint32_t s_next;
+    double2* const my_acc = acc + (size_t)w * Q;
     uint32_t qk = blockIdx.x;
     while (qk < n_items) {
         uint32_t nxt = 0;
         if (tid == 0) nxt = atomicAdd(counter, 1u);  // used at the end of this item
         const uint4 it = item_q[qk];
-        const uint2 rng = item_pk[(size_t)qk * TL_WARPS + w];
+        const uint2 rng = item_rng[(size_t)qk * nw + w];
         const uint32_t t0 = it.y, ntile = it.z, item = it.w;
-        const uint32_t P0 = rng.x, np = rng.y;
-        // descriptor window: lane l holds packet win0 + l (and win0 + 32 + l prefetched), one coalesced load per 32
-        // packets; nothing on the packet path waits for a dependent global load
-        uint32_t win0 = 0;
-        uint2 dwin = lane < np ? pk_d[P0 + lane] : make_uint2(0u, 0u);
-        uint2 dnxt = 32u + lane < np ? pk_d[P0 + 32u + lane] : make_uint2(0u, 0u);
+        const uint4* p = stream + (size_t)rng.x * 32 + lane;
+        const uint32_t n = rng.y - rng.x;
+        uint4 nx[PF];
+#pragma unroll
+        for (int j = 0; j < PF; ++j) nx[j] = (uint32_t)j < n ? ld_stream(p + (size_t)j * 32) : make_uint4(NOP_PAIR, NOP_PAIR, NOP_PAIR, NOP_PAIR);
         if (tid == 0) {
             for (uint32_t k = 0; k < 2 && k < ntile; ++k) {
                 const uint32_t g = g_tile + k;
-                mbar_expect_tx(&tab_full[g & 1], (uint32_t)TL_TAB_BYTES);
-                bulk_g2s(smem + (size_t)(g & 1) * TL_TAB_BUF, tab13 + (size_t)(t0 + k) * TILE_L * TAB13, (uint32_t)TL_TAB_BYTES,
-                         &tab_full[g & 1]);
+                mbar_expect_tx(&tab_full[g & 1], (uint32_t)TB_BYTES);
+                bulk_g2s(smem + (size_t)(g & 1) * TB_BUF, tab16 + (size_t)(t0 + k) * TILE_SLOTS * 2, (uint32_t)TB_BYTES, &tab_full[g & 1]);
             }
         }
-        // packet i of this warp goes to ring stage (cons_c at item start + i) % STAGES; issue runs STAGES ahead
-        const uint32_t c_base = cons_c;
-        auto issue = [&](uint32_t i) {
-            if (i >= np) return;
-            if (i >= win0 + 32u) {
-                win0 += 32u;
-                dwin = dnxt;
-                dnxt = win0 + 32u + lane < np ? pk_d[P0 + win0 + 32u + lane] : make_uint2(0u, 0u);
-            }
-            const uint32_t q0 = __shfl_sync(0xffffffffu, dwin.x, (int)(i - win0));
-            const uint32_t bytes = __shfl_sync(0xffffffffu, dwin.y, (int)(i - win0)) * 16u;
-            const uint32_t s = (c_base + i) % RING_STAGES;
-#ifdef CLX_TILED_DEBUG
-            if (lane == 0 && (bytes == 0 || bytes > STAGE_BYTES))
-                printf("bad packet: blk %d w %d item %u i %u q0 %u bytes %u\n", blockIdx.x, w, item, i, q0, bytes);
-#endif
-            if (lane == 0) {
-                mbar_expect_tx(&my_bar[s], bytes);
-                bulk_g2s(my_ring + (size_t)s * STAGE_BYTES, stream + (size_t)q0 * 4, bytes, &my_bar[s]);
-            }
-        };
-        for (uint32_t i = 0; i < (uint32_t)RING_STAGES; ++i) issue(i);
-        // hand a table buffer over: the last warp to leave tile k starts the copy of tile k + 2 into it.  No CTA
-        // barrier: cells never change warps, so accumulators need none, and warps drift by at most two tiles.
-        auto leave_tile = [&](uint32_t k) {
-            const uint32_t g = g_tile + k;
-            __syncwarp();
-            if (lane == 0) {
-                const unsigned int done = atomicAdd(&tab_done[g & 1], 1u);
-                if (done == TL_WARPS - 1) {
-                    tab_done[g & 1] = 0;
-                    if (k + 2 < ntile) {
-                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                        mbar_expect_tx(&tab_full[g & 1], (uint32_t)TL_TAB_BYTES);
-                        bulk_g2s(smem + (size_t)(g & 1) * TL_TAB_BUF, tab13 + (size_t)(t0 + k + 2) * TILE_L * TAB13,
-                                 (uint32_t)TL_TAB_BYTES, &tab_full[g & 1]);
+        int k = -1;                    // item-local tile this warp is in
+        const double2* tab = nullptr;  // its staged slots
+        double sT = 0.0, sE = 0.0;     // the lane's run
+        double2* cell_acc = my_acc;
+        bool has = false;
+        auto word = [&](uint32_t v) {
+            if (v & WD_HEADER) {
+                if (v & WD_NEWTILE) {
+                    tab = reinterpret_cast<const double2*>(smem + enter_tile(smem, k, g_tile, t0, ntile, nw, tab16));
+                    ++k;
+                }
+                if (!(v & WD_NOP)) {
+                    has = !(v & WD_IDLE);
+                    cell_acc = my_acc + (v & WD_QMASK);
+                    sT = 0.0;
+                    sE = 0.0;
+                }
+            } else {
+                const double2 te = tab[v & WD_SLOT];
+                sT += te.x;
+                sE += te.y;
+                if (v & WD_LAST) {
+                    if (has) {
+                        double2 a = *cell_acc;
+                        a.x += sT;
+                        a.y += sE;
+                        *cell_acc = a;
                     }
                 }
             }
         };
-        // every warp walks every tile of the item in order (waits for its table, leaves it), with or without packets
-        uint32_t k = 0;
-        mbar_wait(&tab_full[g_tile & 1], (g_tile >> 1) & 1u);
-        for (uint32_t i = 0; i < np; ++i) {
-            const uint32_t s = cons_c % RING_STAGES;
-            mbar_wait(&my_bar[s], (cons_c / RING_STAGES) & 1u);
-            const unsigned char* pk = my_ring + (size_t)s * STAGE_BYTES;
-            const uint32_t kt = reinterpret_cast<const uint32_t*>(pk)[1] - t0;  // tile of this packet, item-local
-#ifdef CLX_TILED_DEBUG
-            if (lane == 0 && (kt >= ntile || kt < k))
-                printf("bad tile: blk %d w %d item %u i %u kt %u k %u ntile %u\n", blockIdx.x, w, item, i, kt, k, ntile);
-#endif
-            while (k < kt) {
-                leave_tile(k);
-                ++k;
-                mbar_wait(&tab_full[(g_tile + k) & 1], ((g_tile + k) >> 1) & 1u);
+        for (uint32_t c = 0; c < n; c += PF) {
+            uint4 cur[PF];
+#pragma unroll
+            for (int j = 0; j < PF; ++j) cur[j] = nx[j];
+#pragma unroll
+            for (int j = 0; j < PF; ++j)
+                nx[j] = c + PF + j < n ? ld_stream(p + (size_t)(c + PF + j) * 32) : make_uint4(NOP_PAIR, NOP_PAIR, NOP_PAIR, NOP_PAIR);
+#pragma unroll
+            for (int j = 0; j < PF; ++j) {
+                // chunks past the end are no-op headers: no test needed
+                word(cur[j].x & 0xFFFFu);
+                word(cur[j].x >> 16);
+                word(cur[j].y & 0xFFFFu);
+                word(cur[j].y >> 16);
+                word(cur[j].z & 0xFFFFu);
+                word(cur[j].z >> 16);
+                word(cur[j].w & 0xFFFFu);
+                word(cur[j].w >> 16);
             }
-            const double* tab = reinterpret_cast<const double*>(smem + (size_t)((g_tile + k) & 1) * TL_TAB_BUF);
-            tiled_packet<WITH_E>(pk, tab, acc, lane, w, st, Q);
-            __syncwarp();
-            ++cons_c;
-            issue(i + RING_STAGES);  // refill the stage just drained
         }
-        for (;;) {
-            leave_tile(k);
-            if (++k >= ntile) break;
-            mbar_wait(&tab_full[(g_tile + k) & 1], ((g_tile + k) >> 1) & 1u);
+        // every warp walks every tile of the item (waits for its table, leaves it); the stream carries one NEWTILE
+        // header per tile, so the loop body only runs for an item without chunks
+        while (k + 1 < (int)ntile) {
+            enter_tile(smem, k, g_tile, t0, ntile, nw, tab16);
+            ++k;
         }
+        leave_tile(smem, (uint32_t)k, g_tile, t0, ntile, nw, tab16);
         g_tile += ntile;
-        if (tid == 0) s_next = nxt;
+        if (tid == 0) *s_next = nxt;
         __syncthreads();  // every warp has added its last run; the next queue slot is posted
-        // partials out, accumulators cleared for the next item in the same sweep
+        // partials out (cell_local = q * nw + warp lives in accumulator slot warp * Q + q), accumulators cleared
         double2* dst = reinterpret_cast<double2*>(part) + (size_t)item * NB;
-        for (uint32_t i = tid; i < 32u * Q; i += blockDim.x) {
-            const uint32_t slot = acc_slot(i, Q);
-            if (i < NB) dst[i] = acc[slot];
+        for (uint32_t i = tid; i < NB; i += blockDim.x) {
+            const uint32_t slot = (i % nw) * Q + i / nw;
+            dst[i] = acc[slot];
             acc[slot] = make_double2(0.0, 0.0);
         }
-        qk = s_next;
+        qk = *s_next;
         __syncthreads();
     }
 }
@@ -473,16 +459,19 @@ __global__ void __launch_bounds__(TL_WARPS * 32, 1)
 // Adds the partials of a cell's block in item order (FIN_LANES lanes per cell, each a fixed subsequence, combined
 // by a fixed shuffle tree: deterministic), appends the heavy values in row order, and (EM pass) normalises by
 // loci_used_per_cell (main.rs:313-323).
+//   SCORE_EM       out0 = log_likelihood, out1 = expected_log_likelihood, + n_loci, normalised value
+//   SCORE_POST_AB  out0 = minority, out1 = majority log likelihood (heavy values hv0 / hv1)
+//   SCORE_POST_C   out0 = doublet log likelihood
 constexpr int FIN_LANES = 8;
-template <bool EM>
+template <int MODE>
 __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__ part, const uint32_t* __restrict__ cb_item,
                                                       uint32_t NB, uint32_t n_cells, const uint32_t* __restrict__ h_row_ptr,
-                                                      const double* __restrict__ hv_ll, const double* __restrict__ hv_e,
-                                                      const uint32_t* __restrict__ n_used, double* __restrict__ ll,
-                                                      double* __restrict__ ell, uint32_t* __restrict__ nloci,
+                                                      const double* __restrict__ hv0, const double* __restrict__ hv1,
+                                                      const uint32_t* __restrict__ n_used, double* __restrict__ out0,
+                                                      double* __restrict__ out1, uint32_t* __restrict__ nloci,
                                                       double* __restrict__ norm, unsigned int* __restrict__ nan_flag,
                                                       uint32_t* __restrict__ queue_counter, uint32_t first_round) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) *queue_counter = first_round;  // re-arm the work queue of k_score_tiled
+    if (blockIdx.x == 0 && threadIdx.x == 0) *queue_counter = first_round;  // re-arm the work queue of k_score_runs
     // lanes 0..3 of a warp take cells c0..c0+3 for sub 0, lanes 4..7 the same cells for sub 1, ...: partial loads of one
     // sub are 4 consecutive double2 (64 B)
     const uint32_t warp_cell0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / FIN_LANES);
@@ -493,29 +482,29 @@ __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__
     const uint32_t cb = ii / NB, cl = ii % NB;
     const uint32_t it0 = cb_item[cb], it1 = cb_item[cb + 1];
     const double2* p2 = reinterpret_cast<const double2*>(part);
-    double sT = 0.0, sE = 0.0;
+    double s0 = 0.0, s1 = 0.0;
     for (uint32_t it = it0 + sub; it < it1; it += FIN_LANES) {
         const double2 p = __ldg(p2 + (size_t)it * NB + cl);
-        sT += p.x;
-        sE += p.y;
+        s0 += p.x;
+        s1 += p.y;
     }
 #pragma unroll
     for (int off = 32 / FIN_LANES; off < 32; off <<= 1) {
-        sT += __shfl_xor_sync(0xffffffffu, sT, off);
-        if (EM) sE += __shfl_xor_sync(0xffffffffu, sE, off);
+        s0 += __shfl_xor_sync(0xffffffffu, s0, off);
+        if (MODE != SCORE_POST_C) s1 += __shfl_xor_sync(0xffffffffu, s1, off);
     }
     if (!live || sub != 0) return;
     const uint32_t hb = h_row_ptr[i], he = h_row_ptr[i + 1];
     for (uint32_t h = hb; h < he; ++h) {
-        sT += hv_ll[h];
-        if (EM) sE += hv_e[h];
+        s0 += hv0[h];
+        if (MODE != SCORE_POST_C) s1 += hv1[h];
     }
-    ll[i] = sT;
-    if (EM) {
-        ell[i] = sE;
+    out0[i] = s0;
+    if (MODE != SCORE_POST_C) out1[i] = s1;
+    if (MODE == SCORE_EM) {
         const uint32_t cnt = n_used[i];
         nloci[i] = cnt;
-        const double nv = cnt > 0 ? sT / (double)cnt : 0.0;
+        const double nv = cnt > 0 ? s0 / (double)cnt : 0.0;
         norm[i] = nv;
         if (nv != nv) atomicOr(nan_flag, 1u);
     }
@@ -523,39 +512,37 @@ __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__
 
 }  // namespace
 
-// Scores every cell against memo table `table` (0 in the EM pass; 0..2 in the posterior pass).
-int score_tiled(clx_ctx* c, int table, bool with_e, bool em_outputs) {
+// One scoring pass over the run stream.  SCORE_EM reads table pass 0 ({T, E} slots); the posterior pass reads
+// {T_minority, T_majority} (pass 0 of tab16 as rebuilt by k_tables<1>) and {T_doublet, 0} (pass 1).
+int score_tiled(clx_ctx* c, ScoreMode mode) {
     cudaStream_t s = c->stream;
     const uint32_t N = c->n_cells;
     if (N == 0) return CLX_OK;
-    static bool attr_done = false;
-    if (!attr_done) {
-        CLX_CUDA(c, cudaFuncSetAttribute(k_score_tiled<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TL_SMEM));
-        CLX_CUDA(c, cudaFuncSetAttribute(k_score_tiled<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TL_SMEM));
-        attr_done = true;
+    if (!c->tl_attr_set) {  // per context: the attribute is per device
+        CLX_CUDA(c, cudaFuncSetAttribute(k_score_runs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TL_SMEM));
+        c->tl_attr_set = true;
     }
-    const double* tab = c->tab13.p + (size_t)table * c->tl_nT * TILE_L * TAB13;
+    const double* tab = c->tab16.p + (mode == SCORE_POST_C ? (size_t)c->tl_nT * TILE_SLOTS * 2 : 0);
     if (c->tl_n_items) {
-        const unsigned grid = c->tl_grid;
-        if (with_e)
-            k_score_tiled<true><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_d.p, c->tl_item_q.p, c->tl_item_pk.p,
-                                                                    c->tl_n_items, c->tl_counter.p, tab, c->tl_NB, c->tl_part.p);
-        else
-            k_score_tiled<false><<<grid, TL_WARPS * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_pk_d.p, c->tl_item_q.p, c->tl_item_pk.p,
-                                                                     c->tl_n_items, c->tl_counter.p, tab, c->tl_NB, c->tl_part.p);
+        k_score_runs<<<c->tl_grid, c->tl_W * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_item_q.p, c->tl_item_rng.p, c->tl_n_items,
+                                                              c->tl_counter.p, tab, c->tl_NB, c->tl_part.p);
         c->launches++;
-        CLX_DEBUG_SYNC(c, "k_score_tiled");
+        CLX_DEBUG_SYNC(c, "k_score_runs");
     }
-    const double* hv = c->hv_ll.p + (size_t)table * c->n_heavy;
+    const size_t nh = c->n_heavy;
     const unsigned fgrid = (unsigned)(((uint64_t)N * FIN_LANES + 255) / 256);
-    if (em_outputs)
-        k_score_finish<true><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, hv, c->hv_e.p,
-                                                  c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag,
-                                                  c->tl_counter.p, c->tl_grid);
+    if (mode == SCORE_EM)
+        k_score_finish<SCORE_EM><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p,
+                                                      c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag,
+                                                      c->tl_counter.p, c->tl_grid);
+    else if (mode == SCORE_POST_AB)
+        k_score_finish<SCORE_POST_AB><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p,
+                                                           c->hv_ll.p + nh, nullptr, c->post_ll.p, c->post_ll.p + N, nullptr, nullptr,
+                                                           nullptr, c->tl_counter.p, c->tl_grid);
     else
-        k_score_finish<false><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, hv, nullptr, nullptr,
-                                                   c->ll.p + (size_t)table * N, nullptr, nullptr, nullptr, nullptr, c->tl_counter.p,
-                                                   c->tl_grid);
+        k_score_finish<SCORE_POST_C><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p + 2 * nh,
+                                                          nullptr, nullptr, c->post_ll.p + 2 * (size_t)N, nullptr, nullptr, nullptr, nullptr,
+                                                          c->tl_counter.p, c->tl_grid);
     c->launches++;
     return CLX_OK;
 }
@@ -568,43 +555,39 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     CLX_CUDA(c, c->row_len.alloc((size_t)N + 1));
     CLX_CUDA(c, c->n_used.alloc((size_t)N + 1));
     CLX_CUDA(c, cudaMemsetAsync(c->row_len.p, 0, c->row_len.bytes(), s));
-    // cell blocks: few (every block re-reads the table tiles) but enough (cell block, tile) units to fill the SMs
+    // cell blocks: few and large (every block re-reads the table tiles, and a sub-unit should pool >= 256 runs so that
+    // the runs of a group have equal lengths) but enough (cell block, tile) units to fill the SMs
     c->tl_nT = L ? (L + TILE_L - 1) / TILE_L : 1;
     {
+        uint32_t W = W_MAX;
+        const char* env_w = getenv("CLX_TILED_W");
         uint32_t pc = N ? (N + NB_MAX - 1) / NB_MAX : 1;
-        // one work item per SM, each at least ~4 consecutive tiles long (table copies pipeline inside an item, and the
-        // cut points of an item are whole tiles: short items balance badly)
+        // two work items per SM, each at least ~2 consecutive tiles long
         const uint32_t want = (4u * (uint32_t)c->sm_count + c->tl_nT - 1) / c->tl_nT;
-        const uint32_t pc_cap = N ? std::max<uint32_t>(1u, N / NB_MIN) : 1u;
+        const uint32_t pc_cap = N ? std::max<uint32_t>(1u, N / 512u) : 1u;
         pc = std::max(pc, std::min(want, pc_cap));
         const char* env = getenv("CLX_TILED_PC");
         if (env && *env) pc = std::max<uint32_t>(pc, (uint32_t)atoi(env));
-        c->tl_Pc = pc;
         uint32_t nb = N ? (N + pc - 1) / pc : 1;
-        // whole groups: 32 warps x 32 lanes = 1024 cells give every (tile, warp) exactly 32 runs; a ragged tail of a few
-        // runs per warp costs a whole padded group per tile
-        const uint32_t nb_even = (nb + 31) / 32 * 32;
-        if (nb >= 1024) {
-            const uint32_t nb_whole = std::min<uint32_t>(NB_MAX, nb / 1024 * 1024);
-            const uint32_t tail = N % nb_whole;  // cells of the ragged last block
-            nb = (tail == 0 || 2 * tail >= nb_whole) ? nb_whole : nb_even;
-        } else {
-            nb = nb_even;
-        }
-        const char* env_nb = getenv("CLX_TILED_NB");  // experiments: force the cell-block size (tools/tiled_model.py)
-        if (env_nb && *env_nb) nb = std::min<uint32_t>(NB_MAX, std::max<uint32_t>(32u, ((uint32_t)atoi(env_nb) + 31u) / 32u * 32u));
+        const char* env_nb = getenv("CLX_TILED_NB");  // experiments: force the cell-block size
+        if (env_nb && *env_nb) nb = (uint32_t)atoi(env_nb);
+        if (nb < 2048) W = 8;  // small blocks: fewer warps keep the per-warp run pool (and the groups) large
+        if (env_w && *env_w) W = std::min<uint32_t>(W_MAX, std::max<uint32_t>(1u, (uint32_t)atoi(env_w)));
+        const uint32_t gran = 8u * W;  // Q = NB / W is a multiple of 8: accumulator bank groups follow q mod 8
+        nb = std::min<uint32_t>(NB_MAX, std::max<uint32_t>(gran, (nb + gran - 1) / gran * gran));
+        c->tl_W = W;
         c->tl_NB = nb;
-        c->tl_Pc = N ? (N + c->tl_NB - 1) / c->tl_NB : 1;
+        c->tl_Pc = N ? (N + nb - 1) / nb : 1;
     }
+    const uint32_t W = c->tl_W;
     c->tl_n_units = c->tl_Pc * c->tl_nT;
     if ((uint64_t)c->tl_Pc * c->tl_nT >= (1ull << 31)) return fail(c, CLX_ERR_ARG, "too many (cell block, tile) units");
     const uint32_t n_units = c->tl_n_units;
 
-    DevBuf<unsigned long long> keys, keys_sorted, d_nlight, ukeys, key2, key2_sorted, run_start, unit_entries;
+    DevBuf<unsigned long long> keys, keys_sorted, d_nlight, ukeys, key2, key2_sorted, run_start, unit_cost, d_steps;
     DevBuf<uint16_t> vals, vals_sorted;
     DevBuf<int> counts, d_nruns;
-    DevBuf<uint32_t> ridx, ridx_sorted, n_pk;
-    DevBuf<unsigned int> too_long;
+    DevBuf<uint32_t> ridx, ridx_sorted;
     DevBuf<uint8_t> tmp;
     size_t tb = 0;
     CLX_CUDA(c, keys.alloc(nnz + 1));
@@ -613,10 +596,10 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     CLX_CUDA(c, vals_sorted.alloc(nnz + 1));
     CLX_CUDA(c, d_nlight.alloc(1));
     CLX_CUDA(c, d_nruns.alloc(1));
-    CLX_CUDA(c, too_long.alloc(1));
+    CLX_CUDA(c, d_steps.alloc(1));
     CLX_CUDA(c, cudaMemsetAsync(d_nlight.p, 0, 8, s));
     CLX_CUDA(c, cudaMemsetAsync(d_nruns.p, 0, 4, s));
-    CLX_CUDA(c, cudaMemsetAsync(too_long.p, 0, 4, s));
+    CLX_CUDA(c, cudaMemsetAsync(d_steps.p, 0, 8, s));
     unsigned long long n_light = 0;
     if (nnz) {
         k_tile_keys<<<grid_for(nnz), TPB, 0, s>>>(c->csr.p, d_cell_of_entry, nnz, c->tl_NB, c->tl_nT, keys.p, vals.p, d_nlight.p,
@@ -648,26 +631,24 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     }
     keys_sorted.release();
     const uint32_t R = (uint32_t)n_runs;
-    const uint64_t n_sub = (uint64_t)n_units * TL_WARPS;
-    if (n_sub >= (1ull << 32) - 2) return fail(c, CLX_ERR_ARG, "too many (cell block, tile, warp) sub-units");
-    DevBuf<uint32_t> sub_run, n_quads, q_base;
+    const uint64_t n_sub = (uint64_t)n_units * W;
+    if (n_sub >= (1ull << 31) - 2) return fail(c, CLX_ERR_ARG, "too many (cell block, tile, warp) sub-units");
+    DevBuf<uint32_t> sub_run, n_chunks, chunk_off;
     CLX_CUDA(c, run_start.alloc((size_t)R + 1));
     CLX_CUDA(c, key2.alloc((size_t)R + 1));
     CLX_CUDA(c, key2_sorted.alloc((size_t)R + 1));
     CLX_CUDA(c, ridx.alloc((size_t)R + 1));
     CLX_CUDA(c, ridx_sorted.alloc((size_t)R + 1));
     CLX_CUDA(c, sub_run.alloc(n_sub + 2));
-    CLX_CUDA(c, n_pk.alloc(n_sub + 2));
-    CLX_CUDA(c, n_quads.alloc(n_sub + 2));
-    CLX_CUDA(c, q_base.alloc(n_sub + 2));
-    CLX_CUDA(c, unit_entries.alloc((size_t)n_units + 2));
-    CLX_CUDA(c, c->tl_pk_base.alloc(n_sub + 2));
+    CLX_CUDA(c, n_chunks.alloc(n_sub + 2));
+    CLX_CUDA(c, chunk_off.alloc(n_sub + 2));
+    CLX_CUDA(c, unit_cost.alloc((size_t)n_units + 2));
     if (R) {
         cub::TransformInputIterator<unsigned long long, IntToU64, const int*> cnt64(counts.p, IntToU64());
         CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt64, run_start.p, (int)R, s));
         CLX_CUDA(c, tmp.alloc(tb));
         CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, cnt64, run_start.p, (int)R, s));
-        k_run_keys<<<(R + TPB - 1) / TPB, TPB, 0, s>>>(ukeys.p, counts.p, R, c->tl_nT, key2.p, ridx.p, too_long.p);
+        k_run_keys<<<(R + TPB - 1) / TPB, TPB, 0, s>>>(ukeys.p, counts.p, R, c->tl_nT, W, key2.p, ridx.p);
         int bits2 = 17;
         while (bits2 < 63 && (1ull << bits2) <= (n_sub << 16)) ++bits2;
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tb, key2.p, key2_sorted.p, ridx.p, ridx_sorted.p, (int)R, 0, bits2, s));
@@ -676,47 +657,46 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         c->launches += 7;
     }
     k_sub_runs<<<(unsigned)((n_sub + 1 + TPB - 1) / TPB), TPB, 0, s>>>(key2_sorted.p, R, n_sub, sub_run.p);
-    k_sub_count<<<(unsigned)((n_sub + 1 + TPB - 1) / TPB), TPB, 0, s>>>(sub_run.p, ridx_sorted.p, counts.p, n_sub, n_pk.p, n_quads.p);
-    k_unit_cost<<<(n_units + TPB - 1) / TPB, TPB, 0, s>>>(n_quads.p, n_units, c->tl_nT, unit_entries.p);
-    CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tb, n_pk.p, c->tl_pk_base.p, (int)(n_sub + 1), s));
+    k_sub_count<<<(unsigned)(((n_sub + 1) * 32 + TPB - 1) / TPB), TPB, 0, s>>>(sub_run.p, ridx_sorted.p, counts.p, n_sub, n_chunks.p,
+                                                                               d_steps.p);
+    k_unit_cost<<<(n_units + TPB - 1) / TPB, TPB, 0, s>>>(n_chunks.p, n_units, c->tl_nT, W, unit_cost.p);
+    CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tb, n_chunks.p, chunk_off.p, (int)(n_sub + 1), s));
     CLX_CUDA(c, tmp.alloc(tb));
-    CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, n_pk.p, c->tl_pk_base.p, (int)(n_sub + 1), s));
-    CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tb, n_quads.p, q_base.p, (int)(n_sub + 1), s));
-    CLX_CUDA(c, tmp.alloc(tb));
-    CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, n_quads.p, q_base.p, (int)(n_sub + 1), s));
-    c->launches += 7;
-    uint32_t n_packets = 0, total_q = 0;
-    unsigned int h_too_long = 0;
+    CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, n_chunks.p, chunk_off.p, (int)(n_sub + 1), s));
+    c->launches += 5;
+    uint32_t total_chunks = 0;
+    unsigned long long h_steps = 0;
     std::vector<unsigned long long> h_unit((size_t)n_units + 1);
-    CLX_CUDA(c, cudaMemcpyAsync(&n_packets, c->tl_pk_base.p + n_sub, 4, cudaMemcpyDeviceToHost, s));
-    CLX_CUDA(c, cudaMemcpyAsync(&total_q, q_base.p + n_sub, 4, cudaMemcpyDeviceToHost, s));
-    CLX_CUDA(c, cudaMemcpyAsync(&h_too_long, too_long.p, 4, cudaMemcpyDeviceToHost, s));
-    CLX_CUDA(c, cudaMemcpyAsync(h_unit.data(), unit_entries.p, (size_t)n_units * 8, cudaMemcpyDeviceToHost, s));
+    CLX_CUDA(c, cudaMemcpyAsync(&total_chunks, chunk_off.p + n_sub, 4, cudaMemcpyDeviceToHost, s));
+    CLX_CUDA(c, cudaMemcpyAsync(&h_steps, d_steps.p, 8, cudaMemcpyDeviceToHost, s));
+    CLX_CUDA(c, cudaMemcpyAsync(h_unit.data(), unit_cost.p, (size_t)n_units * 8, cudaMemcpyDeviceToHost, s));
     CLX_CUDA(c, cudaStreamSynchronize(s));
-    if (h_too_long) {
-        // more than 65535 entries of one cell inside one locus tile (massively duplicated coordinates): the batch
-        // format does not hold such a run; the gather kernel scores this matrix instead
-        CLX_CUDA(c, c->tab13.alloc(TAB13));
-        return CLX_OK;
+    {
+        unsigned long long sum = 0;
+        for (uint32_t u = 0; u < n_units; ++u) sum += h_unit[u];
+        if (sum >= (1ull << 32)) return fail(c, CLX_ERR_ARG, "run stream longer than 2^32 chunks (2 TB): shard the cells over more ranks");
     }
-    c->tl_stream_len = (uint64_t)total_q * 4;  // in 4-byte words
-    CLX_CUDA(c, c->tl_stream.alloc(c->tl_stream_len + 4));
-    CLX_CUDA(c, c->tl_pk_d.alloc((size_t)n_packets + 2));
-    if (n_packets) {
-        k_sub_fill<<<(unsigned)((n_sub * 32 + TPB - 1) / TPB), TPB, 0, s>>>(sub_run.p, c->tl_pk_base.p, q_base.p, ridx_sorted.p, ukeys.p,
-                                                                          counts.p, run_start.p, vals_sorted.p, n_sub, c->tl_nT,
-                                                                          c->tl_pk_d.p, c->tl_stream.p);
+    c->tl_stream_chunks = total_chunks;
+    c->tl_stream_steps = h_steps * 32ull;
+    if (getenv("CLX_TILED_STATS"))
+        fprintf(stderr, "[clx] run stream: N %u L %u NB %u W %u Pc %u nT %u | light entries %llu runs %u | chunks %u (%.2f B/entry) lookup steps %llu (%.3f per entry)\n",
+                N, L, c->tl_NB, W, c->tl_Pc, c->tl_nT, (unsigned long long)n_light, R, total_chunks,
+                n_light ? 512.0 * total_chunks / (double)n_light : 0.0, (unsigned long long)c->tl_stream_steps,
+                n_light ? (double)c->tl_stream_steps / (double)n_light : 0.0);
+    CLX_CUDA(c, c->tl_stream.alloc((size_t)total_chunks * 32 + 32));
+    if (total_chunks) {
+        k_sub_fill<<<(unsigned)((n_sub * 32 + TPB - 1) / TPB), TPB, 0, s>>>(sub_run.p, chunk_off.p, ridx_sorted.p, ukeys.p, counts.p,
+                                                                          run_start.p, vals_sorted.p, n_sub, W, c->tl_stream.p);
         c->launches++;
     }
-    CLX_CUDA(c, cudaStreamSynchronize(s));
 
     const char* env_it = getenv("CLX_TILED_ITEMS_PER_SM");
     const int env_items = env_it && *env_it ? std::max(1, atoi(env_it)) : 2;
-    // ---- work items: every cell block gets a share of (items per SM x SMs) items proportional to its entries; its tiles are cut
-    //      into that many consecutive ranges of about equal entry counts
+    // ---- work items: every cell block gets a share of (items per SM x SMs) items proportional to its chunks; its tiles are cut
+    //      into that many consecutive ranges of about equal chunk counts
     {
         std::vector<uint32_t> items, cb_item;
-        std::vector<unsigned long long> item_entries;
+        std::vector<unsigned long long> item_cost;
         unsigned long long cost_total = 0;
         for (uint32_t u = 0; u < n_units; ++u) cost_total += h_unit[u];
         const uint64_t total_items = std::max<uint64_t>(1, (uint64_t)env_items * (uint64_t)c->sm_count);
@@ -744,7 +724,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
                     items.push_back(t0);
                     items.push_back(t1);
                     items.push_back(0);
-                    item_entries.push_back(in_range);
+                    item_cost.push_back(in_range);
                 }
                 t0 = t1;
             }
@@ -753,11 +733,11 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         c->tl_n_items = (uint32_t)(items.size() / 4);
         c->tl_grid = std::min<uint32_t>(c->tl_n_items, (uint32_t)c->sm_count);
         CLX_CUDA(c, c->tl_item_q.alloc((size_t)c->tl_n_items + 1));
-        CLX_CUDA(c, c->tl_item_pk.alloc((size_t)c->tl_n_items * TL_WARPS + 1));
+        CLX_CUDA(c, c->tl_item_rng.alloc((size_t)c->tl_n_items * W + 1));
         CLX_CUDA(c, c->tl_cb_item.alloc(cb_item.size()));
         std::vector<uint32_t> order(c->tl_n_items);
         for (uint32_t i = 0; i < c->tl_n_items; ++i) order[i] = i;
-        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_entries[a] > item_entries[b]; });
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_cost[a] > item_cost[b]; });
         std::vector<uint4> queue(c->tl_n_items);  // largest first
         for (uint32_t q = 0; q < c->tl_n_items; ++q) {
             const uint32_t i = order[q];
@@ -767,16 +747,15 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         CLX_CUDA(c, cudaMemcpyAsync(c->tl_counter.p, &c->tl_grid, 4, cudaMemcpyHostToDevice, s));
         if (!queue.empty()) {
             CLX_CUDA(c, cudaMemcpyAsync(c->tl_item_q.p, queue.data(), queue.size() * sizeof(uint4), cudaMemcpyHostToDevice, s));
-            k_item_pk<<<c->tl_n_items, TL_WARPS, 0, s>>>(c->tl_item_q.p, c->tl_n_items, c->tl_pk_base.p, c->tl_nT, c->tl_item_pk.p);
+            k_item_rng<<<c->tl_n_items, W, 0, s>>>(c->tl_item_q.p, c->tl_n_items, chunk_off.p, c->tl_nT, W, c->tl_item_rng.p);
             c->launches++;
         }
         CLX_CUDA(c, cudaMemcpyAsync(c->tl_cb_item.p, cb_item.data(), cb_item.size() * 4, cudaMemcpyHostToDevice, s));
-        CLX_CUDA(c, cudaStreamSynchronize(s));
+        CLX_CUDA(c, cudaStreamSynchronize(s));  // the host vectors above go out of scope
     }
     CLX_CUDA(c, c->tl_part.alloc((size_t)c->tl_n_items * c->tl_NB * 2 + 2));
-    CLX_CUDA(c, c->tab13.alloc(3ull * c->tl_nT * TILE_L * TAB13 + TAB13));
-    CLX_CUDA(c, cudaMemsetAsync(c->tab13.p, 0, c->tab13.bytes(), s));
-    CLX_CUDA(c, cudaStreamSynchronize(s));
+    CLX_CUDA(c, c->tab16.alloc(2ull * c->tl_nT * TILE_SLOTS * 2 + 2));
+    CLX_CUDA(c, cudaMemsetAsync(c->tab16.p, 0, c->tab16.bytes(), s));
     CLX_CUDA(c, cudaGetLastError());
     c->tiled_ready = true;
     return CLX_OK;
