@@ -54,6 +54,7 @@ constexpr uint32_t WD_NOP = 0x2000u;      // header: no group follows (empty sub
 constexpr uint32_t WD_IDLE = 0x1000u;     // header: this lane has no run in the group
 constexpr uint32_t WD_QMASK = 0x01FFu;    // header: index of the lane's cell among the warp's cells
 constexpr uint32_t WD_LAST = 0x4000u;     // entry word: last step of the group
+constexpr uint32_t WD_PAD = 0x2000u;      // entry word: padding (the lane has no entry in this step): no lookup
 constexpr uint32_t WD_SLOT = 0x1FFFu;     // entry word: slot inside the staged tile
 constexpr uint32_t NULL_SLOT = (uint32_t)TILE_SLOTS;
 static_assert(TILE_SLOTS < 0x1FFF, "slot index fits 13 bits");
@@ -65,8 +66,9 @@ inline unsigned grid_for(uint64_t n, int tpb = TPB, unsigned cap = 148u * 16u) {
 }
 
 // ---------------------------------------------------------------------------------------------- builder
-// key = (cell block * nT + tile) << 12 | cell_local   (sorts to unit, then cell; stable: file order inside a run);
-// non-light entries get ~0 and sort to the end
+// key = ((cell block * nT + tile) << 12 | cell_local) << 3 | bank group of the slot   (sorts to unit, then cell, then
+// bank group: the entries of a run come out grouped by the 16-byte bank group their lookup hits, which is what the
+// conflict-aware step order of k_sub_fill needs); non-light entries get ~0 and sort to the end
 __global__ void k_tile_keys(const RowEntry* __restrict__ csr, const uint32_t* __restrict__ cell_of, uint64_t nnz,
                             uint32_t NB, uint32_t nT, unsigned long long* __restrict__ keys, uint16_t* __restrict__ vals,
                             unsigned long long* __restrict__ n_light, uint32_t* __restrict__ row_len) {
@@ -80,8 +82,8 @@ __global__ void k_tile_keys(const RowEntry* __restrict__ csr, const uint32_t* __
         uint16_t v = 0;
         if (n >= 1 && n <= (uint32_t)K_LIGHT) {
             const uint32_t cb = c / NB, cl = c % NB, t = e.locus / TILE_L, ll = e.locus % TILE_L;
-            k = (((unsigned long long)cb * nT + t) << 12) | cl;
             v = (uint16_t)(ll * (uint32_t)TAB_SLOTS + (uint32_t)tab_slot((int)e.alt, (int)n));
+            k = (((((unsigned long long)cb * nT + t) << 12) | cl) << 3) | (unsigned long long)(v & 7u);
             ++mine;
         }
         keys[i] = k;
@@ -91,6 +93,9 @@ __global__ void k_tile_keys(const RowEntry* __restrict__ csr, const uint32_t* __
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(n_light, mine);
 }
 
+struct DropBank {  // run key of an entry key
+    __device__ unsigned long long operator()(unsigned long long k) const { return k >> 3; }
+};
 struct IntToU64 {
     __device__ unsigned long long operator()(int v) const { return (unsigned long long)v; }
 };
@@ -112,22 +117,25 @@ __device__ __forceinline__ unsigned long long sub_unit_of(unsigned long long uni
     const unsigned long long cb = unit / nT, t = unit % nT;
     return (cb * W + w) * nT + t;
 }
-// runs (unique keys + counts, from cub::DeviceRunLengthEncode) -> sort key (sub-unit << 16 | 0xFFFF - min(count, 0xFFFF)):
-// longest first inside a sub-unit.  The order only decides how much padding a group carries, never the result.
+// runs (unique keys + counts, from cub::DeviceRunLengthEncode) -> sort key ((sub-unit * 8 + class) << 16 | 0xFFFF -
+// min(count, 0xFFFF)), class = q mod 8 = the 16-byte bank group of the run's accumulator slot: longest first inside a
+// (sub-unit, class).  The order only decides how much padding a group carries, never the result.
 __global__ void k_run_keys(const unsigned long long* __restrict__ ukeys, const int* __restrict__ counts, uint32_t n_runs,
                            uint32_t nT, uint32_t W, unsigned long long* __restrict__ key2, uint32_t* __restrict__ idx) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_runs) return;
     const uint32_t cnt = (uint32_t)counts[r];
-    const unsigned long long unit = ukeys[r] >> 12, cl = ukeys[r] & 0xFFFull;
-    key2[r] = (sub_unit_of(unit, (uint32_t)(cl % W), nT, W) << 16) | (unsigned long long)(0xFFFFu - (cnt > 0xFFFFu ? 0xFFFFu : cnt));
+    const unsigned long long unit = ukeys[r] >> 12;
+    const uint32_t cl = (uint32_t)(ukeys[r] & 0xFFFull);
+    const unsigned long long sc = sub_unit_of(unit, cl % W, nT, W) * 8ull + ((cl / W) & 7u);
+    key2[r] = (sc << 16) | (unsigned long long)(0xFFFFu - (cnt > 0xFFFFu ? 0xFFFFu : cnt));
     idx[r] = r;
 }
-// first sorted run of every sub-unit, su in [0, n_sub]
-__global__ void k_sub_runs(const unsigned long long* __restrict__ key2_sorted, uint32_t n_runs, uint64_t n_sub,
+// first sorted run of every (sub-unit, class), i in [0, 8 * n_sub]
+__global__ void k_sub_runs(const unsigned long long* __restrict__ key2_sorted, uint32_t n_runs, uint64_t n_sc,
                            uint32_t* __restrict__ sub_run) {
-    const uint64_t su = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-    if (su <= n_sub) sub_run[su] = (uint32_t)lower_bound_dev<unsigned long long>(key2_sorted, 0, n_runs, su << 16);
+    const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (i <= n_sc) sub_run[i] = (uint32_t)lower_bound_dev<unsigned long long>(key2_sorted, 0, n_runs, i << 16);
 }
 
 __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) {
@@ -135,6 +143,25 @@ __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) {
     for (int off = 16; off > 0; off >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, off));
     return v;
 }
+
+// GROUPS of a sub-unit.  Lane l of a group sums a run of class v = l & 7 (accumulator slots of class v live in 16-byte
+// bank group v): group g gives lane l = 8 j + v the (4 g + j)-th longest run of class v, so the 8 lanes of every quarter
+// warp hold accumulator slots in 8 distinct bank groups and the group's accumulator update is conflict-free.  Classes
+// are iid samples of the cells, so the runs of a group still have nearly equal lengths.
+struct GroupWalk {
+    uint32_t b, e;  // this lane's class: sorted runs [b, e)
+    uint32_t G;     // groups of the sub-unit
+    __device__ __forceinline__ GroupWalk(const uint32_t* __restrict__ sub_run, uint64_t su, uint32_t lane) {
+        b = sub_run[su * 8 + (lane & 7u)];
+        e = sub_run[su * 8 + (lane & 7u) + 1];
+        G = warp_max_u32((e - b + 3u) / 4u);
+    }
+    // index into the sorted run list of this lane's run in group g, or 0xFFFFFFFF
+    __device__ __forceinline__ uint32_t run_of(uint32_t g, uint32_t lane) const {
+        const uint32_t r = b + 4u * g + (lane >> 3);
+        return r < e ? r : 0xFFFFFFFFu;
+    }
+};
 
 // one warp per sub-unit: words per lane = sum over groups of (1 header + longest run), at least the one header an
 // empty sub-unit needs; rounded up to whole chunks.  steps = lookup steps (padding included) of the sub-unit.
@@ -148,10 +175,11 @@ __global__ void k_sub_count(const uint32_t* __restrict__ sub_run, const uint32_t
         if (lane == 0) n_chunks[su] = 0;
         return;
     }
-    const uint32_t r0 = sub_run[su], r1 = sub_run[su + 1];
+    const GroupWalk gw(sub_run, su, lane);
     uint64_t words = 0, steps = 0;
-    for (uint32_t g0 = r0; g0 < r1; g0 += 32) {
-        const uint32_t M = warp_max_u32(g0 + lane < r1 ? (uint32_t)counts[idx_sorted[g0 + lane]] : 0u);
+    for (uint32_t g = 0; g < gw.G; ++g) {
+        const uint32_t r = gw.run_of(g, lane);
+        const uint32_t M = warp_max_u32(r != 0xFFFFFFFFu ? (uint32_t)counts[idx_sorted[r]] : 0u);
         words += 1u + M;
         steps += M;
     }
@@ -188,27 +216,36 @@ struct WordSink {
     }
 };
 
+// STEP ORDER inside a group.  The entries of a run may be summed in any order, and a lookup costs one shared-memory
+// wavefront per distinct address in the most loaded 16-byte bank group of its quarter warp: random order averages 2.4
+// wavefronts per quarter-warp step.  The builder therefore picks, step by step and quarter by quarter, which of its
+// remaining entries each lane takes: lanes that must take one now (entries left >= steps left) go first and take the
+// entry whose bank group is least used in this step; the others take an entry only if its bank group is still free,
+// else they sit the step out with a padding word (no lookup is issued for it).  ~1.6 wavefronts per step on
+// 5-entry runs.  The run's entries arrive sorted by bank group (k_tile_keys), so "an entry of bank group b" is a
+// cursor per bank group; cursors live in shared memory ([bank][lane]: conflict-free).
 __global__ void __launch_bounds__(TPB) k_sub_fill(const uint32_t* __restrict__ sub_run, const uint32_t* __restrict__ chunk_off,
                                                   const uint32_t* __restrict__ idx_sorted, const unsigned long long* __restrict__ ukeys,
                                                   const int* __restrict__ counts, const unsigned long long* __restrict__ run_start,
                                                   const uint16_t* __restrict__ vals_sorted, uint64_t n_sub, uint32_t W,
                                                   uint4* __restrict__ stream) {
-    __shared__ uint32_t s_cnt[TPB / 32][32], s_q[TPB / 32][32];
-    __shared__ unsigned long long s_src[TPB / 32][32];
+    __shared__ uint32_t s_left[TPB / 32][8][32];  // entries of bank group b this lane has not placed yet
+    __shared__ uint32_t s_cur[TPB / 32][8][32];   // offset inside the run of the next one
     const uint64_t su = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     if (su >= n_sub) return;
-    const uint32_t r0 = sub_run[su], r1 = sub_run[su + 1];
+    const GroupWalk gw(sub_run, su, lane);
     WordSink sink;
     sink.dst = stream + (size_t)chunk_off[su] * 32 + lane;
     sink.lo = sink.hi = 0;
     sink.pos = 0;
-    if (r0 == r1) sink.put(WD_HEADER | WD_NEWTILE | WD_NOP);
-    for (uint32_t g0 = r0; g0 < r1; g0 += 32) {
-        const uint32_t r = g0 + lane;
+    if (gw.G == 0) sink.put(WD_HEADER | WD_NEWTILE | WD_NOP);
+    const int qbase = (int)(lane & ~7u);
+    for (uint32_t g = 0; g < gw.G; ++g) {
+        const uint32_t r = gw.run_of(g, lane);
+        const bool has = r != 0xFFFFFFFFu;
         uint32_t cnt = 0, q = 0;
         unsigned long long src = 0;
-        bool has = r < r1;
         if (has) {
             const uint32_t rid = idx_sorted[r];
             cnt = (uint32_t)counts[rid];
@@ -216,34 +253,62 @@ __global__ void __launch_bounds__(TPB) k_sub_fill(const uint32_t* __restrict__ s
             q = (uint32_t)(ukeys[rid] & 0xFFFull) / W;  // accumulator slot of the cell = warp * Q + q, Q a multiple of 8
         }
         const uint32_t M = warp_max_u32(cnt);
-        // deal the runs to lanes so that a quarter warp's accumulator slots fall in distinct 16-byte bank groups: rank
-        // the runs by (q mod 8, lane) and give rank k to lane (k mod 4) * 8 + k / 4; idle lanes keep what is left
-        {
-            const uint32_t res = q & 7u;
-            uint32_t rank = 0;
+        sink.put(WD_HEADER | (g == 0 ? WD_NEWTILE : 0u) | (has ? (q & WD_QMASK) : WD_IDLE));
+        // per bank group: how many entries, where they start (the run is sorted by bank group)
+        uint32_t avail = 0;  // bit b: entries of bank group b left
 #pragma unroll
-            for (uint32_t v = 0; v < 8; ++v) {
-                const uint32_t m = __ballot_sync(0xffffffffu, has && res == v);
-                if (has && v < res) rank += __popc(m);
-                if (has && v == res) rank += __popc(m & ((1u << lane) - 1u));
+        for (int b = 0; b < 8; ++b) s_left[wib][b][lane] = 0;
+        for (uint32_t j = 0; j < cnt; ++j) s_left[wib][vals_sorted[src + j] & 7u][lane] += 1;
+        {
+            uint32_t off = 0;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+                const uint32_t n = s_left[wib][b][lane];
+                s_cur[wib][b][lane] = off;
+                off += n;
+                if (n) avail |= 1u << b;
             }
-            const uint32_t m_has = __ballot_sync(0xffffffffu, has);
-            if (!has) rank = __popc(m_has) + __popc(~m_has & ((1u << lane) - 1u));
-            const uint32_t tgt = (rank & 3u) * 8u + (rank >> 2);
-            s_cnt[wib][tgt] = has ? cnt : 0u;
-            s_q[wib][tgt] = has ? q : 0xFFFFFFFFu;
-            s_src[wib][tgt] = src;
-            __syncwarp();
-            cnt = s_cnt[wib][lane];
-            q = s_q[wib][lane];
-            src = s_src[wib][lane];
-            has = q != 0xFFFFFFFFu;
-            __syncwarp();
         }
-        sink.put(WD_HEADER | (g0 == r0 ? WD_NEWTILE : 0u) | (has ? (q & WD_QMASK) : WD_IDLE));
-        for (uint32_t j = 0; j < M; ++j) {
-            const uint32_t slot = j < cnt ? (uint32_t)vals_sorted[src + j] : NULL_SLOT;
-            sink.put(slot | (j + 1 == M ? WD_LAST : 0u));
+        uint32_t rem = cnt;
+        for (uint32_t st = 0; st < M; ++st) {
+            const uint32_t left = M - st;
+            const bool must = rem >= left;  // rem <= left always; rem > 0 here because left > 0
+            uint32_t used = 0;              // 8 x 4-bit use counts of this quarter's bank groups in this step
+            int pick = -1;
+            // round 1: the lanes that must place an entry now, in lane order; round 2: the others, free bank groups only
+#pragma unroll 1
+            for (int round = 0; round < 2; ++round) {
+#pragma unroll 1
+                for (int i = 0; i < 8; ++i) {
+                    int mine = -1;
+                    if ((int)(lane & 7u) == i && rem > 0 && pick < 0 && (round == 0 ? must : !must)) {
+                        uint32_t best_use = 16;
+#pragma unroll
+                        for (int b = 0; b < 8; ++b) {
+                            const uint32_t u = (used >> (4 * b)) & 15u;
+                            if (((avail >> b) & 1u) && u < best_use) {
+                                best_use = u;
+                                mine = b;
+                            }
+                        }
+                        if (round == 1 && best_use != 0) mine = -1;
+                        pick = mine;
+                    }
+                    const int pb = __shfl_sync(0xffffffffu, mine, qbase + i);
+                    if (pb >= 0) used += 1u << (4 * pb);
+                }
+            }
+            uint32_t w16 = WD_PAD | NULL_SLOT;
+            if (pick >= 0) {
+                const uint32_t at = s_cur[wib][pick][lane];
+                w16 = (uint32_t)vals_sorted[src + at];
+                s_cur[wib][pick][lane] = at + 1;
+                const uint32_t l2 = s_left[wib][pick][lane] - 1;
+                s_left[wib][pick][lane] = l2;
+                if (l2 == 0) avail &= ~(1u << pick);
+                --rem;
+            }
+            sink.put(w16 | (st + 1 == M ? WD_LAST : 0u));
         }
     }
     while (sink.pos != 0) sink.put(WD_HEADER | WD_NOP);
@@ -388,24 +453,37 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
         double sT = 0.0, sE = 0.0;     // the lane's run
         double2* cell_acc = my_acc;
         bool has = false;
-        auto word = [&](uint32_t v) {
-            if (v & WD_HEADER) {
-                if (v & WD_NEWTILE) {
-                    tab = reinterpret_cast<const double2*>(smem + enter_tile(smem, k, g_tile, t0, ntile, nw, tab16));
-                    ++k;
-                }
-                if (!(v & WD_NOP)) {
-                    has = !(v & WD_IDLE);
-                    cell_acc = my_acc + (v & WD_QMASK);
-                    sT = 0.0;
-                    sE = 0.0;
-                }
-            } else {
-                const double2 te = tab[v & WD_SLOT];
-                sT += te.x;
-                sE += te.y;
-                if (v & WD_LAST) {
-                    if (has) {
+        // One chunk = 8 words per lane.  A sub-unit starts on a chunk boundary, so only word 0 can announce the next
+        // tile; after that all 8 lookups of the chunk go out back to back (predicated off for header words: eight
+        // independent LDS.128 in flight per warp keep the shared-memory pipe full), then the words are consumed in
+        // order: a header opens a group, the last entry of a group adds the lane's run to its cell's accumulator.
+        auto chunk = [&](const uint4 cw) {
+            uint32_t wd[CHUNK_WORDS] = {cw.x & 0xFFFFu, cw.x >> 16, cw.y & 0xFFFFu, cw.y >> 16,
+                                        cw.z & 0xFFFFu, cw.z >> 16, cw.w & 0xFFFFu, cw.w >> 16};
+            if ((wd[0] & (WD_HEADER | WD_NEWTILE)) == (WD_HEADER | WD_NEWTILE)) {
+                tab = reinterpret_cast<const double2*>(smem + enter_tile(smem, k, g_tile, t0, ntile, nw, tab16));
+                ++k;
+            }
+            double2 te[CHUNK_WORDS];
+#pragma unroll
+            for (int i = 0; i < (int)CHUNK_WORDS; ++i)
+                if (!(wd[i] & (WD_HEADER | WD_PAD))) te[i] = tab[wd[i] & WD_SLOT];
+#pragma unroll
+            for (int i = 0; i < (int)CHUNK_WORDS; ++i) {
+                const uint32_t v = wd[i];
+                if (v & WD_HEADER) {
+                    if (!(v & WD_NOP)) {
+                        has = !(v & WD_IDLE);
+                        cell_acc = my_acc + (v & WD_QMASK);
+                        sT = 0.0;
+                        sE = 0.0;
+                    }
+                } else {
+                    if (!(v & WD_PAD)) {
+                        sT += te[i].x;
+                        sE += te[i].y;
+                    }
+                    if ((v & WD_LAST) && has) {
                         double2 a = *cell_acc;
                         a.x += sT;
                         a.y += sE;
@@ -422,17 +500,7 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
             for (int j = 0; j < PF; ++j)
                 nx[j] = c + PF + j < n ? ld_stream(p + (size_t)(c + PF + j) * 32) : make_uint4(NOP_PAIR, NOP_PAIR, NOP_PAIR, NOP_PAIR);
 #pragma unroll
-            for (int j = 0; j < PF; ++j) {
-                // chunks past the end are no-op headers: no test needed
-                word(cur[j].x & 0xFFFFu);
-                word(cur[j].x >> 16);
-                word(cur[j].y & 0xFFFFu);
-                word(cur[j].y >> 16);
-                word(cur[j].z & 0xFFFFu);
-                word(cur[j].z >> 16);
-                word(cur[j].w & 0xFFFFu);
-                word(cur[j].w >> 16);
-            }
+            for (int j = 0; j < PF; ++j) chunk(cur[j]);  // chunks past the end are no-op headers: no test needed
         }
         // every warp walks every tile of the item (waits for its table, leaves it); the stream carries one NEWTILE
         // header per tile, so the loop body only runs for an item without chunks
@@ -604,8 +672,8 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     if (nnz) {
         k_tile_keys<<<grid_for(nnz), TPB, 0, s>>>(c->csr.p, d_cell_of_entry, nnz, c->tl_NB, c->tl_nT, keys.p, vals.p, d_nlight.p,
                                                   c->row_len.p);
-        int bits = 13;
-        while (bits < 63 && (1ull << bits) <= (((unsigned long long)n_units) << 12)) ++bits;
+        int bits = 16;
+        while (bits < 63 && (1ull << bits) <= (((unsigned long long)n_units) << 15)) ++bits;
         // non-light keys are ~0: sorting on the low `bits + 1` bits still puts them last
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tb, keys.p, keys_sorted.p, vals.p, vals_sorted.p, (int)nnz, 0, bits + 1, s));
         CLX_CUDA(c, tmp.alloc(tb));
@@ -622,9 +690,10 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     CLX_CUDA(c, ukeys.alloc(n_light + 1));
     CLX_CUDA(c, counts.alloc(n_light + 1));
     if (n_light) {
-        CLX_CUDA(c, cub::DeviceRunLengthEncode::Encode(nullptr, tb, keys_sorted.p, ukeys.p, counts.p, d_nruns.p, (int)n_light, s));
+        cub::TransformInputIterator<unsigned long long, DropBank, const unsigned long long*> run_key(keys_sorted.p, DropBank());
+        CLX_CUDA(c, cub::DeviceRunLengthEncode::Encode(nullptr, tb, run_key, ukeys.p, counts.p, d_nruns.p, (int)n_light, s));
         CLX_CUDA(c, tmp.alloc(tb));
-        CLX_CUDA(c, cub::DeviceRunLengthEncode::Encode(tmp.p, tb, keys_sorted.p, ukeys.p, counts.p, d_nruns.p, (int)n_light, s));
+        CLX_CUDA(c, cub::DeviceRunLengthEncode::Encode(tmp.p, tb, run_key, ukeys.p, counts.p, d_nruns.p, (int)n_light, s));
         CLX_CUDA(c, cudaMemcpyAsync(&n_runs, d_nruns.p, 4, cudaMemcpyDeviceToHost, s));
         CLX_CUDA(c, cudaStreamSynchronize(s));
         c->launches += 2;
@@ -632,14 +701,14 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     keys_sorted.release();
     const uint32_t R = (uint32_t)n_runs;
     const uint64_t n_sub = (uint64_t)n_units * W;
-    if (n_sub >= (1ull << 31) - 2) return fail(c, CLX_ERR_ARG, "too many (cell block, tile, warp) sub-units");
+    if (n_sub >= (1ull << 28) - 2) return fail(c, CLX_ERR_ARG, "too many (cell block, tile, warp) sub-units");
     DevBuf<uint32_t> sub_run, n_chunks, chunk_off;
     CLX_CUDA(c, run_start.alloc((size_t)R + 1));
     CLX_CUDA(c, key2.alloc((size_t)R + 1));
     CLX_CUDA(c, key2_sorted.alloc((size_t)R + 1));
     CLX_CUDA(c, ridx.alloc((size_t)R + 1));
     CLX_CUDA(c, ridx_sorted.alloc((size_t)R + 1));
-    CLX_CUDA(c, sub_run.alloc(n_sub + 2));
+    CLX_CUDA(c, sub_run.alloc(8 * n_sub + 2));
     CLX_CUDA(c, n_chunks.alloc(n_sub + 2));
     CLX_CUDA(c, chunk_off.alloc(n_sub + 2));
     CLX_CUDA(c, unit_cost.alloc((size_t)n_units + 2));
@@ -649,14 +718,14 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         CLX_CUDA(c, tmp.alloc(tb));
         CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, cnt64, run_start.p, (int)R, s));
         k_run_keys<<<(R + TPB - 1) / TPB, TPB, 0, s>>>(ukeys.p, counts.p, R, c->tl_nT, W, key2.p, ridx.p);
-        int bits2 = 17;
-        while (bits2 < 63 && (1ull << bits2) <= (n_sub << 16)) ++bits2;
+        int bits2 = 20;
+        while (bits2 < 63 && (1ull << bits2) <= (n_sub << 19)) ++bits2;
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tb, key2.p, key2_sorted.p, ridx.p, ridx_sorted.p, (int)R, 0, bits2, s));
         CLX_CUDA(c, tmp.alloc(tb));
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp.p, tb, key2.p, key2_sorted.p, ridx.p, ridx_sorted.p, (int)R, 0, bits2, s));
         c->launches += 7;
     }
-    k_sub_runs<<<(unsigned)((n_sub + 1 + TPB - 1) / TPB), TPB, 0, s>>>(key2_sorted.p, R, n_sub, sub_run.p);
+    k_sub_runs<<<(unsigned)((8 * n_sub + 1 + TPB - 1) / TPB), TPB, 0, s>>>(key2_sorted.p, R, 8 * n_sub, sub_run.p);
     k_sub_count<<<(unsigned)(((n_sub + 1) * 32 + TPB - 1) / TPB), TPB, 0, s>>>(sub_run.p, ridx_sorted.p, counts.p, n_sub, n_chunks.p,
                                                                                d_steps.p);
     k_unit_cost<<<(n_units + TPB - 1) / TPB, TPB, 0, s>>>(n_chunks.p, n_units, c->tl_nT, W, unit_cost.p);
@@ -691,7 +760,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     }
 
     const char* env_it = getenv("CLX_TILED_ITEMS_PER_SM");
-    const int env_items = env_it && *env_it ? std::max(1, atoi(env_it)) : 2;
+    const int env_items = env_it && *env_it ? std::max(1, atoi(env_it)) : 1;
     // ---- work items: every cell block gets a share of (items per SM x SMs) items proportional to its chunks; its tiles are cut
     //      into that many consecutive ranges of about equal chunk counts
     {
