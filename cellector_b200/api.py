@@ -142,6 +142,17 @@ class CtxApi:
         self.n_loci_used, self.nnz_used = int(nl.value), int(nz.value)
         return self.n_loci_used, self.nnz_used
 
+    def load_cell_data_ptrs(self, locus_ptr, cell_ptr, ref_ptr, alt_ptr, nnz0, n_loci0, n_cells, min_ref=4, min_alt=4):
+        """load_cell_data from raw addresses of four uint32 arrays — host or DEVICE memory (clx_load_coo copies with
+        cudaMemcpyDefault), e.g. torch tensors' data_ptr() for matrices generated on the GPU."""
+        nl, nz = C.c_uint32(0), C.c_uint64(0)
+        self._check(self._f("load_coo")(self._h, int(nnz0), n_loci0, n_cells, C.c_void_p(locus_ptr), C.c_void_p(cell_ptr),
+                                        C.c_void_p(ref_ptr), C.c_void_p(alt_ptr), min_ref, min_alt, C.byref(nl), C.byref(nz)),
+                    "load_coo")
+        self.n_cells, self.n_loci0 = int(n_cells), int(n_loci0)
+        self.n_loci_used, self.nnz_used = int(nl.value), int(nz.value)
+        return self.n_loci_used, self.nnz_used
+
     def load_cell_data_packed(self, locus, cell, ref_alt, n_loci0, n_cells, min_ref=4, min_alt=4):
         """load_cell_data with both counts of an entry in one word (ref | alt << 16)."""
         arrs = [np.ascontiguousarray(x, dtype=np.uint32) for x in (locus, cell, ref_alt)]

@@ -5,6 +5,8 @@
 
 #include <new>
 
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX v3: ranges show up in Nsight Systems / ncu --nvtx, cost nothing otherwise
+
 #include "ctx.h"
 #include "numerics.cuh"
 
@@ -34,7 +36,15 @@ static cudaEvent_t get_event(clx_ctx* c) {
     return e;
 }
 
+static const char* const kPhaseName[CLX_PHASE_COUNT] = {"clx:tables", "clx:score", "clx:heavy", "clx:select", "clx:column", "clx:comm"};
+
+NvtxRange::NvtxRange(const char* name) { nvtxRangePushA(name); }
+NvtxRange::~NvtxRange() { nvtxRangePop(); }
+
+// A phase is always an NVTX range (host side: the enqueue of its kernels, also while a graph is being captured) and,
+// under CLX_FLAG_PROFILE, a CUDA event pair on the stream.
 void phase_begin(clx_ctx* c, int phase) {
+    nvtxRangePushA(kPhaseName[phase]);
     if (!(c->flags & CLX_FLAG_PROFILE)) return;
     PendingEvent p{phase, get_event(c), get_event(c)};
     if (c->capturing) {  // inside a stream capture only "external" records become timing nodes of the graph
@@ -46,6 +56,7 @@ void phase_begin(clx_ctx* c, int phase) {
     }
 }
 void phase_end(clx_ctx* c, int phase) {
+    nvtxRangePop();
     if (!(c->flags & CLX_FLAG_PROFILE)) return;
     std::vector<PendingEvent>& v = c->capturing ? c->graph_events : c->pending;
     for (size_t i = v.size(); i-- > 0;) {

@@ -215,7 +215,15 @@ int fail(clx_ctx* c, int code, const std::string& msg);
         }                                                                                                \
     } while (0)
 
-// profiling scopes (no-ops unless CLX_FLAG_PROFILE)
+// NVTX range for the lifetime of the object (load stages, one EM iteration, the posterior pass)
+struct NvtxRange {
+    explicit NvtxRange(const char* name);
+    ~NvtxRange();
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
+
+// profiling scopes: always an NVTX range; CUDA events only under CLX_FLAG_PROFILE
 void phase_begin(clx_ctx* c, int phase);
 void phase_end(clx_ctx* c, int phase);
 void phase_resolve(clx_ctx* c);  // after a stream sync

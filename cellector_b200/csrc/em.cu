@@ -364,6 +364,7 @@ int enqueue_iteration(clx_ctx* c) {
 
 int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
     if (!c->loaded) return fail(c, CLX_ERR_STATE, "clx_em_iteration before clx_load_coo");
+    NvtxRange nvtx("clx:em_iteration");
     cudaStream_t s = c->stream;
     c->h_params->iqr_multiple = iqr_multiple;
     // The iteration is replayed as a CUDA graph (a dozen launches, ~100 us of work at 10x scale: launch gaps matter),
@@ -432,6 +433,7 @@ int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
 
 int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used) {
     if (!c->loaded) return fail(c, CLX_ERR_STATE, "clx_posteriors before clx_load_coo");
+    NvtxRange nvtx("clx:posteriors");
     cudaStream_t s = c->stream;
     const uint32_t N = c->n_cells, L = c->n_loci;
     // main.rs:240, 250, 259-265 — scalars on the host in the reference's expression order

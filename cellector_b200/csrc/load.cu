@@ -190,6 +190,7 @@ int bits_for(uint64_t n) {
 
 int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, const uint32_t* locus,
              const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt) {
+    NvtxRange nvtx("clx:load_coo");
     cudaStream_t s = c->stream;
     c->loaded = false;
     // every cub call below takes a 32-bit signed item count
@@ -221,15 +222,17 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     CLX_CUDA(c, d_ref.alloc(nnz0));
     CLX_CUDA(c, d_alt.alloc(nnz0));
     if (nnz0) {
-        CLX_CUDA(c, cudaMemcpyAsync(d_locus.p, locus, nnz0 * 4, cudaMemcpyHostToDevice, s));
-        CLX_CUDA(c, cudaMemcpyAsync(d_cell.p, cell, nnz0 * 4, cudaMemcpyHostToDevice, s));
+        // cudaMemcpyDefault: the caller's arrays may be pageable or pinned host memory, or device memory (a host that
+        // parses or generates on the GPU); the copy engine picks the path from the pointer
+        CLX_CUDA(c, cudaMemcpyAsync(d_locus.p, locus, nnz0 * 4, cudaMemcpyDefault, s));
+        CLX_CUDA(c, cudaMemcpyAsync(d_cell.p, cell, nnz0 * 4, cudaMemcpyDefault, s));
         if (alt) {
-            CLX_CUDA(c, cudaMemcpyAsync(d_ref.p, ref, nnz0 * 4, cudaMemcpyHostToDevice, s));
-            CLX_CUDA(c, cudaMemcpyAsync(d_alt.p, alt, nnz0 * 4, cudaMemcpyHostToDevice, s));
+            CLX_CUDA(c, cudaMemcpyAsync(d_ref.p, ref, nnz0 * 4, cudaMemcpyDefault, s));
+            CLX_CUDA(c, cudaMemcpyAsync(d_alt.p, alt, nnz0 * 4, cudaMemcpyDefault, s));
         } else {  // both counts in one word: 4 bytes less per entry over PCIe, split on the device
             DevBuf<uint32_t> d_packed;
             CLX_CUDA(c, d_packed.alloc(nnz0));
-            CLX_CUDA(c, cudaMemcpyAsync(d_packed.p, ref, nnz0 * 4, cudaMemcpyHostToDevice, s));
+            CLX_CUDA(c, cudaMemcpyAsync(d_packed.p, ref, nnz0 * 4, cudaMemcpyDefault, s));
             k_unpack_counts<<<grid_for(nnz0), TPB, 0, s>>>(d_packed.p, nnz0, d_ref.p, d_alt.p);
             c->launches++;
         }

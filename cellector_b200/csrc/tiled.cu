@@ -44,18 +44,30 @@ namespace {
 
 constexpr int TPB = 256;
 constexpr uint32_t NB_MAX = 4096;        // cells per block: 16 B of accumulators each = 64 KB of shared memory
-constexpr uint32_t W_MAX = 16;           // warps per CTA
+constexpr uint32_t W_MAX = 32;           // warps per CTA
 constexpr uint32_t CHUNK_WORDS = 8;      // 16-bit words per lane and chunk (one LDG.128)
-constexpr int PF = 3;                    // chunks in flight per lane ahead of the one being summed
-// word encoding (all flags are identical in the 32 lanes of a chunk position, except WD_IDLE)
-constexpr uint32_t WD_HEADER = 0x8000u;   // header word: opens a group (or is a no-op)
-constexpr uint32_t WD_NEWTILE = 0x4000u;  // header: this sub-unit belongs to the next tile of the item
-constexpr uint32_t WD_NOP = 0x2000u;      // header: no group follows (empty sub-unit / chunk padding)
-constexpr uint32_t WD_IDLE = 0x1000u;     // header: this lane has no run in the group
-constexpr uint32_t WD_QMASK = 0x01FFu;    // header: index of the lane's cell among the warp's cells
-constexpr uint32_t WD_LAST = 0x4000u;     // entry word: last step of the group
-constexpr uint32_t WD_PAD = 0x2000u;      // entry word: padding (the lane has no entry in this step): no lookup
+// Stream format.  A chunk is 8 words per lane; every chunk is either a CELL chunk or an ENTRY chunk, and which one is
+// warp-uniform (bit 15 of word 0):
+//   cell chunk   word i = the accumulator index of the lane's cell in the i-th of the next (up to) 8 groups
+//                (WC_IDLE: the lane has no run in that group); word 0 also carries WC_CELLS and, for the first chunk of
+//                a sub-unit, WC_NEWTILE.  The entry chunks of those groups follow; the next cell chunk comes after
+//                them, on a chunk boundary.
+//   entry chunk  two PIECES of 4 words.  A group is a whole number of pieces, so the decoder is straight-line code per
+//                piece: word = slot inside the staged tile; word 0 also carries (valid words of the piece - 1) in
+//                WD_CNT, word 1 carries WD_LAST if the group ends with this piece (both warp-uniform).  A lane with no
+//                entry in a step reads one of the 8 all-zero slots behind the tile, the one in a bank group no other
+//                lane of its quarter warp uses in that step: padding costs no shared-memory wavefront and no branch.
+constexpr uint32_t WC_CELLS = 0x8000u;    // word 0 of a cell chunk
+constexpr uint32_t WC_NEWTILE = 0x4000u;  // word 0 of a cell chunk: this sub-unit belongs to the next tile of the item
+constexpr uint32_t WC_IDLE = 0x1000u;     // cell word: this lane has no run in the group
+constexpr uint32_t WC_QMASK = 0x01FFu;    // cell word: index of the lane's cell among the warp's cells
+constexpr uint32_t WD_CNT_SHIFT = 13;     // word 0 of a piece: valid words - 1 (2 bits)
+constexpr uint32_t WD_LAST = 0x4000u;     // word 1 of a piece: the group ends with this piece
 constexpr uint32_t WD_SLOT = 0x1FFFu;     // entry word: slot inside the staged tile
+constexpr uint32_t STREAM_PF = 3;          // 512-byte stream chunks in flight per warp (registers)
+constexpr uint32_t PIECE_WORDS = 4;
+constexpr uint32_t ZERO_SLOTS = 8;        // all-zero slots behind a staged tile, one per 16-byte bank group
+constexpr uint32_t GROUPS_PER_CELL_CHUNK = 8;
 constexpr uint32_t NULL_SLOT = (uint32_t)TILE_SLOTS;
 static_assert(TILE_SLOTS < 0x1FFF, "slot index fits 13 bits");
 
@@ -163,8 +175,7 @@ struct GroupWalk {
     }
 };
 
-// one warp per sub-unit: words per lane = sum over groups of (1 header + longest run), at least the one header an
-// empty sub-unit needs; rounded up to whole chunks.  steps = lookup steps (padding included) of the sub-unit.
+// one warp per sub-unit: its chunks.  steps = lookup steps (padding included) of the sub-unit.
 __global__ void k_sub_count(const uint32_t* __restrict__ sub_run, const uint32_t* __restrict__ idx_sorted,
                             const int* __restrict__ counts, uint64_t n_sub, uint32_t* __restrict__ n_chunks,
                             unsigned long long* __restrict__ total_steps) {
@@ -176,16 +187,21 @@ __global__ void k_sub_count(const uint32_t* __restrict__ sub_run, const uint32_t
         return;
     }
     const GroupWalk gw(sub_run, su, lane);
-    uint64_t words = 0, steps = 0;
+    // per block of 8 groups: one cell chunk + the entry words of the groups rounded up to whole chunks
+    uint64_t chunks = 0, steps = 0, block_words = 0;
     for (uint32_t g = 0; g < gw.G; ++g) {
         const uint32_t r = gw.run_of(g, lane);
         const uint32_t M = warp_max_u32(r != 0xFFFFFFFFu ? (uint32_t)counts[idx_sorted[r]] : 0u);
-        words += 1u + M;
+        block_words += (M + PIECE_WORDS - 1) / PIECE_WORDS * PIECE_WORDS;
         steps += M;
+        if ((g + 1) % GROUPS_PER_CELL_CHUNK == 0 || g + 1 == gw.G) {
+            chunks += 1 + (block_words + CHUNK_WORDS - 1) / CHUNK_WORDS;
+            block_words = 0;
+        }
     }
-    if (words == 0) words = 1;
+    if (gw.G == 0) chunks = 1;  // the cell chunk that announces the tile
     if (lane == 0) {
-        n_chunks[su] = (uint32_t)((words + CHUNK_WORDS - 1) / CHUNK_WORDS);
+        n_chunks[su] = (uint32_t)chunks;
         if (steps) atomicAdd(total_steps, (unsigned long long)steps);
     }
 }
@@ -239,21 +255,32 @@ __global__ void __launch_bounds__(TPB) k_sub_fill(const uint32_t* __restrict__ s
     sink.dst = stream + (size_t)chunk_off[su] * 32 + lane;
     sink.lo = sink.hi = 0;
     sink.pos = 0;
-    if (gw.G == 0) sink.put(WD_HEADER | WD_NEWTILE | WD_NOP);
+    if (gw.G == 0) {
+        sink.put(WC_CELLS | WC_NEWTILE | WC_IDLE);
+        while (sink.pos != 0) sink.put(WC_IDLE);
+    }
     const int qbase = (int)(lane & ~7u);
     for (uint32_t g = 0; g < gw.G; ++g) {
+        if (g % GROUPS_PER_CELL_CHUNK == 0) {
+            // close the previous block on a chunk boundary, then the cell chunk of groups g .. g + 7
+            while (sink.pos != 0) sink.put(NULL_SLOT);  // a filler piece: one valid word that reads a zero slot, no WD_LAST
+            for (uint32_t i = 0; i < GROUPS_PER_CELL_CHUNK; ++i) {
+                const uint32_t ri = g + i < gw.G ? gw.run_of(g + i, lane) : 0xFFFFFFFFu;
+                uint32_t cw = WC_IDLE;
+                if (ri != 0xFFFFFFFFu) cw = ((uint32_t)(ukeys[idx_sorted[ri]] & 0xFFFull) / W) & WC_QMASK;  // slot = warp * Q + q
+                sink.put(cw | (i == 0 ? (WC_CELLS | (g == 0 ? WC_NEWTILE : 0u)) : 0u));
+            }
+        }
         const uint32_t r = gw.run_of(g, lane);
         const bool has = r != 0xFFFFFFFFu;
-        uint32_t cnt = 0, q = 0;
+        uint32_t cnt = 0;
         unsigned long long src = 0;
         if (has) {
             const uint32_t rid = idx_sorted[r];
             cnt = (uint32_t)counts[rid];
             src = run_start[rid];
-            q = (uint32_t)(ukeys[rid] & 0xFFFull) / W;  // accumulator slot of the cell = warp * Q + q, Q a multiple of 8
         }
         const uint32_t M = warp_max_u32(cnt);
-        sink.put(WD_HEADER | (g == 0 ? WD_NEWTILE : 0u) | (has ? (q & WD_QMASK) : WD_IDLE));
         // per bank group: how many entries, where they start (the run is sorted by bank group)
         uint32_t avail = 0;  // bit b: entries of bank group b left
 #pragma unroll
@@ -298,7 +325,7 @@ __global__ void __launch_bounds__(TPB) k_sub_fill(const uint32_t* __restrict__ s
                     if (pb >= 0) used += 1u << (4 * pb);
                 }
             }
-            uint32_t w16 = WD_PAD | NULL_SLOT;
+            uint32_t w16;
             if (pick >= 0) {
                 const uint32_t at = s_cur[wib][pick][lane];
                 w16 = (uint32_t)vals_sorted[src + at];
@@ -307,11 +334,20 @@ __global__ void __launch_bounds__(TPB) k_sub_fill(const uint32_t* __restrict__ s
                 s_left[wib][pick][lane] = l2;
                 if (l2 == 0) avail &= ~(1u << pick);
                 --rem;
+            } else {  // sit the step out on the zero slot of a bank group nobody in this quarter uses now
+                uint32_t f = 0;
+                while (f < 7 && ((used >> (4 * f)) & 15u)) ++f;
+                w16 = NULL_SLOT + f;
             }
-            sink.put(w16 | (st + 1 == M ? WD_LAST : 0u));
+            const uint32_t pos = st % PIECE_WORDS, piece0 = st - pos;
+            if (pos == 0) w16 |= (min(PIECE_WORDS, M - piece0) - 1u) << WD_CNT_SHIFT;
+            if (pos == 1 && piece0 + PIECE_WORDS >= M) w16 |= WD_LAST;
+            sink.put(w16);
         }
+        // complete the group's last piece (word 1 of a one-word piece still carries WD_LAST)
+        for (uint32_t st = M; st % PIECE_WORDS != 0; ++st) sink.put(NULL_SLOT | (st % PIECE_WORDS == 1 ? WD_LAST : 0u));
     }
-    while (sink.pos != 0) sink.put(WD_HEADER | WD_NOP);
+    while (sink.pos != 0) sink.put(NULL_SLOT);
 }
 
 // per queue slot and warp: the warp's chunk range over the item's tiles (one consecutive range, see sub_unit_of)
@@ -362,11 +398,10 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
 }
 
 constexpr size_t TB_BYTES = (size_t)TILE_SLOTS * 16;                              // bytes one table bulk copy moves
-constexpr size_t TB_BUF = (((size_t)(TILE_SLOTS + 1) * 16) + 127) / 128 * 128;    // + the all-zero slot
+constexpr size_t TB_BUF = (((size_t)(TILE_SLOTS + ZERO_SLOTS) * 16) + 127) / 128 * 128;  // + the all-zero slots
 constexpr size_t TL_ACC_BYTES = (size_t)NB_MAX * 16;
 constexpr size_t TL_SMEM = 2 * TB_BUF + TL_ACC_BYTES + 64;
 static_assert(TL_SMEM <= 227 * 1024, "shared memory budget of the scoring kernel");
-constexpr uint32_t NOP_PAIR = (WD_HEADER | WD_NOP) | ((WD_HEADER | WD_NOP) << 16);
 
 // Table buffers: tile g of a CTA (counted over all its items) lives in buffer g & 1; tab_full[b] is the mbarrier its
 // bulk copy completes on (parity (g >> 1) & 1), tab_done[b] counts the warps that have finished with the buffer.
@@ -423,8 +458,8 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
         tab_done[1] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (tid < 2)  // the all-zero slot behind each table buffer (padding entries point at it)
-        reinterpret_cast<double2*>(smem + (size_t)tid * TB_BUF)[TILE_SLOTS] = make_double2(0.0, 0.0);
+    if (tid < 2 * ZERO_SLOTS)  // the all-zero slots behind each table buffer (padding words point at them)
+        reinterpret_cast<double2*>(smem + (size_t)(tid / ZERO_SLOTS) * TB_BUF)[TILE_SLOTS + tid % ZERO_SLOTS] = make_double2(0.0, 0.0);
     for (uint32_t i = tid; i < NB; i += blockDim.x) acc[i] = make_double2(0.0, 0.0);
     __syncthreads();
     uint32_t g_tile = 0;  // tiles consumed by this CTA so far (buffer = g & 1, parity = (g >> 1) & 1)
@@ -438,9 +473,11 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
         const uint32_t t0 = it.y, ntile = it.z, item = it.w;
         const uint4* p = stream + (size_t)rng.x * 32 + lane;
         const uint32_t n = rng.y - rng.x;
-        uint4 nx[PF];
+        // three chunks in flight per lane: registers, no staging ring (loads past the end re-read the last chunk)
+        const uint32_t nl = n ? n - 1 : 0;
+        uint4 pf[STREAM_PF];
 #pragma unroll
-        for (int j = 0; j < PF; ++j) nx[j] = (uint32_t)j < n ? ld_stream(p + (size_t)j * 32) : make_uint4(NOP_PAIR, NOP_PAIR, NOP_PAIR, NOP_PAIR);
+        for (uint32_t j = 0; j < STREAM_PF; ++j) pf[j] = ld_stream(p + (size_t)min(j, nl) * 32);
         if (tid == 0) {
             for (uint32_t k = 0; k < 2 && k < ntile; ++k) {
                 const uint32_t g = g_tile + k;
@@ -451,57 +488,67 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
         int k = -1;                    // item-local tile this warp is in
         const double2* tab = nullptr;  // its staged slots
         double sT = 0.0, sE = 0.0;     // the lane's run
-        double2* cell_acc = my_acc;
-        bool has = false;
-        // One chunk = 8 words per lane.  A sub-unit starts on a chunk boundary, so only word 0 can announce the next
-        // tile; after that all 8 lookups of the chunk go out back to back (predicated off for header words: eight
-        // independent LDS.128 in flight per warp keep the shared-memory pipe full), then the words are consumed in
-        // order: a header opens a group, the last entry of a group adds the lane's run to its cell's accumulator.
-        auto chunk = [&](const uint4 cw) {
-            uint32_t wd[CHUNK_WORDS] = {cw.x & 0xFFFFu, cw.x >> 16, cw.y & 0xFFFFu, cw.y >> 16,
-                                        cw.z & 0xFFFFu, cw.z >> 16, cw.w & 0xFFFFu, cw.w >> 16};
-            if ((wd[0] & (WD_HEADER | WD_NEWTILE)) == (WD_HEADER | WD_NEWTILE)) {
-                tab = reinterpret_cast<const double2*>(smem + enter_tile(smem, k, g_tile, t0, ntile, nw, tab16));
-                ++k;
-            }
-            double2 te[CHUNK_WORDS];
-#pragma unroll
-            for (int i = 0; i < (int)CHUNK_WORDS; ++i)
-                if (!(wd[i] & (WD_HEADER | WD_PAD))) te[i] = tab[wd[i] & WD_SLOT];
-#pragma unroll
-            for (int i = 0; i < (int)CHUNK_WORDS; ++i) {
-                const uint32_t v = wd[i];
-                if (v & WD_HEADER) {
-                    if (!(v & WD_NOP)) {
-                        has = !(v & WD_IDLE);
-                        cell_acc = my_acc + (v & WD_QMASK);
-                        sT = 0.0;
-                        sE = 0.0;
-                    }
-                } else {
-                    if (!(v & WD_PAD)) {
-                        sT += te[i].x;
-                        sE += te[i].y;
-                    }
-                    if ((v & WD_LAST) && has) {
-                        double2 a = *cell_acc;
-                        a.x += sT;
-                        a.y += sE;
-                        *cell_acc = a;
-                    }
+        uint4 cq = make_uint4(0u, 0u, 0u, 0u);  // accumulator indices of the lane's cells in the coming groups, 16 bits each
+        // One chunk = 8 words per lane.  A cell chunk refills cq (and may announce the next tile).  In an entry chunk
+        // all 8 lookups go out back to back (predicated off for padding words: eight independent LDS.128 in flight
+        // per warp keep the shared-memory pipe full), then the words are consumed in order; the last step of a group
+        // (warp-uniform) adds the lane's run to its cell's accumulator and takes the next cell off cq.
+        // One piece = 4 words per lane, 1..4 of them valid (warp-uniform count): the lookups go out back to back, then
+        // the sums; if the group ends here (warp-uniform flag) the lane's run is added to its cell's accumulator and
+        // the next cell comes off cq.
+        auto piece = [&](const uint32_t lo, const uint32_t hi) {
+            const uint32_t cnt = (lo >> WD_CNT_SHIFT) & 3u;
+            const double2 t0 = tab[lo & WD_SLOT];
+            double2 t1 = make_double2(0.0, 0.0), t2 = t1, t3 = t1;
+            if (cnt >= 1) t1 = tab[(lo >> 16) & WD_SLOT];
+            if (cnt >= 2) t2 = tab[hi & WD_SLOT];
+            if (cnt >= 3) t3 = tab[(hi >> 16) & WD_SLOT];
+            sT += (t0.x + t1.x) + (t2.x + t3.x);
+            sE += (t0.y + t1.y) + (t2.y + t3.y);
+            if (lo & (WD_LAST << 16)) {
+                const uint32_t cell = cq.x;
+                cq.x = __funnelshift_r(cq.x, cq.y, 16);
+                cq.y = __funnelshift_r(cq.y, cq.z, 16);
+                cq.z = __funnelshift_r(cq.z, cq.w, 16);
+                cq.w >>= 16;
+                if (!(cell & WC_IDLE)) {
+                    double2* cell_acc = my_acc + (cell & WC_QMASK);
+                    double2 a = *cell_acc;
+                    a.x += sT;
+                    a.y += sE;
+                    *cell_acc = a;
                 }
+                sT = 0.0;
+                sE = 0.0;
             }
         };
-        for (uint32_t c = 0; c < n; c += PF) {
-            uint4 cur[PF];
+        auto chunk = [&](const uint4 cw) {
+            if (cw.x & WC_CELLS) {
+                if (cw.x & WC_NEWTILE) {
+                    tab = reinterpret_cast<const double2*>(smem + enter_tile(smem, k, g_tile, t0, ntile, nw, tab16));
+                    ++k;
+                }
+                cq = cw;
+                return;
+            }
+            piece(cw.x, cw.y);
+            piece(cw.z, cw.w);
+        };
+        // three chunks per trip, each register set reloaded right after its chunk is consumed: moving an in-flight
+        // load between registers would wait for it (measured: long-scoreboard stalls dominated the rotated form)
+        uint32_t c = 0;
+#pragma unroll 1
+        for (; c + STREAM_PF <= n; c += STREAM_PF) {
 #pragma unroll
-            for (int j = 0; j < PF; ++j) cur[j] = nx[j];
-#pragma unroll
-            for (int j = 0; j < PF; ++j)
-                nx[j] = c + PF + j < n ? ld_stream(p + (size_t)(c + PF + j) * 32) : make_uint4(NOP_PAIR, NOP_PAIR, NOP_PAIR, NOP_PAIR);
-#pragma unroll
-            for (int j = 0; j < PF; ++j) chunk(cur[j]);  // chunks past the end are no-op headers: no test needed
+            for (uint32_t j = 0; j < STREAM_PF; ++j) {
+                const uint4 cur = pf[j];
+                pf[j] = ld_stream(p + (size_t)min(c + STREAM_PF + j, nl) * 32);
+                chunk(cur);
+            }
         }
+#pragma unroll
+        for (uint32_t j = 0; j + 1 < STREAM_PF; ++j)
+            if (c + j < n) chunk(pf[j]);
         // every warp walks every tile of the item (waits for its table, leaves it); the stream carries one NEWTILE
         // header per tile, so the loop body only runs for an item without chunks
         while (k + 1 < (int)ntile) {
@@ -616,6 +663,7 @@ int score_tiled(clx_ctx* c, ScoreMode mode) {
 }
 
 int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
+    NvtxRange nvtx("clx:build_run_stream");
     cudaStream_t s = c->stream;
     c->tiled_ready = false;
     const uint32_t N = c->n_cells, L = c->n_loci;
@@ -627,11 +675,11 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     // the runs of a group have equal lengths) but enough (cell block, tile) units to fill the SMs
     c->tl_nT = L ? (L + TILE_L - 1) / TILE_L : 1;
     {
-        uint32_t W = W_MAX;
+        uint32_t W = 16;
         const char* env_w = getenv("CLX_TILED_W");
         uint32_t pc = N ? (N + NB_MAX - 1) / NB_MAX : 1;
-        // two work items per SM, each at least ~2 consecutive tiles long
-        const uint32_t want = (4u * (uint32_t)c->sm_count + c->tl_nT - 1) / c->tl_nT;
+        // at least ~2 (cell block, tile) units per SM, so that the one-item-per-SM split has something to balance
+        const uint32_t want = (2u * (uint32_t)c->sm_count + c->tl_nT - 1) / c->tl_nT;
         const uint32_t pc_cap = N ? std::max<uint32_t>(1u, N / 512u) : 1u;
         pc = std::max(pc, std::min(want, pc_cap));
         const char* env = getenv("CLX_TILED_PC");

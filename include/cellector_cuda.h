@@ -104,7 +104,8 @@ int clx_nccl_unique_id(void* out128);
 int clx_comm_init(clx_ctx* ctx, int rank, int world, const void* unique_id128);
 
 /* Load this rank's cells.  COO arrays are in FILE ORDER (the order of the lines of alt.mtx/ref.mtx),
- * 0-based, caller-owned, pageable or pinned host memory.  `cell` holds rank-local cell ids in
+ * 0-based, caller-owned: pageable or pinned host memory, or device memory (copied with cudaMemcpyDefault).
+ * `cell` holds rank-local cell ids in
  * [0, n_cells).  Duplicated coordinates are kept as separate entries and zero-total entries are kept,
  * exactly like load_data.rs:151-174.  The locus filter (load_data.rs:268-273) counts, per locus, the
  * entries with ref>0 and with alt>0 (over all ranks) and keeps loci with both counts >= min. */

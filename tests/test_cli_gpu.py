@@ -130,6 +130,33 @@ def test_cli_outputs_match_oracle(tmp_path, oracle_lib, with_vcf):
                 assert maj[0] in ("./.", "0/0", "0/1", "1/1") and 1 / 3 - 1e-9 <= float(maj[1]) <= 1.0 + 1e-12
             ao = np.array([int(x[9].split(":")[2]) for x in recs])
             assert_equal(ao, mj[:, 1].astype(np.int64), "vcf majority AO")
+            # GT / GP of EVERY record against main.rs:79-118 restated with the oracle's statrs Binomial::pmf
+            pmf = oracle_lib.orc_binomial_pmf
+
+            def call(a, r, soup):
+                ps = [(1.0 - 0.03) * q + 0.03 * soup for q in (0.99, 0.5, 0.01)]
+                like = [pmf(q, int(a + r), int(a)) for q in ps]
+                den = 1.0 / 3.0 * like[0] + 1.0 / 3.0 * like[1] + 1.0 / 3.0 * like[2]
+                post = [l * 1.0 / 3.0 / den for l in like]
+                gt_s = "./."
+                for pp, name in zip(post, ("1/1", "0/1", "0/0")):
+                    if pp > 0.99:
+                        gt_s = name
+                        break
+                return gt_s, max(post)
+
+            n_called = 0
+            for i, rec in enumerate(recs):
+                ta, tr = int(mn[i, 1] + mj[i, 1]), int(mn[i, 0] + mj[i, 0])
+                soup = ta / (ta + tr) if ta + tr > 0 else 0.5
+                for field, cnt in ((rec[9], mj[i]), (rec[10], mn[i])):
+                    g, gp, a_s, r_s = field.split(":")
+                    want_gt, want_gp = call(int(cnt[1]), int(cnt[0]), soup)
+                    assert (int(a_s), int(r_s)) == (int(cnt[1]), int(cnt[0]))
+                    assert g == want_gt, (i, field, want_gt)
+                    assert float(gp) == pytest.approx(want_gp, rel=1e-9, abs=1e-300), (i, field, want_gp)
+                    n_called += g != "./."
+            assert n_called > d.n_loci // 4  # the check above is not vacuous: many genotypes are called
         else:
             assert not os.path.exists(out / "cellector.vcf")
     import json

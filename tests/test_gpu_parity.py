@@ -30,6 +30,9 @@ CASES = {
     "skewed": synth.SynthConfig(n_cells=3000, n_loci=6000, density=0.01, minority_frac=0.05, seed=7, row_sigma=2.0),
     "doublets": synth.SynthConfig(n_cells=1500, n_loci=5000, density=0.03, minority_frac=0.1, seed=9, doublet_frac=0.05),
     "big_select": synth.SynthConfig(n_cells=40000, n_loci=1500, density=0.004, minority_frac=0.05, seed=11),
+    # the oracle rescues 2 cells and the -80 rule switches 11 loci off over 5 iterations (searched with the oracle)
+    "rescue_filter": synth.SynthConfig(n_cells=700, n_loci=2000, density=0.05, minority_frac=0.1, seed=2, deep_frac=0.08,
+                                       deep_mean=100.0, doublet_frac=0.05),
 }
 
 
@@ -217,3 +220,50 @@ def test_parity_dense_tiles(libs, monkeypatch):
     cfg = synth.SynthConfig(n_cells=3072, n_loci=1536, density=2.0, minority_frac=0.05, seed=13)
     with gpu, orc:
         run_parity(gpu, orc, synth.generate(cfg))
+
+
+def _worker(case, flags=0, env=None):
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "parity_worker.py"), case, str(flags)], capture_output=True, text=True,
+                       timeout=900, cwd=root, env={**os.environ, **(env or {})})
+    assert r.returncode == 0 and "PARITY_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_parity_rescued_cells_and_filtered_loci(libs):
+    """The case must really exercise the rescue counter and the -80 rule (checked on the oracle's own statistics)."""
+    gpu, orc = _pair(libs)
+    d = synth.generate(CASES["rescue_filter"])
+    with gpu, orc:
+        run_parity(gpu, orc, d)
+        orc.reset()
+        rescued = filtered = 0
+        for _ in range(30):
+            st = orc.compute_new_excluded(5.0)
+            rescued += st.n_rescued
+            filtered += st.n_loci_filtered
+            if not st.any_change:
+                break
+        assert rescued >= 1 and filtered >= 2, (rescued, filtered)
+
+
+def test_parity_gather_kernel_flag(libs):
+    """CLX_FLAG_KERNEL_V0: the CSR gather scorer (k_score_rows) instead of the run-stream kernel, EM and posterior pass."""
+    gpu, orc = _pair(libs, flags=4)
+    with gpu, orc:
+        run_parity(gpu, orc, synth.generate(CASES["deep"]))
+
+
+def test_parity_multi_launch_select():
+    """CLX_SELECT_MODE=2: the multi-launch radix select (the path of N > 2.4 M gathered cells), forced on a small case."""
+    _worker("c1_slice", env={"CLX_SELECT_MODE": "2"})
+    _worker("deep", env={"CLX_SELECT_MODE": "2"})
+
+
+def test_parity_select_four_keys_per_thread():
+    _worker("select_r4")
+
+
+def test_parity_giant_heavy_entries():
+    _worker("giant")
