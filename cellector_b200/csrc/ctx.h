@@ -114,6 +114,7 @@ struct clx_ctx {
     clx::DevBuf<uint64_t> row_ptr;            // [n_cells + 1]
     clx::DevBuf<clx::ColEntry> csc;           // [nnz] columns = used loci, cells ascending inside a column
     clx::DevBuf<uint64_t> col_ptr;            // [n_loci + 1]
+    clx::DevBuf<uint32_t> cls_all;            // [n_loci][CLS_STRIDE] stored entries of every locus by (alt | total) class
     clx::DevBuf<unsigned long long> locus_tot;  // [2 * n_loci] (ref, alt) totals over all ranks
     // heavy entries (total > K_LIGHT or a count that does not fit u16), CSR order
     clx::DevBuf<uint32_t> h_cell, h_locus, h_ref, h_alt;  // [n_heavy]
@@ -154,6 +155,8 @@ struct clx_ctx {
     bool have_iteration = false;
     clx::DevBuf<uint32_t> excl_bits;                  // [(n_cells + 31) / 32] current excluded set, updated in place
     clx::DevBuf<uint8_t> loci_used;                   // [n_loci]
+    clx::DevBuf<uint32_t> cls_min;                    // [n_loci][CLS_STRIDE] the same counts over the excluded cells only
+    clx::DevBuf<uint32_t> excl_prev;                  // excluded set cls_min was last brought up to date with
     clx::DevBuf<unsigned long long> min_cnt;          // [2 * n_loci] minority (ref, alt) over all stored entries
     clx::DevBuf<double> tab;                          // [3][n_loci][16] memo tables (slot 0 = EM, 0..2 = posteriors)
     clx::DevBuf<double> ll, ell, norm;                // [n_cells] outputs of the last EM iteration

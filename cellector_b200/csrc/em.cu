@@ -84,6 +84,26 @@ void launch_columns(clx_ctx* c, int G) {
     c->launches++;
 }
 
+// the column pass from per-locus class counts (k_excl_delta + k_locus_finish, em_kernels.cuh)
+template <bool FUSE>
+void launch_locus_classes(clx_ctx* c) {
+    const uint32_t N = c->n_cells, L = c->n_loci;
+    if (N) {
+        const uint32_t words = (N + 31u) / 32u;
+        k_excl_delta<<<(unsigned)(((uint64_t)words * 32 + TPB - 1) / TPB), TPB, 0, c->stream>>>(c->csr.p, c->row_ptr.p, N, c->excl_bits.p,
+                                                                                            c->excl_prev.p, c->cls_min.p);
+        c->launches++;
+    }
+    if (L == 0) return;
+    double* out_ll = c->p2p ? reinterpret_cast<double*>((unsigned char*)c->win + c->win_off_part_ll) : c->loc_ll.p;
+    unsigned long long* out_int = c->p2p ? reinterpret_cast<unsigned long long*>((unsigned char*)c->win + c->win_off_part_int) : c->loc_int.p;
+    k_locus_finish<FUSE><<<(L + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->cls_all.p, c->cls_min.p, L, c->tab.p, c->loci_used.p, c->excl_bits.p,
+                                                                    c->hc_col_ptr.p, c->hc_perm.p, c->h_cell.p, c->h_ref.p, c->h_alt.p,
+                                                                    c->hv_ll.p, c->csc.p, c->col_ptr.p, out_ll, out_int, c->n_used.p,
+                                                                    c->d_stats.p);
+    c->launches++;
+}
+
 // ranks + interpolation weights of statrs' Data::{median, quantile} for n values
 void quantile_plan(uint64_t n, double tau, unsigned long long* ra, unsigned long long* rb, double* frac, int* mode) {
     *ra = *rb = 0;
@@ -176,6 +196,8 @@ int em_alloc(clx_ctx* c) {
     em_drop_graph(c);
     CLX_CUDA(c, c->excl_bits.alloc(words));
     CLX_CUDA(c, c->loci_used.alloc(L + 1));
+    CLX_CUDA(c, c->cls_min.alloc((L + 1) * CLS_STRIDE));
+    CLX_CUDA(c, c->excl_prev.alloc(words));
     CLX_CUDA(c, c->tab.alloc(3 * L * TAB_STRIDE + TAB_STRIDE));
     CLX_CUDA(c, c->ll.alloc(N + 1));
     CLX_CUDA(c, c->post_ll.alloc(3 * N + 1));
@@ -213,6 +235,8 @@ int em_reset(clx_ctx* c) {
     cudaStream_t s = c->stream;
     CLX_CUDA(c, cudaMemsetAsync(c->excl_bits.p, 0, c->excl_bits.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->loci_used.p, 1, c->loci_used.bytes(), s));
+    CLX_CUDA(c, cudaMemsetAsync(c->cls_min.p, 0, c->cls_min.bytes(), s));
+    CLX_CUDA(c, cudaMemsetAsync(c->excl_prev.p, 0, c->excl_prev.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->loc_int.p, 0, c->loc_int.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->loc_ll.p, 0, c->loc_ll.bytes(), s));
     if (c->n_cells) CLX_CUDA(c, cudaMemcpyAsync(c->n_used.p, c->row_len.p, (size_t)c->n_cells * 4, cudaMemcpyDeviceToDevice, s));
@@ -324,8 +348,13 @@ int enqueue_iteration(clx_ctx* c) {
     // 4. per-locus contributions split by the NEW set (main.rs:343) + minority allele counts for the next
     //    alpha/beta + the -80 locus filter (main.rs:444-451; after the allreduce when cells are sharded)
     phase_begin(c, CLX_PHASE_COLUMN);
-    if (c->world > 1) launch_columns<false>(c, c->col_G);
-    else launch_columns<true>(c, c->col_G);
+    if (c->flags & CLX_FLAG_KERNEL_V0) {  // the column walk (k_columns): kept as the cross-check of the class-count pass
+        if (c->world > 1) launch_columns<false>(c, c->col_G);
+        else launch_columns<true>(c, c->col_G);
+    } else {
+        if (c->world > 1) launch_locus_classes<false>(c);
+        else launch_locus_classes<true>(c);
+    }
     phase_end(c, CLX_PHASE_COLUMN);
     CLX_DEBUG_SYNC(c, "k_columns");
     if (c->world > 1) {

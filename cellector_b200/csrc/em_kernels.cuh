@@ -636,6 +636,128 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Column pass without the column walk.  A light entry's log_pmf depends only on (locus, alt, total), so the per-locus
+// sums of get_locus_log_likelihoods (main.rs:368-420) are dot products of per-locus CLASS COUNTS with the locus's
+// memo record: cls_all (all stored entries, fixed at load) and cls_min (entries of the excluded cells).  cls_min is
+// kept up to date incrementally: only the rows of cells whose excluded bit changed since the last pass are walked
+// (integer atomics, so the result does not depend on the order), which after the first iterations is a handful of rows
+// instead of every nonzero of the matrix.
+//
+// One warp per 32-cell bitmap word; the changed cells of the word are taken one after the other, the row spread over
+// the lanes.  The warp owns prev[word] and brings it up to date itself.
+__global__ void __launch_bounds__(256) k_excl_delta(const RowEntry* __restrict__ csr, const uint64_t* __restrict__ row_ptr,
+                                                    uint32_t n_cells, const uint32_t* __restrict__ bits,
+                                                    uint32_t* __restrict__ prev, uint32_t* __restrict__ cls_min) {
+    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (w >= (n_cells + 31u) / 32u) return;
+    const uint32_t now = bits[w];
+    uint32_t diff = now ^ prev[w];
+    if (diff == 0) return;
+    __syncwarp();
+    if (lane == 0) prev[w] = now;
+    while (diff) {
+        const uint32_t b = (uint32_t)__ffs((int)diff) - 1u;
+        diff &= diff - 1u;
+        const uint32_t cell = w * 32u + b;
+        if (cell >= n_cells) break;
+        const uint32_t delta = ((now >> b) & 1u) ? 1u : 0xFFFFFFFFu;  // joined the excluded set : left it
+        const uint64_t e = row_ptr[cell + 1];
+        for (uint64_t i = row_ptr[cell] + lane; i < e; i += 32) {
+            const RowEntry x = csr[i];
+            const uint32_t n = (uint32_t)x.ref + (uint32_t)x.alt;
+            const uint32_t cls = (n - 1u) < (uint32_t)K_LIGHT ? (uint32_t)tab_slot((int)x.alt, (int)n) : (uint32_t)CLS_OTHER;
+            atomicAdd(&cls_min[(size_t)x.locus * CLS_STRIDE + cls], delta);
+        }
+    }
+}
+
+// One thread per locus: the sums from the class counts, the heavy entries of the column appended in column order, the
+// outputs of k_columns (same arrays, same meaning) and, on one GPU, the -80 locus filter (main.rs:431-451).
+template <bool FUSE_FILTER>
+__global__ void __launch_bounds__(256) k_locus_finish(const uint32_t* __restrict__ cls_all, const uint32_t* __restrict__ cls_min,
+                                                      uint32_t n_loci, const double* __restrict__ tab, uint8_t* __restrict__ used,
+                                                      const uint32_t* __restrict__ excl_bits,
+                                                      const uint32_t* __restrict__ hc_col_ptr, const uint32_t* __restrict__ hc_perm,
+                                                      const uint32_t* __restrict__ h_cell, const uint32_t* __restrict__ h_ref,
+                                                      const uint32_t* __restrict__ h_alt, const double* __restrict__ hv_ll,
+                                                      const ColEntry* __restrict__ csc, const uint64_t* __restrict__ col_ptr,
+                                                      double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int,
+                                                      uint32_t* __restrict__ n_used, DeviceStats* __restrict__ st) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    bool filtered = false, in_use = false;
+    if (l < n_loci) {
+        uint32_t ca[CLS_STRIDE], cm[CLS_STRIDE];
+#pragma unroll
+        for (int q = 0; q < CLS_STRIDE / 4; ++q) {
+            const uint4 a = __ldg(reinterpret_cast<const uint4*>(cls_all + (size_t)l * CLS_STRIDE) + q);
+            const uint4 m = __ldg(reinterpret_cast<const uint4*>(cls_min + (size_t)l * CLS_STRIDE) + q);
+            ca[4 * q] = a.x; ca[4 * q + 1] = a.y; ca[4 * q + 2] = a.z; ca[4 * q + 3] = a.w;
+            cm[4 * q] = m.x; cm[4 * q + 1] = m.y; cm[4 * q + 2] = m.z; cm[4 * q + 3] = m.w;
+        }
+        const double* rec = tab + (size_t)l * TAB_STRIDE;
+        double s_min = 0.0, s_maj = 0.0;
+        unsigned long long c_min = cm[CLS_OTHER], c_maj = ca[CLS_OTHER] - cm[CLS_OTHER];
+        unsigned long long R_min = 0, A_min = 0, R_maj = 0, A_maj = 0;
+#pragma unroll
+        for (int n = 1; n <= K_LIGHT; ++n) {
+#pragma unroll
+            for (int a = 0; a <= n; ++a) {
+                const int k = tab_slot(a, n);
+                const uint32_t mi = cm[k], mj = ca[k] - cm[k];
+                const double v = __ldg(rec + tab_idx_T(a, n));
+                if (mi) s_min += (double)mi * v;  // a class nobody is in never touches its value
+                if (mj) s_maj += (double)mj * v;
+                c_min += mi;
+                c_maj += mj;
+                R_min += (unsigned long long)mi * (unsigned)(n - a);
+                A_min += (unsigned long long)mi * (unsigned)a;
+                R_maj += (unsigned long long)mj * (unsigned)(n - a);
+                A_maj += (unsigned long long)mj * (unsigned)a;
+            }
+        }
+        const uint32_t hb = hc_col_ptr[l], he = hc_col_ptr[l + 1];
+        for (uint32_t j = hb; j < he; ++j) {
+            const uint32_t h = hc_perm[j];
+            const uint32_t c = h_cell[h];
+            const bool ex = (excl_bits[c >> 5] >> (c & 31)) & 1u;
+            const double v = hv_ll[h];
+            if (ex) { s_min += v; R_min += h_ref[h]; A_min += h_alt[h]; }
+            else    { s_maj += v; R_maj += h_ref[h]; A_maj += h_alt[h]; }
+        }
+        const bool on = used[l] != 0;  // entries were scored only if the locus was in use (main.rs:556)
+        const size_t L = n_loci;
+        loc_ll[l] = on ? s_min : 0.0;
+        loc_ll[L + l] = on ? s_maj : 0.0;
+        loc_int[0 * L + l] = on ? c_min : 0;
+        loc_int[1 * L + l] = on ? c_maj : 0;
+        loc_int[2 * L + l] = on ? R_min : 0;
+        loc_int[3 * L + l] = on ? A_min : 0;
+        loc_int[4 * L + l] = on ? R_maj : 0;
+        loc_int[5 * L + l] = on ? A_maj : 0;
+        loc_int[6 * L + l] = R_min;  // init_alpha_betas subtracts every stored entry of an excluded cell (main.rs:603-608)
+        loc_int[7 * L + l] = A_min;
+        if (FUSE_FILTER) {  // main.rs:431-451 on this locus
+            const double per_cell = (on && c_min != 0) ? s_min / (double)c_min : 0.0;
+            if (per_cell < -80.0) {
+                filtered = on;
+                used[l] = 0;
+                if (on)  // rare: the cells of the locus stop counting it (loci_used_per_cell, main.rs:575)
+                    for (uint64_t i = col_ptr[l]; i < col_ptr[l + 1]; ++i) atomicSub(&n_used[csc[i].cell], 1u);
+            } else {
+                in_use = on;
+            }
+        }
+    }
+    if (FUSE_FILTER) {
+        const uint32_t f = __popc(__ballot_sync(0xffffffffu, filtered)), u = __popc(__ballot_sync(0xffffffffu, in_use));
+        if ((threadIdx.x & 31) == 0) {
+            if (f) atomicAdd(&st->n_loci_filtered, (unsigned long long)f);
+            if (u) atomicAdd(&st->n_loci_in_use, (unsigned long long)u);
+        }
+    }
+}
+
 // The -80 rule (main.rs:431-451): per-cell minority log likelihood of the locus below -80 switches it off.
 __global__ void __launch_bounds__(256) k_locus_filter(const double* __restrict__ loc_ll,
                                                       const unsigned long long* __restrict__ loc_int, uint32_t n_loci,

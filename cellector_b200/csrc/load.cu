@@ -84,7 +84,8 @@ __global__ void k_pack_csr(const uint32_t* __restrict__ csr_src, const uint32_t*
                            const uint32_t* __restrict__ ref, const uint32_t* __restrict__ alt,
                            const uint32_t* __restrict__ used_idx, uint64_t nnz, RowEntry* __restrict__ csr,
                            uint32_t* __restrict__ keys2, uint32_t* __restrict__ vals2, uint8_t* __restrict__ heavy,
-                           uint32_t* __restrict__ col_cnt, unsigned long long* __restrict__ locus_tot) {
+                           uint32_t* __restrict__ col_cnt, unsigned long long* __restrict__ locus_tot,
+                           uint32_t* __restrict__ cls_all) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < nnz; i += (uint64_t)gridDim.x * blockDim.x) {
         const uint32_t src = csr_src[i];
         const uint32_t l = used_idx[locus[src]];
@@ -99,6 +100,8 @@ __global__ void k_pack_csr(const uint32_t* __restrict__ csr_src, const uint32_t*
         vals2[i] = (uint32_t)i;
         heavy[i] = hv ? 1 : 0;
         atomicAdd(&col_cnt[l], 1u);
+        const uint32_t n = e.ref + e.alt;  // clipped counts: anything above K_LIGHT stays above it
+        atomicAdd(&cls_all[(size_t)l * CLS_STRIDE + ((n - 1u) < (uint32_t)K_LIGHT ? (uint32_t)tab_slot((int)e.alt, (int)n) : (uint32_t)CLS_OTHER)], 1u);
         if (r) atomicAdd(&locus_tot[2 * (size_t)l], (unsigned long long)r);
         if (a) atomicAdd(&locus_tot[2 * (size_t)l + 1], (unsigned long long)a);
     }
@@ -330,12 +333,14 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     CLX_CUDA(c, c->locus_tot.alloc(2 * (size_t)n_loci + 2));
     CLX_CUDA(c, cudaMemsetAsync(col_cnt.p, 0, col_cnt.bytes(), s));
     CLX_CUDA(c, cudaMemsetAsync(c->locus_tot.p, 0, c->locus_tot.bytes(), s));
+    CLX_CUDA(c, c->cls_all.alloc(((size_t)n_loci + 1) * CLS_STRIDE));
+    CLX_CUDA(c, cudaMemsetAsync(c->cls_all.p, 0, c->cls_all.bytes(), s));
     CLX_CUDA(c, c->col_ptr.alloc((size_t)n_loci + 1));
     CLX_CUDA(c, c->csc.alloc((size_t)nnz + 2));
     if (nnz) {
         // keys / keys_sorted are reused as the locus keys of the second sort
         k_pack_csr<<<grid_for(nnz), TPB, 0, s>>>(csr_src.p, d_locus.p, d_ref.p, d_alt.p, used_idx.p, nnz, c->csr.p, keys.p,
-                                                 vals2.p, heavy.p, col_cnt.p, c->locus_tot.p);
+                                                 vals2.p, heavy.p, col_cnt.p, c->locus_tot.p, c->cls_all.p);
         c->launches++;
         // tiled scoring layout: keys_sorted still holds the cell of every CSR entry here
         CLX_TRY(build_tiled(c, keys_sorted.p));

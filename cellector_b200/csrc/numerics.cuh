@@ -41,6 +41,8 @@ CLX_HD int lbc_idx(int a, int n) { return (n * (n + 1)) / 2 + a; }
 // of a staged tile is the all-zero slot padding entries point at.  In the posterior pass the same slots carry
 // {T_minority, T_majority} (pass 0) and {T_doublet, 0} (pass 1).
 constexpr int TILE_L = 512;                          // loci per table tile
+constexpr int CLS_STRIDE = 12;                        // per-locus entry-class counters: 9 light (a | n) classes,
+constexpr int CLS_OTHER = 9;                          // [9] = entries without a memoised value (total 0 or heavy), 2 pads
 constexpr int TAB_SLOTS = 9;                         // (a | n) pairs with n <= K_LIGHT
 constexpr int TILE_SLOTS = TILE_L * TAB_SLOTS;       // 4608 slots = 73,728 bytes of shared memory per tile
 CLX_HD int tab_slot(int a, int n) { return (n * (n + 1)) / 2 - 1 + a; }

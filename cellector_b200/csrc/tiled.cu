@@ -675,11 +675,12 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     // the runs of a group have equal lengths) but enough (cell block, tile) units to fill the SMs
     c->tl_nT = L ? (L + TILE_L - 1) / TILE_L : 1;
     {
-        uint32_t W = 16;
+        uint32_t W;
         const char* env_w = getenv("CLX_TILED_W");
         uint32_t pc = N ? (N + NB_MAX - 1) / NB_MAX : 1;
-        // at least ~2 (cell block, tile) units per SM, so that the one-item-per-SM split has something to balance
-        const uint32_t want = (2u * (uint32_t)c->sm_count + c->tl_nT - 1) / c->tl_nT;
+        // about 1.5 (cell block, tile) units per SM, so that the one-item-per-SM split has something to balance; more cell
+        // blocks than that only re-read the table tiles (C2: 4 blocks of 3072 cells 25.9 us, 5 of 2048 31.9 us)
+        const uint32_t want = (3u * (uint32_t)c->sm_count + 2u * c->tl_nT - 1) / (2u * c->tl_nT);
         const uint32_t pc_cap = N ? std::max<uint32_t>(1u, N / 512u) : 1u;
         pc = std::max(pc, std::min(want, pc_cap));
         const char* env = getenv("CLX_TILED_PC");
@@ -687,9 +688,12 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         uint32_t nb = N ? (N + pc - 1) / pc : 1;
         const char* env_nb = getenv("CLX_TILED_NB");  // experiments: force the cell-block size
         if (env_nb && *env_nb) nb = (uint32_t)atoi(env_nb);
-        if (nb < 2048) W = 8;  // small blocks: fewer warps keep the per-warp run pool (and the groups) large
+        // warps: as many as keep >= 64 cells (8 per accumulator class) in every warp's pool; 8 warps per scheduler hide
+        // the shared-memory latency that 4 do not (C3s: W=32 77 us, W=16 83-89 us)
+        W = nb > 1536 ? 32u : (nb > 768 ? 16u : 8u);
         if (env_w && *env_w) W = std::min<uint32_t>(W_MAX, std::max<uint32_t>(1u, (uint32_t)atoi(env_w)));
-        const uint32_t gran = 8u * W;  // Q = NB / W is a multiple of 8: accumulator bank groups follow q mod 8
+        // Q = NB / W is a multiple of 32: the 8 accumulator classes of a warp's pool hold whole groups of 4 runs
+        const uint32_t gran = 32u * W;
         nb = std::min<uint32_t>(NB_MAX, std::max<uint32_t>(gran, (nb + gran - 1) / gran * gran));
         c->tl_W = W;
         c->tl_NB = nb;

@@ -44,7 +44,7 @@ extern "C" {
 /* clx_create flags */
 #define CLX_FLAG_PROFILE 1u        /* record CUDA events around every kernel phase (clx_get_phase_ms) */
 #define CLX_FLAG_NO_EXPECTED 2u    /* skip the expected_log_likelihood diagnostic column (stats.rs:8-33) */
-#define CLX_FLAG_KERNEL_V0 4u      /* use the plain CSR/L2-gather scoring kernel instead of the tiled one */
+#define CLX_FLAG_KERNEL_V0 4u      /* plain CSR gather scoring kernel + CSC column walk instead of the run stream + class counts */
 #define CLX_FLAG_KEEP_COO 8u       /* keep the unfiltered COO on the device (needed by clx_final_locus_counts) */
 #define CLX_FLAG_NO_GRAPH 16u      /* enqueue the kernels of an iteration one by one instead of replaying a CUDA graph */
 
