@@ -441,7 +441,7 @@ def run_large(args, dd, lib, name, rank, world, local_rank, balanced=True, slice
     n_loci_used, nnz_used = ctx.load_cell_data_ptrs(d.locus.data_ptr(), d.cell.data_ptr(), d.ref.data_ptr(), d.alt.data_ptr(),
                                                     d.nnz, d.n_loci, d.n_cells)
     load_s = time.perf_counter() - t0
-    sl = sd.to_host(d, 0, min(d.n_cells, args.slice_cells)) if (slice_parity and rank == 0) else None
+    sl = sd.to_host(d, 0, min(d.n_cells, args.slice_cells)) if (slice_parity and rank == 0 and args.slice_cells > 0) else None
     n_local, nnz0_local = d.n_cells, d.nnz
     del d
     torch.cuda.empty_cache()

@@ -131,11 +131,11 @@ struct clx_ctx {
     uint64_t tl_n_light = 0, tl_stream_chunks = 0;    // light entries; stream length in 512-byte warp chunks
     uint64_t tl_stream_steps = 0;                     // lookup steps x 32 lanes of one pass (padding included)
     clx::DevBuf<uint4> tl_stream;                     // [tl_stream_chunks][32] one 16-byte piece (8 words) per lane
-    clx::DevBuf<uint4> tl_item_q;                     // [n_items] work queue, largest first: cell block, first tile, n tiles, item id
-    clx::DevBuf<uint2> tl_item_rng;                   // [n_items][W] per queue slot and warp: first chunk, end chunk
-    uint32_t tl_grid = 0;                             // CTAs of k_score_runs (the first tl_grid queue slots are taken statically)
+    clx::DevBuf<uint4> tl_item_q;                     // [n_items] items in block-major order: cell block, first tile, n tiles, item id
+    clx::DevBuf<uint4> tl_item_rng;                   // [n_items][W] per item and warp: first chunk, end chunk, leading tiles to skip
+    uint32_t tl_grid = 0;                             // CTAs of k_score_runs (one per SM)
     clx::DevBuf<uint32_t> tl_cb_item;                 // [Pc + 1] first item of every cell block
-    clx::DevBuf<uint32_t> tl_counter;                 // [1] work-queue cursor (k_score_finish re-arms it)
+    clx::DevBuf<uint32_t> tl_cta_first;               // [tl_grid + 1] first item of every CTA (static, contiguous pieces of equal cost)
     clx::DevBuf<double> tl_part;                      // [n_items][NB][2] per-item partial sums of the two slot halves
     clx::DevBuf<double> tab16;                        // [2][nT * TILE_L][TAB_SLOTS][2] staged tables (pass 0 / pass 1)
     bool tl_attr_set = false;                         // dynamic shared-memory limit set on this context's device

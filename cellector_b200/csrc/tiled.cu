@@ -350,14 +350,18 @@ __global__ void __launch_bounds__(TPB) k_sub_fill(const uint32_t* __restrict__ s
     while (sink.pos != 0) sink.put(NULL_SLOT);
 }
 
-// per queue slot and warp: the warp's chunk range over the item's tiles (one consecutive range, see sub_unit_of)
-__global__ void k_item_rng(const uint4* __restrict__ item_q, uint32_t n_items, const uint32_t* __restrict__ chunk_off, uint32_t nT,
-                           uint32_t W, uint2* __restrict__ item_rng) {
+// per item and warp: the warp's chunk range over its tiles of the item (one consecutive range, see sub_unit_of) and how
+// many of the item's leading tiles it skips.  An item is a range of (tile, warp) sub-units of one cell block in tile-major
+// order: it starts at warp w_a of tile t_a and ends before warp w_e of tile t_e, so warp w owns the tiles
+// [t_a + (w < w_a), t_e + (w < w_e)).
+__global__ void k_item_rng(const uint4* __restrict__ item_q, const uint4* __restrict__ item_x, uint32_t n_items,
+                           const uint32_t* __restrict__ chunk_off, uint32_t nT, uint32_t W, uint4* __restrict__ item_rng) {
     const uint32_t q = blockIdx.x, w = threadIdx.x;
     if (q >= n_items || w >= W) return;
-    const uint4 it = item_q[q];
-    const size_t su0 = ((size_t)it.x * W + w) * nT + it.y;
-    item_rng[(size_t)q * W + w] = make_uint2(chunk_off[su0], chunk_off[su0 + it.z]);
+    const uint4 it = item_q[q], x = item_x[q];
+    const uint32_t first = it.y + (w < x.x ? 1u : 0u), end = max(first, x.y + (w < x.z ? 1u : 0u));
+    const size_t su0 = ((size_t)it.x * W + w) * nT;
+    item_rng[(size_t)q * W + w] = make_uint4(chunk_off[su0 + first], chunk_off[su0 + end], first - it.y, 0u);
 }
 
 }  // namespace
@@ -440,14 +444,13 @@ __device__ __noinline__ uint32_t enter_tile(unsigned char* smem, int k, uint32_t
 // Work queue: CTA b takes queue slot b first, later slots come from an atomic cursor that starts at gridDim.x; the
 // cursor for the NEXT item is fetched while the current one is being scored, so no item waits for the atomic.
 __global__ void __launch_bounds__(W_MAX * 32, 1)
-    k_score_runs(const uint4* __restrict__ stream, const uint4* __restrict__ item_q, const uint2* __restrict__ item_rng,
-                 uint32_t n_items, uint32_t* __restrict__ counter, const double* __restrict__ tab16, uint32_t NB,
+    k_score_runs(const uint4* __restrict__ stream, const uint4* __restrict__ item_q, const uint4* __restrict__ item_rng,
+                 const uint32_t* __restrict__ cta_first, const double* __restrict__ tab16, uint32_t NB,
                  double* __restrict__ part) {
     extern __shared__ __align__(128) unsigned char smem[];
     double2* acc = reinterpret_cast<double2*>(smem + 2 * TB_BUF);
     uint64_t* tab_full = reinterpret_cast<uint64_t*>(smem + 2 * TB_BUF + TL_ACC_BYTES);
     unsigned int* tab_done = reinterpret_cast<unsigned int*>(tab_full + 2);  // [2] warps done with a buffer
-    uint32_t* s_next = reinterpret_cast<uint32_t*>(tab_done + 2);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t nw = blockDim.x >> 5;
     const uint32_t Q = NB / nw;  // cells per warp (NB is a multiple of 8 * nw)
@@ -464,12 +467,10 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
     __syncthreads();
     uint32_t g_tile = 0;  // tiles consumed by this CTA so far (buffer = g & 1, parity = (g >> 1) & 1)
     double2* const my_acc = acc + (size_t)w * Q;
-    uint32_t qk = blockIdx.x;
-    while (qk < n_items) {
-        uint32_t nxt = 0;
-        if (tid == 0) nxt = atomicAdd(counter, 1u);  // used at the end of this item
+    const uint32_t q_end = cta_first[blockIdx.x + 1];
+    for (uint32_t qk = cta_first[blockIdx.x]; qk < q_end; ++qk) {
         const uint4 it = item_q[qk];
-        const uint2 rng = item_rng[(size_t)qk * nw + w];
+        const uint4 rng = item_rng[(size_t)qk * nw + w];
         const uint32_t t0 = it.y, ntile = it.z, item = it.w;
         const uint4* p = stream + (size_t)rng.x * 32 + lane;
         const uint32_t n = rng.y - rng.x;
@@ -487,6 +488,10 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
         }
         int k = -1;                    // item-local tile this warp is in
         const double2* tab = nullptr;  // its staged slots
+        if (rng.z) {                   // the item's first tile belongs to the previous piece for this warp: pass through it
+            enter_tile(smem, k, g_tile, t0, ntile, nw, tab16);
+            ++k;
+        }
         double sT = 0.0, sE = 0.0;     // the lane's run
         uint4 cq = make_uint4(0u, 0u, 0u, 0u);  // accumulator indices of the lane's cells in the coming groups, 16 bits each
         // One chunk = 8 words per lane.  A cell chunk refills cq (and may announce the next tile).  In an entry chunk
@@ -557,8 +562,7 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
         }
         leave_tile(smem, (uint32_t)k, g_tile, t0, ntile, nw, tab16);
         g_tile += ntile;
-        if (tid == 0) *s_next = nxt;
-        __syncthreads();  // every warp has added its last run; the next queue slot is posted
+        __syncthreads();  // every warp has added its last run
         // partials out (cell_local = q * nw + warp lives in accumulator slot warp * Q + q), accumulators cleared
         double2* dst = reinterpret_cast<double2*>(part) + (size_t)item * NB;
         for (uint32_t i = tid; i < NB; i += blockDim.x) {
@@ -566,7 +570,6 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
             dst[i] = acc[slot];
             acc[slot] = make_double2(0.0, 0.0);
         }
-        qk = *s_next;
         __syncthreads();
     }
 }
@@ -584,9 +587,7 @@ __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__
                                                       const double* __restrict__ hv0, const double* __restrict__ hv1,
                                                       const uint32_t* __restrict__ n_used, double* __restrict__ out0,
                                                       double* __restrict__ out1, uint32_t* __restrict__ nloci,
-                                                      double* __restrict__ norm, unsigned int* __restrict__ nan_flag,
-                                                      uint32_t* __restrict__ queue_counter, uint32_t first_round) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) *queue_counter = first_round;  // re-arm the work queue of k_score_runs
+                                                      double* __restrict__ norm, unsigned int* __restrict__ nan_flag) {
     // lanes 0..3 of a warp take cells c0..c0+3 for sub 0, lanes 4..7 the same cells for sub 1, ...: partial loads of one
     // sub are 4 consecutive double2 (64 B)
     const uint32_t warp_cell0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / FIN_LANES);
@@ -639,8 +640,8 @@ int score_tiled(clx_ctx* c, ScoreMode mode) {
     }
     const double* tab = c->tab16.p + (mode == SCORE_POST_C ? (size_t)c->tl_nT * TILE_SLOTS * 2 : 0);
     if (c->tl_n_items) {
-        k_score_runs<<<c->tl_grid, c->tl_W * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_item_q.p, c->tl_item_rng.p, c->tl_n_items,
-                                                              c->tl_counter.p, tab, c->tl_NB, c->tl_part.p);
+        k_score_runs<<<c->tl_grid, c->tl_W * 32, TL_SMEM, s>>>(c->tl_stream.p, c->tl_item_q.p, c->tl_item_rng.p, c->tl_cta_first.p, tab,
+                                                              c->tl_NB, c->tl_part.p);
         c->launches++;
         CLX_DEBUG_SYNC(c, "k_score_runs");
     }
@@ -648,16 +649,14 @@ int score_tiled(clx_ctx* c, ScoreMode mode) {
     const unsigned fgrid = (unsigned)(((uint64_t)N * FIN_LANES + 255) / 256);
     if (mode == SCORE_EM)
         k_score_finish<SCORE_EM><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p,
-                                                      c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag,
-                                                      c->tl_counter.p, c->tl_grid);
+                                                      c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag);
     else if (mode == SCORE_POST_AB)
         k_score_finish<SCORE_POST_AB><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p,
                                                            c->hv_ll.p + nh, nullptr, c->post_ll.p, c->post_ll.p + N, nullptr, nullptr,
-                                                           nullptr, c->tl_counter.p, c->tl_grid);
+                                                           nullptr);
     else
         k_score_finish<SCORE_POST_C><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p + 2 * nh,
-                                                          nullptr, nullptr, c->post_ll.p + 2 * (size_t)N, nullptr, nullptr, nullptr, nullptr,
-                                                          c->tl_counter.p, c->tl_grid);
+                                                          nullptr, nullptr, c->post_ll.p + 2 * (size_t)N, nullptr, nullptr, nullptr, nullptr);
     c->launches++;
     return CLX_OK;
 }
@@ -811,68 +810,74 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         c->launches++;
     }
 
-    const char* env_it = getenv("CLX_TILED_ITEMS_PER_SM");
-    const int env_items = env_it && *env_it ? std::max(1, atoi(env_it)) : 1;
-    // ---- work items: every cell block gets a share of (items per SM x SMs) items proportional to its chunks; its tiles are cut
-    //      into that many consecutive ranges of about equal chunk counts
+    // ---- work items: the (cell block, tile, warp) sub-units in that order are one sequence of costs (a unit's chunks
+    //      spread evenly over its warps: cells are dealt to warps round-robin); it is cut into one contiguous piece of equal
+    //      cost per SM, and a piece that crosses cell-block boundaries becomes one item per block (same CTA, one after the
+    //      other).  Static: no queue, every launch does the same work on the same CTA.  A piece boundary inside a tile
+    //      gives the tile's first warps to one CTA and the rest to the next (both stage the tile).
     {
-        std::vector<uint32_t> items, cb_item;
-        std::vector<unsigned long long> item_cost;
+        std::vector<uint4> queue, extra;  // {cell block, first tile, n tiles, item id} / {w_a, t_e, w_e, 0}
+        std::vector<uint32_t> cb_item(c->tl_Pc + 1, 0), cta_first;
         unsigned long long cost_total = 0;
         for (uint32_t u = 0; u < n_units; ++u) cost_total += h_unit[u];
-        const uint64_t total_items = std::max<uint64_t>(1, (uint64_t)env_items * (uint64_t)c->sm_count);
-        for (uint32_t cb = 0; cb < c->tl_Pc; ++cb) {
-            cb_item.push_back((uint32_t)(items.size() / 4));
-            const unsigned long long* ue = h_unit.data() + (size_t)cb * c->tl_nT;
-            unsigned long long cb_total = 0;
-            for (uint32_t t = 0; t < c->tl_nT; ++t) cb_total += ue[t];
-            if (cb_total == 0) continue;
-            uint64_t want = cost_total ? (cb_total * total_items + cost_total / 2) / cost_total : 1;
-            want = std::max<uint64_t>(1, std::min<uint64_t>(want, c->tl_nT));
-            unsigned long long acc = 0;
-            uint32_t t0 = 0;
-            for (uint64_t j = 1; j <= want && t0 < c->tl_nT; ++j) {
-                const unsigned long long goal = cb_total * j / want;
-                uint32_t t1 = t0;
-                while (t1 < c->tl_nT && (acc < goal || t1 == t0)) acc += ue[t1++];
-                if (j == want) {
-                    while (t1 < c->tl_nT) acc += ue[t1++];
-                }
-                unsigned long long in_range = 0;
-                for (uint32_t t = t0; t < t1; ++t) in_range += ue[t];
-                if (in_range) {
-                    items.push_back(cb);
-                    items.push_back(t0);
-                    items.push_back(t1);
-                    items.push_back(0);
-                    item_cost.push_back(in_range);
-                }
-                t0 = t1;
+        const uint32_t G = (uint32_t)std::max(1, c->sm_count);
+        const uint64_t S = (uint64_t)n_units * W, per_block = (uint64_t)c->tl_nT * W;
+        std::vector<uint64_t> cut(G + 1, S);
+        cut[0] = 0;
+        {
+            unsigned long long run = 0;
+            uint32_t u = 0;
+            for (uint32_t g = 1; g < G; ++g) {
+                const long double target = (long double)cost_total * g / G;
+                while (u < n_units && (long double)(run + h_unit[u]) <= target) run += h_unit[u++];
+                if (u >= n_units) break;  // the remaining cuts stay at S
+                const long double f = h_unit[u] ? (target - (long double)run) / (long double)h_unit[u] : 0.0L;
+                cut[g] = (uint64_t)u * W + std::min<uint64_t>(W, (uint64_t)(f * W + 0.5L));
+            }
+            for (uint32_t g = 1; g <= G; ++g) cut[g] = std::max(cut[g], cut[g - 1]);
+        }
+        cta_first.assign(G + 1, 0);
+        for (uint32_t g = 0; g < G; ++g) {
+            cta_first[g] = (uint32_t)queue.size();
+            uint64_t sa = cut[g];
+            const uint64_t sb = cut[g + 1];
+            while (sa < sb) {
+                const uint32_t cb = (uint32_t)(sa / per_block);
+                const uint64_t base = (uint64_t)cb * per_block, se = std::min(sb, base + per_block);
+                const uint32_t t_a = (uint32_t)((sa - base) / W), w_a = (uint32_t)((sa - base) % W);
+                const uint32_t t_e = (uint32_t)((se - base) / W), w_e = (uint32_t)((se - base) % W);
+                const uint32_t t_hi = t_e + (w_e ? 1u : 0u);
+                queue.push_back(make_uint4(cb, t_a, t_hi - t_a, (uint32_t)queue.size()));
+                extra.push_back(make_uint4(w_a, t_e, w_e, 0u));
+                sa = se;
             }
         }
-        cb_item.push_back((uint32_t)(items.size() / 4));
-        c->tl_n_items = (uint32_t)(items.size() / 4);
-        c->tl_grid = std::min<uint32_t>(c->tl_n_items, (uint32_t)c->sm_count);
+        cta_first[G] = (uint32_t)queue.size();
+        c->tl_n_items = (uint32_t)queue.size();
+        {   // first item of every cell block (items are in block-major order)
+            uint32_t q = 0;
+            for (uint32_t cb = 0; cb <= c->tl_Pc; ++cb) {
+                while (q < c->tl_n_items && queue[q].x < cb) ++q;
+                cb_item[cb] = q;
+            }
+        }
+        c->tl_grid = c->tl_n_items ? G : 0;
+        DevBuf<uint4> item_x;
         CLX_CUDA(c, c->tl_item_q.alloc((size_t)c->tl_n_items + 1));
+        CLX_CUDA(c, item_x.alloc((size_t)c->tl_n_items + 1));
         CLX_CUDA(c, c->tl_item_rng.alloc((size_t)c->tl_n_items * W + 1));
         CLX_CUDA(c, c->tl_cb_item.alloc(cb_item.size()));
-        std::vector<uint32_t> order(c->tl_n_items);
-        for (uint32_t i = 0; i < c->tl_n_items; ++i) order[i] = i;
-        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_cost[a] > item_cost[b]; });
-        std::vector<uint4> queue(c->tl_n_items);  // largest first
-        for (uint32_t q = 0; q < c->tl_n_items; ++q) {
-            const uint32_t i = order[q];
-            queue[q] = make_uint4(items[4 * i], items[4 * i + 1], items[4 * i + 2] - items[4 * i + 1], i);
-        }
-        CLX_CUDA(c, c->tl_counter.alloc(1));
-        CLX_CUDA(c, cudaMemcpyAsync(c->tl_counter.p, &c->tl_grid, 4, cudaMemcpyHostToDevice, s));
+        CLX_CUDA(c, c->tl_cta_first.alloc(cta_first.size()));
+        CLX_CUDA(c, cudaMemcpyAsync(c->tl_cta_first.p, cta_first.data(), cta_first.size() * 4, cudaMemcpyHostToDevice, s));
         if (!queue.empty()) {
             CLX_CUDA(c, cudaMemcpyAsync(c->tl_item_q.p, queue.data(), queue.size() * sizeof(uint4), cudaMemcpyHostToDevice, s));
-            k_item_rng<<<c->tl_n_items, W, 0, s>>>(c->tl_item_q.p, c->tl_n_items, chunk_off.p, c->tl_nT, W, c->tl_item_rng.p);
+            CLX_CUDA(c, cudaMemcpyAsync(item_x.p, extra.data(), extra.size() * sizeof(uint4), cudaMemcpyHostToDevice, s));
+            k_item_rng<<<c->tl_n_items, W, 0, s>>>(c->tl_item_q.p, item_x.p, c->tl_n_items, chunk_off.p, c->tl_nT, W, c->tl_item_rng.p);
             c->launches++;
         }
         CLX_CUDA(c, cudaMemcpyAsync(c->tl_cb_item.p, cb_item.data(), cb_item.size() * 4, cudaMemcpyHostToDevice, s));
         CLX_CUDA(c, cudaStreamSynchronize(s));  // the host vectors above go out of scope
+        if (getenv("CLX_TILED_STATS")) fprintf(stderr, "[clx] run stream: %u items on %u CTAs\n", c->tl_n_items, G);
     }
     CLX_CUDA(c, c->tl_part.alloc((size_t)c->tl_n_items * c->tl_NB * 2 + 2));
     CLX_CUDA(c, c->tab16.alloc(2ull * c->tl_nT * TILE_SLOTS * 2 + 2));

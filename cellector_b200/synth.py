@@ -43,6 +43,9 @@ CONFIGS = {
     "C3": SynthConfig(n_cells=100_000, n_loci=500_000, density=0.01, minority_frac=0.05),
     # one rank's share of C3 on 8 GPUs (12.5k cells x all 500k loci): the per-GPU shape of the sharded run
     "C3s": SynthConfig(n_cells=12_500, n_loci=500_000, density=0.01, minority_frac=0.05),
+    # halves and quarters of C3's cells (diagnostics of the sharded shapes on one GPU)
+    "C3h": SynthConfig(n_cells=50_000, n_loci=500_000, density=0.01, minority_frac=0.05),
+    "C3q": SynthConfig(n_cells=25_000, n_loci=500_000, density=0.01, minority_frac=0.05),
     "C4": SynthConfig(n_cells=1_000_000, n_loci=1_000_000, density=0.005, minority_frac=0.05),
     "C5": SynthConfig(n_cells=200_000, n_loci=2_000_000, density=0.0005, minority_frac=0.05, row_sigma=2.0),
 }
