@@ -331,6 +331,17 @@ def measure(ctx, dd, args, local_rank, n_local, L, nnz_used, nnz_total, collecti
             "ms_per_step_with_phase_events": mx(sum(dev_ms_prof) / len(dev_ms_prof))}
 
 
+def apply_traffic(roofline, name):
+    """roofline.traffic = DRAM bytes of one scoring launch from the committed ncu capture of this workload (profiles/)."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "score_kernel_traffic.json")))["records"].get(name)
+    except Exception:
+        rec = None
+    if rec:
+        roofline["traffic"] = rec.get("dram_bytes_per_launch")
+        roofline["traffic_source"] = rec.get("source")
+
+
 def _max_rel(a, b):
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     if a.size == 0:
@@ -470,6 +481,8 @@ def run_large(args, dd, lib, name, rank, world, local_rank, balanced=True, slice
                      "score_us_max_over_mean": max(p["score_us"] for p in per_rank) / (sum(p["score_us"] for p in per_rank) / world),
                      "per_rank": per_rank}
     ctx.close()
+    if world == 1:
+        apply_traffic(m["roofline"], name)
     out = dict(m)
     out.update({"name": name, "n_gpus": world, "nnz_scored_total": int(nnz_total), "loci_used": int(n_loci_used), "nnz0_local": int(nnz0_local),
                 "generate_s": gen_s, "load_s": load_s, "properties": props, "imbalance": imbalance, "cfg": cfg, "balanced": balanced})
@@ -606,13 +619,7 @@ def main():
         ctx = Cellector(local_rank, args.flags, lib)
         n_loci_used, nnz_used = ctx.load_cell_data(*host, data.n_loci, data.n_cells)
         m = measure(ctx, dd, args, local_rank, data.n_cells, n_loci_used, nnz_used, float(nnz_used))
-        try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "score_kernel_traffic.json")))
-            if tj.get("workload") == name:
-                m["roofline"]["traffic"] = tj.get("dram_bytes_per_launch")
-                m["roofline"]["traffic_source"] = tj.get("source")
-        except Exception:
-            pass
+        apply_traffic(m["roofline"], name)
         e2e = None if args.no_e2e else e2e_job(args, dd, ctx, data, host, float(nnz_used))
         cpu, par = (None, None) if args.no_cpu_baseline else cpu_baseline_and_parity(args, ctx, data)
         ctx.close()
