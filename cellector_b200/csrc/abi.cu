@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include <new>
+#include <time.h>
 
 #include <nvtx3/nvToolsExt.h>  // header-only NVTX v3: ranges show up in Nsight Systems / ncu --nvtx, cost nothing otherwise
 
@@ -37,6 +38,25 @@ static cudaEvent_t get_event(clx_ctx* c) {
 }
 
 static const char* const kPhaseName[CLX_PHASE_COUNT] = {"clx:tables", "clx:score", "clx:heavy", "clx:select", "clx:column", "clx:comm"};
+
+static double wall_ms() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return 1e3 * (double)ts.tv_sec + 1e-6 * (double)ts.tv_nsec;
+}
+StageClock::StageClock(cudaStream_t st, const char* w) : s(st), on(getenv("CLX_LOAD_TIMING") != nullptr), t0(0.0), what(w) {
+    if (on) {
+        cudaStreamSynchronize(s);
+        t0 = wall_ms();
+    }
+}
+void StageClock::mark(const char* stage) {
+    if (!on) return;
+    cudaStreamSynchronize(s);
+    const double t = wall_ms();
+    fprintf(stderr, "[clx] %s: %-28s %8.3f ms\n", what, stage, t - t0);
+    t0 = t;
+}
 
 NvtxRange::NvtxRange(const char* name) { nvtxRangePushA(name); }
 NvtxRange::~NvtxRange() { nvtxRangePop(); }

@@ -219,6 +219,16 @@ int fail(clx_ctx* c, int code, const std::string& msg);
     } while (0)
 
 // NVTX range for the lifetime of the object (load stages, one EM iteration, the posterior pass)
+// CLX_LOAD_TIMING=1: wall-clock of the load stages (a stream sync at every mark: diagnostics only)
+struct StageClock {
+    cudaStream_t s;
+    bool on;
+    double t0;
+    const char* what;
+    StageClock(cudaStream_t st, const char* w);
+    void mark(const char* stage);
+};
+
 struct NvtxRange {
     explicit NvtxRange(const char* name);
     ~NvtxRange();

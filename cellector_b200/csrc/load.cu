@@ -195,6 +195,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
              const uint32_t* cell, const uint32_t* ref, const uint32_t* alt, uint32_t min_ref, uint32_t min_alt) {
     NvtxRange nvtx("clx:load_coo");
     cudaStream_t s = c->stream;
+    StageClock clk(s, "load");
     c->loaded = false;
     // every cub call below takes a 32-bit signed item count
     if (nnz0 >= 0x7FFFFFFFull) return fail(c, CLX_ERR_ARG, "more than 2^31-2 nonzeros per GPU: shard the cells over more ranks");
@@ -241,6 +242,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         }
     }
 
+    clk.mark("COO to device");
     // ---- pass 1: locus filter
     DevBuf<unsigned int> cnt, err;
     DevBuf<uint32_t> flag, used_idx;
@@ -280,6 +282,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         c->launches++;
     }
 
+    clk.mark("locus filter");
     // ---- compaction of the kept nonzeros (file order preserved)
     DevBuf<uint32_t> kept_idx, n_sel;
     CLX_CUDA(c, kept_idx.alloc(nnz0));
@@ -297,6 +300,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     }
     c->nnz = nnz;
 
+    clk.mark("compaction");
     // ---- CSR: stable sort by cell
     DevBuf<uint32_t> keys, keys_sorted, csr_src, row_cnt;
     CLX_CUDA(c, keys.alloc(nnz));
@@ -322,6 +326,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         c->launches += 2;
     }
 
+    clk.mark("CSR sort");
     // ---- pack CSR, locus totals, CSC keys
     DevBuf<uint8_t> heavy;
     DevBuf<uint32_t> col_cnt, vals2, csc_src;
@@ -342,8 +347,10 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         k_pack_csr<<<grid_for(nnz), TPB, 0, s>>>(csr_src.p, d_locus.p, d_ref.p, d_alt.p, used_idx.p, nnz, c->csr.p, keys.p,
                                                  vals2.p, heavy.p, col_cnt.p, c->locus_tot.p, c->cls_all.p);
         c->launches++;
+        clk.mark("pack CSR");
         // tiled scoring layout: keys_sorted still holds the cell of every CSR entry here
         CLX_TRY(build_tiled(c, keys_sorted.p));
+        clk.mark("run stream");
         const int eb = bits_for(n_loci);
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys_sorted.p, vals2.p, csc_src.p, (int)nnz, 0, eb, s));
         CLX_CUDA(c, tmp.alloc(tmp_bytes));
@@ -381,6 +388,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         c->launches++;
     }
 
+    clk.mark("CSC + ln_gamma memo");
     // ---- heavy side lists
     DevBuf<uint32_t> hpos, hcpos;
     CLX_CUDA(c, hpos.alloc(nnz));
@@ -444,7 +452,9 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         d_ref.release();
         d_alt.release();
     }
+    clk.mark("heavy lists");
     CLX_TRY(em_alloc(c));
+    clk.mark("EM buffers");
     c->loaded = true;
     return CLX_OK;
 }

@@ -32,6 +32,7 @@
 //     cell block in item order (fixed order: deterministic), appends the heavy values and normalises.
 #include <cub/cub.cuh>
 #include <stdio.h>
+#include <string.h>
 
 #include <algorithm>
 #include <vector>
@@ -103,6 +104,12 @@ __global__ void k_tile_keys(const RowEntry* __restrict__ csr, const uint32_t* __
     }
     for (int off = 16; off > 0; off >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, off);
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(n_light, mine);
+}
+
+// stored entries per cell (the start value of loci_used_per_cell) when the run stream is not built
+__global__ void k_row_len(const uint64_t* __restrict__ row_ptr, uint32_t n_cells, uint32_t* __restrict__ row_len) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_cells) row_len[i] = (uint32_t)(row_ptr[i + 1] - row_ptr[i]);
 }
 
 struct DropBank {  // run key of an entry key
@@ -664,6 +671,7 @@ int score_tiled(clx_ctx* c, ScoreMode mode) {
 int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     NvtxRange nvtx("clx:build_run_stream");
     cudaStream_t s = c->stream;
+    StageClock clk(s, "  run stream");
     c->tiled_ready = false;
     const uint32_t N = c->n_cells, L = c->n_loci;
     const uint64_t nnz = c->nnz;
@@ -700,6 +708,31 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     }
     const uint32_t W = c->tl_W;
     c->tl_n_units = c->tl_Pc * c->tl_nT;
+    {
+        // Very sparse matrices: every (cell block, tile) unit stages a 72 KB table tile, an entry gathered straight from
+        // the per-locus records costs ~72 B (entry + two sectors).  Below ~1000 entries per unit the gather kernel
+        // (k_score_rows) moves fewer bytes; the run stream is then not built at all.  Small matrices (tables that stay in
+        // L2 anyway) always take the stream.  C5 (density 5e-4): 448 entries per unit, 8.0 ms per pass as a stream.
+        const uint64_t units = (uint64_t)c->tl_Pc * c->tl_nT;
+        bool gather = units * (uint64_t)TB_BYTES > (16ull << 20) && nnz < 1024ull * units;
+        const char* path = getenv("CLX_SCORE_PATH");  // "stream" / "gather": force one (tests, experiments)
+        if (path && !strcmp(path, "gather")) gather = true;
+        if (path && !strcmp(path, "stream")) gather = false;
+        if (gather) {
+            if (N) k_row_len<<<(N + TPB - 1) / TPB, TPB, 0, s>>>(c->row_ptr.p, N, c->row_len.p);
+            c->launches++;
+            c->tl_n_items = c->tl_n_units = c->tl_grid = 0;
+            c->tl_n_light = c->tl_stream_chunks = c->tl_stream_steps = 0;
+            c->tl_stream.release();
+            c->tl_part.release();
+            c->tab16.release();
+            if (getenv("CLX_TILED_STATS"))
+                fprintf(stderr, "[clx] gather scoring: N %u L %u, %.0f entries per (cell block, tile) unit\n", N, L,
+                        units ? (double)nnz / (double)units : 0.0);
+            CLX_CUDA(c, cudaGetLastError());
+            return CLX_OK;
+        }
+    }
     if ((uint64_t)c->tl_Pc * c->tl_nT >= (1ull << 31)) return fail(c, CLX_ERR_ARG, "too many (cell block, tile) units");
     const uint32_t n_units = c->tl_n_units;
 
@@ -734,6 +767,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         CLX_CUDA(c, cudaStreamSynchronize(s));
     }
     c->tl_n_light = n_light;
+    clk.mark("entry keys + sort");
     keys.release();
     vals.release();
     // ---- runs
@@ -751,6 +785,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     }
     keys_sorted.release();
     const uint32_t R = (uint32_t)n_runs;
+    clk.mark("runs (RLE)");
     const uint64_t n_sub = (uint64_t)n_units * W;
     if (n_sub >= (1ull << 28) - 2) return fail(c, CLX_ERR_ARG, "too many (cell block, tile, warp) sub-units");
     DevBuf<uint32_t> sub_run, n_chunks, chunk_off;
@@ -797,6 +832,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         if (sum >= (1ull << 32)) return fail(c, CLX_ERR_ARG, "run stream longer than 2^32 chunks (2 TB): shard the cells over more ranks");
     }
     c->tl_stream_chunks = total_chunks;
+    clk.mark("run sort + chunk counts");
     c->tl_stream_steps = h_steps * 32ull;
     if (getenv("CLX_TILED_STATS"))
         fprintf(stderr, "[clx] run stream: N %u L %u NB %u W %u Pc %u nT %u | light entries %llu runs %u | chunks %u (%.2f B/entry) lookup steps %llu (%.3f per entry)\n",
@@ -810,6 +846,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         c->launches++;
     }
 
+    clk.mark("stream fill");
     // ---- work items: the (cell block, tile, warp) sub-units in that order are one sequence of costs (a unit's chunks
     //      spread evenly over its warps: cells are dealt to warps round-robin); it is cut into one contiguous piece of equal
     //      cost per SM, and a piece that crosses cell-block boundaries becomes one item per block (same CTA, one after the
@@ -879,6 +916,7 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
         CLX_CUDA(c, cudaStreamSynchronize(s));  // the host vectors above go out of scope
         if (getenv("CLX_TILED_STATS")) fprintf(stderr, "[clx] run stream: %u items on %u CTAs\n", c->tl_n_items, G);
     }
+    clk.mark("work items");
     CLX_CUDA(c, c->tl_part.alloc((size_t)c->tl_n_items * c->tl_NB * 2 + 2));
     CLX_CUDA(c, c->tab16.alloc(2ull * c->tl_nT * TILE_SLOTS * 2 + 2));
     CLX_CUDA(c, cudaMemsetAsync(c->tab16.p, 0, c->tab16.bytes(), s));

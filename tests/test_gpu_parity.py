@@ -222,6 +222,28 @@ def test_parity_dense_tiles(libs, monkeypatch):
         run_parity(gpu, orc, synth.generate(cfg))
 
 
+def test_parity_gather_scoring_forced(libs, monkeypatch):
+    """CLX_SCORE_PATH=gather: the per-row gather kernel scores, the class-count column pass stays (the combination very
+    sparse matrices take by themselves)."""
+    monkeypatch.setenv("CLX_SCORE_PATH", "gather")
+    gpu, orc = _pair(libs)
+    with gpu, orc:
+        run_parity(gpu, orc, synth.generate(CASES["rescue_filter"]))
+
+
+def test_parity_very_sparse_takes_gather_scoring(libs, capfd, monkeypatch):
+    """Many cell blocks (forced small: 24 blocks of 256 cells) over ~60 locus tiles: ~100 MB of table staging per pass for
+    a few hundred entries per (cell block, tile) unit, so the load picks the gather kernel by itself (checked on the load
+    statistics line).  The shape of C5 (200 000 cells x 2 M loci at density 5e-4) in small."""
+    monkeypatch.setenv("CLX_TILED_STATS", "1")
+    monkeypatch.setenv("CLX_TILED_NB", "256")
+    gpu, orc = _pair(libs)
+    cfg = synth.SynthConfig(n_cells=6000, n_loci=100_000, density=0.002, minority_frac=0.06, seed=21)
+    with gpu, orc:
+        run_parity(gpu, orc, synth.generate(cfg))
+    assert "gather scoring" in capfd.readouterr().err
+
+
 def _worker(case, flags=0, env=None):
     import subprocess
     import sys
