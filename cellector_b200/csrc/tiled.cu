@@ -710,11 +710,12 @@ int build_tiled(clx_ctx* c, const uint32_t* d_cell_of_entry) {
     c->tl_n_units = c->tl_Pc * c->tl_nT;
     {
         // Very sparse matrices: every (cell block, tile) unit stages a 72 KB table tile, an entry gathered straight from
-        // the per-locus records costs ~72 B (entry + two sectors).  Below ~1000 entries per unit the gather kernel
+        // the per-locus records costs ~72 B (entry + two sectors).  Below one entry per cell and tile the runs degenerate
+        // to single entries, the 32-lane groups are mostly padding (C5: 10 lookup steps per entry) and the gather kernel
         // (k_score_rows) moves fewer bytes; the run stream is then not built at all.  Small matrices (tables that stay in
         // L2 anyway) always take the stream.  C5 (density 5e-4): 448 entries per unit, 8.0 ms per pass as a stream.
         const uint64_t units = (uint64_t)c->tl_Pc * c->tl_nT;
-        bool gather = units * (uint64_t)TB_BYTES > (16ull << 20) && nnz < 1024ull * units;
+        bool gather = units * (uint64_t)TB_BYTES > (16ull << 20) && nnz < 4096ull * units;
         const char* path = getenv("CLX_SCORE_PATH");  // "stream" / "gather": force one (tests, experiments)
         if (path && !strcmp(path, "gather")) gather = true;
         if (path && !strcmp(path, "stream")) gather = false;

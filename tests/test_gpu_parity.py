@@ -184,14 +184,17 @@ def test_packed_load_is_the_same_load(libs):
             assert np.array_equal(a[k], b[k]), k
 
 
-def test_gpu_against_committed_golden(libs):
-    """The CUDA path against tests/golden/oracle_c1_slice.json with no oracle in the loop: integers and the excluded
-    sets identical, fp64 sums and quantiles within 1e-9 relative."""
+@pytest.mark.parametrize("fixture", ["oracle_c1_slice.json", "oracle_c1.json", "oracle_c2.json"])
+def test_gpu_against_committed_golden(libs, fixture):
+    """The CUDA path against the committed oracle outputs with no oracle in the loop — a small deep case and BASELINE.json
+    configs[0] / configs[1] at full size: integers and the excluded sets identical, fp64 sums, sampled per-cell and
+    per-locus values and quantiles within 1e-9 relative."""
     import json
     import os
-    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "oracle_c1_slice.json")))
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", fixture)))
     d = synth.generate(synth.SynthConfig(**g["config"]))
     gpu, _ = _pair(libs)
+    close = lambda got, want: np.testing.assert_allclose(np.asarray(got, np.float64), np.asarray(want, np.float64), rtol=1e-9, atol=1e-12)
     with gpu:
         assert list(gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)) == g["loaded"]
         for want in g["iterations"]:
@@ -206,9 +209,33 @@ def test_gpu_against_committed_golden(libs):
             assert float(cv["expected_ll"].sum()) == pytest.approx(want["expected_ll_sum"], rel=1e-9)
             assert int(cv["n_loci"].sum()) == want["n_loci_sum"]
             assert np.flatnonzero(cv["excluded"]).tolist() == want["excluded"]
+            if "cell_idx" in want:
+                lv = gpu.locus_vectors()
+                close(cv["ll"][want["cell_idx"]], want["cell_ll"])
+                assert cv["n_loci"][want["cell_idx"]].astype(int).tolist() == want["cell_n_loci"]
+                close(lv["ll_minority"][want["locus_idx"]], want["locus_ll_minority"])
+                close(lv["ll_majority"][want["locus_idx"]], want["locus_ll_majority"])
+                assert float(lv["ll_minority"].sum()) == pytest.approx(want["locus_ll_minority_sum"], rel=1e-9, abs=1e-9)
+                assert float(lv["ll_majority"].sum()) == pytest.approx(want["locus_ll_majority_sum"], rel=1e-9)
+                assert int(lv["cells_minority"].astype(np.int64).sum()) == want["locus_cells_minority_sum"]
+                assert int(lv["cells_majority"].astype(np.int64).sum()) == want["locus_cells_majority_sum"]
         p = gpu.calculate_posteriors()
         assert np.bincount(p["label"], minlength=4).tolist() == g["label_counts"]
         assert float(p["ll_minor"].sum()) == pytest.approx(g["ll_minor_sum"], rel=1e-9)
+
+
+def test_more_than_int32_nonzeros_is_refused(libs):
+    """Every cub call of the load takes a 32-bit signed item count: 2^31 - 1 nonzeros on one GPU must be refused before
+    anything is read (the arrays handed in here are 4 entries long), with the advice to shard."""
+    gpu, _ = _pair(libs)
+    four = np.zeros(4, np.uint32)
+    ptr = four.ctypes.data
+    with gpu:
+        for nnz0 in (0x7FFFFFFF, 1 << 33):
+            with pytest.raises(RuntimeError, match="2\\^31-2 nonzeros per GPU: shard"):
+                gpu.load_cell_data_ptrs(ptr, ptr, ptr, ptr, nnz0, 5, 3)
+        # the context is still usable
+        gpu.load_cell_data([0, 1], [0, 0], [5, 5], [5, 5], n_loci0=5, n_cells=3)
 
 
 def test_parity_dense_tiles(libs, monkeypatch):

@@ -159,13 +159,15 @@ def test_mtx_text_roundtrip(tmp_path, oracle_lib):
         assert np.array_equal(got, want)
 
 
-GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "oracle_c1_slice.json")
+GOLDEN_DIR = os.path.join(os.path.dirname(__file__), "golden")
 
 
-def test_oracle_matches_committed_golden():
-    """tests/golden/oracle_c1_slice.json was written by tests/golden/make_golden.py from this oracle: it freezes
-    the oracle's behaviour (a later change of the restatement cannot silently move the target)."""
-    g = json.load(open(GOLDEN))
+@pytest.mark.parametrize("fixture", ["oracle_c1_slice.json", "oracle_c1.json", "oracle_c2.json"])
+def test_oracle_matches_committed_golden(fixture):
+    """The fixtures were written by tests/golden/make_golden.py from this oracle: they freeze the oracle's behaviour (a
+    later change of the restatement cannot silently move the target), at a small deep case and at BASELINE.json
+    configs[0] / configs[1] in full."""
+    g = json.load(open(os.path.join(GOLDEN_DIR, fixture)))
     d = synth.generate(synth.SynthConfig(**g["config"]))
     orc = Oracle()
     assert list(orc.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)) == g["loaded"]
@@ -173,11 +175,14 @@ def test_oracle_matches_committed_golden():
         st = orc.compute_new_excluded(5.0).as_dict()
         for k, v in want["stats"].items():
             assert st[k] == v, (k, st[k], v)   # bit-exact: same code, same libm
-        cv = orc.cell_vectors()
+        cv, lv = orc.cell_vectors(), orc.locus_vectors()
         assert float(cv["ll"].sum()) == want["ll_sum"]
         assert float(cv["expected_ll"].sum()) == want["expected_ll_sum"]
         assert int(cv["n_loci"].sum()) == want["n_loci_sum"]
         assert np.flatnonzero(cv["excluded"]).tolist() == want["excluded"]
+        assert cv["ll"][want["cell_idx"]].tolist() == want["cell_ll"]
+        assert lv["ll_minority"][want["locus_idx"]].tolist() == want["locus_ll_minority"]
+        assert lv["ll_majority"][want["locus_idx"]].tolist() == want["locus_ll_majority"]
     p = orc.calculate_posteriors()
     assert np.bincount(p["label"], minlength=4).tolist() == g["label_counts"]
     assert float(p["ll_minor"].sum()) == g["ll_minor_sum"]
