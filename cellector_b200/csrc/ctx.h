@@ -121,9 +121,15 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> h_row_ptr;                      // [n_cells + 1]
     clx::DevBuf<uint32_t> hc_perm;                        // [n_heavy] CSC order -> index into the CSR-order lists
     clx::DevBuf<uint32_t> hc_col_ptr;                     // [n_loci + 1]
+    // heavy entries with total <= HEAVY_CHAIN_MAX grouped by (locus, total): the (total + 1) log_pmf values and the
+    // expected-log-likelihood chain are evaluated once per group (em_kernels.cuh: k_heavy_groups)
+    clx::DevBuf<uint32_t> hg_member;                      // [n_heavy] heavy entries ordered by (locus, total); chain entries first
+    clx::DevBuf<uint32_t> hg_start;                       // [n_heavy + 1] first member of every group (only [0, *hg_count] valid)
+    clx::DevBuf<uint32_t> hg_count;                       // [2] device: number of groups, number of chain entries
     clx::DevBuf<uint32_t> giant_idx;                      // [n_giant] heavy entries with total > HEAVY_GIANT_TOTAL
     uint32_t n_giant = 0;
     clx::DevBuf<double> hv_ll, hv_e;                      // [3 * n_heavy] values of the current scoring pass
+    clx::DevBuf<double> hrow;                             // [3][n_cells] the same summed per cell (k_heavy_row_sums)
     // --- run-stream scoring layout (tiled.cu): light entries (total 1..3) as 2-byte words, ordered by runs (one cell x
     //     one locus tile) in length-sorted groups of 32; one work item = one cell block x a range of locus tiles
     bool tiled_ready = false;

@@ -49,7 +49,7 @@ void launch_score_rows(clx_ctx* c, int G) {
     if (n == 0) return;
 #define CLX_SCORE(GG)                                                                                                  \
     k_score_rows<GG, NT, WITH_E><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                 \
-        c->csr.p, c->row_ptr.p, n, c->tab.p, c->n_loci, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p, (uint32_t)c->n_heavy,   \
+        c->csr.p, c->row_ptr.p, n, c->tab.p, c->n_loci, c->hrow.p,                                                      \
         NT == 1 ? c->ll.p : c->post_ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag)
     switch (G) {
         case 4: CLX_SCORE(4); break;
@@ -201,6 +201,8 @@ int em_alloc(clx_ctx* c) {
     CLX_CUDA(c, c->tab.alloc(3 * L * TAB_STRIDE + TAB_STRIDE));
     CLX_CUDA(c, c->ll.alloc(N + 1));
     CLX_CUDA(c, c->post_ll.alloc(3 * N + 1));
+    CLX_CUDA(c, c->hrow.alloc(3 * N + 1));
+    CLX_CUDA(c, cudaMemsetAsync(c->hrow.p, 0, c->hrow.bytes(), c->stream));
     CLX_CUDA(c, c->ell.alloc(N + 1));
     const size_t norm_n = std::max<size_t>(N, c->max_local_cells) + 1;
     CLX_CUDA(c, c->norm.alloc(norm_n));
@@ -279,11 +281,20 @@ int enqueue_iteration(clx_ctx* c) {
     auto heavy = [&]() -> int {
         if (!c->n_heavy) return CLX_OK;
         k_heavy_em<<<(unsigned)((c->n_heavy + HEAVY_HB - 1) / HEAVY_HB), TPB, 0, hs>>>(
-            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
-        c->launches++;
+            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, 1);
+        // entries up to HEAVY_CHAIN_TOTAL: one evaluation per (locus, total) group
+        const unsigned gg = (unsigned)std::min<uint64_t>((c->n_heavy + 127) / 128, (uint64_t)c->sm_count * 16);
+        k_heavy_groups<<<gg, 128, 0, hs>>>(c->hg_start.p, c->hg_member.p, c->hg_count.p, c->h_locus.p, c->h_ref.p, c->h_alt.p, cnts,
+                                           c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+        c->launches += 2;
         if (c->n_giant) {
             k_heavy_giant<<<c->n_giant, TPB, 0, hs>>>(c->giant_idx.p, c->n_giant, c->h_locus.p, c->h_ref.p, c->h_alt.p, cnts,
                                                       c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+            c->launches++;
+        }
+        if (c->n_cells) {
+            k_heavy_row_sums<<<(unsigned)(((uint64_t)c->n_cells * 32 + TPB - 1) / TPB), TPB, 0, hs>>>(c->h_row_ptr.p, c->n_cells, c->hv_ll.p,
+                                                                                                    c->hv_e.p, nullptr, c->hrow.p);
             c->launches++;
         }
         return CLX_OK;
@@ -489,7 +500,9 @@ int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used
     if (c->n_heavy) {
         k_heavy_post<<<(unsigned)((3 * c->n_heavy + TPB - 1) / TPB), TPB, 0, s>>>(
             c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, c->tab.p, L, c->lnfact.p, c->hv_ll.p);
-        c->launches++;
+        k_heavy_row_sums<<<(unsigned)(((uint64_t)N * 32 + TPB - 1) / TPB), TPB, 0, s>>>(c->h_row_ptr.p, N, c->hv_ll.p, c->hv_ll.p + c->n_heavy,
+                                                                                     c->hv_ll.p + 2 * c->n_heavy, c->hrow.p);
+        c->launches += 2;
     }
     phase_end(c, CLX_PHASE_HEAVY);
     // get_loci_used_for_posterior_calc pushes true on both branches (main.rs:301-303): every locus is scored

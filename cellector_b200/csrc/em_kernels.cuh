@@ -202,7 +202,7 @@ __device__ __forceinline__ void em_alpha_beta(const EmCounts& k, uint32_t l, dou
 
 constexpr int HEAVY_HB = 256;           // entries per CTA (one thread each)
 constexpr uint32_t HEAVY_GIANT = HEAVY_GIANT_TOTAL;
-constexpr uint32_t HEAVY_CHAIN_MAX = 32;
+constexpr uint32_t HEAVY_CHAIN_MAX = HEAVY_CHAIN_TOTAL;
 
 __device__ __forceinline__ double ln_factorial_int(uint64_t n, const double* __restrict__ lnfact, const double* __restrict__ lng,
                                                    uint32_t lng_n) {
@@ -222,18 +222,21 @@ static __device__ __noinline__ double heavy_ll_k(uint64_t n, uint64_t k, double 
 __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                                        const uint32_t* __restrict__ h_alt, uint32_t n_heavy, EmCounts cnts,
                                                        const double* __restrict__ lnfact, int with_expected,
-                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e, int chains_grouped) {
     const double* __restrict__ lng = cnts.lng;
     const uint32_t lng_n = cnts.lng_n;
     const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u;
-    const bool live = h < n_heavy;
+    bool live = h < n_heavy;
     uint64_t a = 0, n = 0;
     double alpha = 1.0, beta = 1.0, den = 0.0, lgab = 0.0;
     bool on = false;
     if (live) {
         a = h_alt[h];
         n = a + (uint64_t)h_ref[h];
+        if (chains_grouped && n <= HEAVY_CHAIN_MAX) live = false;  // k_heavy_groups evaluates these
+    }
+    if (live) {
         em_alpha_beta(cnts, h_locus[h], &alpha, &beta, &den);
         on = den == den;  // NaN den marks a locus that is switched off: contributes nothing
         if (!on) {
@@ -343,6 +346,48 @@ __global__ void __launch_bounds__(256) k_tables_em(EmCounts cnts, uint32_t n_loc
     rec[tab_idx_E(n)] = e;
 }
 
+// Chain entries by (locus, total) group: the total + 1 values ll_k and the expected-log-likelihood chain (stats.rs:17-22)
+// depend only on the locus and the total, so they are evaluated once per group and handed to every member (own log_pmf
+// = ll_alt).  Same expressions, same order as the per-entry chain of k_heavy_em: bit-identical values, ~4x fewer of them
+// at 14 heavy entries per locus (C3: 287 -> measured in profiles/).
+__global__ void __launch_bounds__(128) k_heavy_groups(const uint32_t* __restrict__ hg_start, const uint32_t* __restrict__ hg_member,
+                                                      const uint32_t* __restrict__ hg_count, const uint32_t* __restrict__ h_locus,
+                                                      const uint32_t* __restrict__ h_ref, const uint32_t* __restrict__ h_alt,
+                                                      EmCounts cnts, const double* __restrict__ lnfact, int with_expected,
+                                                      double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+    const double* __restrict__ lng = cnts.lng;
+    const uint32_t lng_n = cnts.lng_n;
+    const uint32_t n_groups = hg_count[0], n_chain = hg_count[1];
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < n_groups; g += gridDim.x * blockDim.x) {
+        const uint32_t m0 = hg_start[g], m1 = g + 1 < n_groups ? hg_start[g + 1] : n_chain;
+        const uint32_t h0 = hg_member[m0];
+        const uint64_t n = (uint64_t)h_ref[h0] + (uint64_t)h_alt[h0];
+        double alpha, beta, den;
+        em_alpha_beta(cnts, h_locus[h0], &alpha, &beta, &den);
+        if (!(den == den)) {  // switched off by the -80 rule: contributes nothing
+            for (uint32_t m = m0; m < m1; ++m) {
+                const uint32_t h = hg_member[m];
+                hv_ll[h] = 0.0;
+                hv_e[h] = 0.0;
+            }
+            continue;
+        }
+        const double lgab = ln_gamma_int(((double)0 + alpha) + ((double)n + beta), lng, lng_n);
+        double ll[HEAVY_CHAIN_MAX + 1];
+        double ex = 0.0;
+        for (uint64_t k = 0; k <= n; ++k) {
+            const double v = heavy_ll_k(n, k, alpha, beta, lgab, den, lnfact, lng, lng_n);
+            ll[k] = v;
+            if (with_expected) ex = k == 0 ? 2.0 * v : logsumexp2(ex, 2.0 * v);
+        }
+        for (uint32_t m = m0; m < m1; ++m) {
+            const uint32_t h = hg_member[m];
+            hv_ll[h] = ll[h_alt[h]];
+            hv_e[h] = ex;
+        }
+    }
+}
+
 // One CTA per giant entry (total > HEAVY_GIANT): streaming max / sum logsumexp over k = 0..n in fixed chunks.
 __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict__ giant_idx, uint32_t n_giant,
                                                      const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
@@ -408,6 +453,37 @@ __global__ void __launch_bounds__(256) k_heavy_post(const uint32_t* __restrict__
         log_beta_binomial_pmf_den((double)a, (double)r, rec[TAB_ALPHA], rec[TAB_BETA], ln_binomial(a + r, a, lnfact), rec[TAB_DEN]);
 }
 
+// Heavy values summed per cell, one warp per cell (lanes stride over the cell's heavy entries in row order, fixed xor
+// tree: deterministic).  The scoring kernels add these sums instead of walking the heavy list with one lane: a cell of a
+// skewed matrix (C5: the deepest cell holds 390 000 entries, thousands of them heavy) made that walk the whole pass.
+// v0 / v1 / v2: up to three value arrays (EM: log_pmf, expected; posteriors: minority, majority, doublet); out[t][cell].
+__global__ void __launch_bounds__(256) k_heavy_row_sums(const uint32_t* __restrict__ h_row_ptr, uint32_t n_cells,
+                                                        const double* __restrict__ v0, const double* __restrict__ v1,
+                                                        const double* __restrict__ v2, double* __restrict__ out) {
+    const uint32_t row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (row >= n_cells) return;
+    const uint32_t hb = h_row_ptr[row], he = h_row_ptr[row + 1];
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+    for (uint32_t h = hb + lane; h < he; h += 32) {
+        s0 += v0[h];
+        if (v1) s1 += v1[h];
+        if (v2) s2 += v2[h];
+    }
+    if (he - hb > 1) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            s0 += __shfl_xor_sync(0xffffffffu, s0, off);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+            s2 += __shfl_xor_sync(0xffffffffu, s2, off);
+        }
+    }
+    if (lane == 0) {
+        out[row] = s0;
+        if (v1) out[(size_t)n_cells + row] = s1;
+        if (v2) out[2 * (size_t)n_cells + row] = s2;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Gather scoring kernel (get_cell_log_likelihoods, main.rs:541-591) for matrices whose memo table stays in L2:
 // G lanes per CSR row, U independent 128-bit loads of two packed entries per lane in flight, one memo-table
@@ -416,9 +492,7 @@ constexpr int SCORE_UNROLL = 4;
 template <int G, int NT, bool WITH_E>
 __global__ void __launch_bounds__(256) k_score_rows(const RowEntry* __restrict__ csr, const uint64_t* __restrict__ row_ptr,
                                                     uint32_t n_cells, const double* __restrict__ tab, uint32_t n_loci,
-                                                    const uint32_t* __restrict__ h_row_ptr,
-                                                    const double* __restrict__ hv_ll, const double* __restrict__ hv_e,
-                                                    uint32_t n_heavy, double* __restrict__ ll, double* __restrict__ ell,
+                                                    const double* __restrict__ hrow, double* __restrict__ ll, double* __restrict__ ell,
                                                     uint32_t* __restrict__ nloci, double* __restrict__ norm,
                                                     unsigned int* __restrict__ nan_flag) {
     constexpr int U = SCORE_UNROLL;
@@ -479,12 +553,10 @@ __global__ void __launch_bounds__(256) k_score_rows(const RowEntry* __restrict__
         cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
     }
     if (live && g == 0) {
-        const uint32_t hb = h_row_ptr[row], he = h_row_ptr[row + 1];
-        for (uint32_t h = hb; h < he; ++h) {
+        // the cell's heavy entries, already summed (k_heavy_row_sums): [t][cell], EM: [0] log_pmf, [1] expected
 #pragma unroll
-            for (int t = 0; t < NT; ++t) acc[t] += hv_ll[(size_t)t * n_heavy + h];
-            if (WITH_E) acc_e += hv_e[h];
-        }
+        for (int t = 0; t < NT; ++t) acc[t] += hrow[(size_t)t * n_cells + row];
+        if (WITH_E) acc_e += hrow[(size_t)n_cells + row];
 #pragma unroll
         for (int t = 0; t < NT; ++t) ll[(size_t)t * n_cells + row] = acc[t];
         if (NT == 1) {

@@ -67,6 +67,23 @@ struct GiantAt {
     uint64_t limit;
     __device__ bool operator()(uint32_t h) const { return (uint64_t)ref[h] + (uint64_t)alt[h] > limit; }
 };
+// (locus, total) key of a heavy entry whose chain is evaluated per group; deeper entries sort behind all of them
+__global__ void k_heavy_group_keys(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
+                                   const uint32_t* __restrict__ h_alt, uint32_t n_heavy, unsigned long long* __restrict__ keys,
+                                   uint32_t* __restrict__ idx, uint32_t* __restrict__ n_chain) {
+    const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= n_heavy) return;
+    const uint64_t n = (uint64_t)h_ref[h] + (uint64_t)h_alt[h];
+    const bool chain = n <= (uint64_t)HEAVY_CHAIN_TOTAL;
+    keys[h] = chain ? (((unsigned long long)h_locus[h] << 8) | (unsigned long long)n) : ~0ull;
+    idx[h] = h;
+    if (chain) atomicAdd(n_chain, 1u);
+}
+// group boundaries of the sorted keys: start[g] for every first member, the count through an atomic-free scan
+struct GroupHead {
+    const unsigned long long* keys;
+    __device__ bool operator()(uint32_t i) const { return keys[i] != ~0ull && (i == 0 || keys[i] != keys[i - 1]); }
+};
 struct ToU64 {
     __device__ uint64_t operator()(uint32_t v) const { return (uint64_t)v; }
 };
@@ -424,6 +441,29 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, hcpos.p, n_sel.p, (int)nnz, f2, s));
         k_heavy_perm<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, csc_src.p, hpos.p, n_heavy, c->hc_perm.p);
         c->launches += 4;
+    }
+    // chain entries (total <= HEAVY_CHAIN_TOTAL) grouped by (locus, total)
+    CLX_CUDA(c, c->hg_member.alloc(n_heavy));
+    CLX_CUDA(c, c->hg_start.alloc((size_t)n_heavy + 1));
+    CLX_CUDA(c, c->hg_count.alloc(2));
+    CLX_CUDA(c, cudaMemsetAsync(c->hg_count.p, 0, 8, s));
+    if (n_heavy) {
+        DevBuf<unsigned long long> gk, gk_sorted;
+        DevBuf<uint32_t> gi;
+        CLX_CUDA(c, gk.alloc(n_heavy));
+        CLX_CUDA(c, gk_sorted.alloc(n_heavy));
+        CLX_CUDA(c, gi.alloc(n_heavy));
+        k_heavy_group_keys<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(c->h_locus.p, c->h_ref.p, c->h_alt.p, n_heavy, gk.p, gi.p,
+                                                                   c->hg_count.p + 1);
+        CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, gk.p, gk_sorted.p, gi.p, c->hg_member.p, (int)n_heavy, 0, 64, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, gk.p, gk_sorted.p, gi.p, c->hg_member.p, (int)n_heavy, 0, 64, s));
+        cub::CountingInputIterator<uint32_t> counting(0);
+        GroupHead gh{gk_sorted.p};
+        CLX_CUDA(c, cub::DeviceSelect::If(nullptr, tmp_bytes, counting, c->hg_start.p, c->hg_count.p, (int)n_heavy, gh, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, c->hg_start.p, c->hg_count.p, (int)n_heavy, gh, s));
+        c->launches += 7;
     }
     // entries too deep for the batched heavy kernel get a CTA each (em_kernels.cuh: k_heavy_giant)
     c->n_giant = 0;

@@ -23,6 +23,7 @@ namespace clx {
 constexpr int K_LIGHT = 3;
 // Heavy entries deeper than this are evaluated by one CTA each (k_heavy_giant) instead of the batched kernel.
 constexpr uint32_t HEAVY_GIANT_TOTAL = 1000;
+constexpr uint32_t HEAVY_CHAIN_TOTAL = 32;    // heavy entries up to this total: chain evaluated once per (locus, total) group
 // One 128-byte record per locus, laid out so that everything an entry of total n needs sits in one
 // 32-byte sector:   [0..1] T(a=0..1 | n=1)  [2] E(1)  [3] -
 //                   [4..6] T(a=0..2 | n=2)  [7] E(2)

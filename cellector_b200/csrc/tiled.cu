@@ -590,8 +590,8 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
 constexpr int FIN_LANES = 8;
 template <int MODE>
 __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__ part, const uint32_t* __restrict__ cb_item,
-                                                      uint32_t NB, uint32_t n_cells, const uint32_t* __restrict__ h_row_ptr,
-                                                      const double* __restrict__ hv0, const double* __restrict__ hv1,
+                                                      uint32_t NB, uint32_t n_cells, const double* __restrict__ hs0,
+                                                      const double* __restrict__ hs1,
                                                       const uint32_t* __restrict__ n_used, double* __restrict__ out0,
                                                       double* __restrict__ out1, uint32_t* __restrict__ nloci,
                                                       double* __restrict__ norm, unsigned int* __restrict__ nan_flag) {
@@ -617,11 +617,8 @@ __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__
         if (MODE != SCORE_POST_C) s1 += __shfl_xor_sync(0xffffffffu, s1, off);
     }
     if (!live || sub != 0) return;
-    const uint32_t hb = h_row_ptr[i], he = h_row_ptr[i + 1];
-    for (uint32_t h = hb; h < he; ++h) {
-        s0 += hv0[h];
-        if (MODE != SCORE_POST_C) s1 += hv1[h];
-    }
+    s0 += hs0[i];  // the cell's heavy entries, summed by k_heavy_row_sums
+    if (MODE != SCORE_POST_C) s1 += hs1[i];
     out0[i] = s0;
     if (MODE != SCORE_POST_C) out1[i] = s1;
     if (MODE == SCORE_EM) {
@@ -652,17 +649,16 @@ int score_tiled(clx_ctx* c, ScoreMode mode) {
         c->launches++;
         CLX_DEBUG_SYNC(c, "k_score_runs");
     }
-    const size_t nh = c->n_heavy;
     const unsigned fgrid = (unsigned)(((uint64_t)N * FIN_LANES + 255) / 256);
     if (mode == SCORE_EM)
-        k_score_finish<SCORE_EM><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p,
+        k_score_finish<SCORE_EM><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->hrow.p, c->hrow.p + N,
                                                       c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag);
     else if (mode == SCORE_POST_AB)
-        k_score_finish<SCORE_POST_AB><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p,
-                                                           c->hv_ll.p + nh, nullptr, c->post_ll.p, c->post_ll.p + N, nullptr, nullptr,
+        k_score_finish<SCORE_POST_AB><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->hrow.p,
+                                                           c->hrow.p + N, nullptr, c->post_ll.p, c->post_ll.p + N, nullptr, nullptr,
                                                            nullptr);
     else
-        k_score_finish<SCORE_POST_C><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p + 2 * nh,
+        k_score_finish<SCORE_POST_C><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->hrow.p + 2 * (size_t)N,
                                                           nullptr, nullptr, c->post_ll.p + 2 * (size_t)N, nullptr, nullptr, nullptr, nullptr);
     c->launches++;
     return CLX_OK;
