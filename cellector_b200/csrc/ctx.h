@@ -128,6 +128,8 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> hg_count;                       // [2] device: number of groups, number of chain entries
     clx::DevBuf<uint32_t> giant_idx;                      // [n_giant] heavy entries with total > HEAVY_GIANT_TOTAL
     uint32_t n_giant = 0;
+    clx::DevBuf<uint32_t> deep_idx;                       // [n_deep] heavy entries with HEAVY_CHAIN_TOTAL < total <= HEAVY_GIANT_TOTAL
+    uint32_t n_deep = 0;
     clx::DevBuf<double> hv_ll, hv_e;                      // [3 * n_heavy] values of the current scoring pass
     clx::DevBuf<double> hrow;                             // [3][n_cells] the same summed per cell (k_heavy_row_sums)
     // --- run-stream scoring layout (tiled.cu): light entries (total 1..3) as 2-byte words, ordered by runs (one cell x
@@ -180,6 +182,10 @@ struct clx_ctx {
     clx::DevBuf<clx::DeviceStats> d_stats;
     clx::DevBuf<clx::IterParams> d_params;
     clx::IterParams* h_params = nullptr;              // pinned; copied to d_params at the head of every iteration
+    // gather scoring kernel: rows in segments of ROW_SEG entries
+    clx::DevBuf<uint32_t> seg_first, seg_row, seg_cnt;  // [n_cells + 1] / [n_seg] / [n_seg]
+    clx::DevBuf<double> seg_part;                     // [4][n_seg] partial sums of multi-segment rows
+    uint32_t n_seg = 0;
     int score_G = 32, col_G = 8;                      // lanes per CSR row / CSC column (picked at load)
     void* iter_graph_exec = nullptr;                  // cudaGraphExec_t of one EM iteration (world == 1)
     uint64_t graph_launches = 0;                      // kernels inside that graph

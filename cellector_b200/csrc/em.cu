@@ -8,6 +8,8 @@
 
 #include <algorithm>
 
+#include <cub/cub.cuh>
+
 #include "ctx.h"
 #include "em_kernels.cuh"
 #include "numerics.cuh"
@@ -47,10 +49,11 @@ template <int NT, bool WITH_E>
 void launch_score_rows(clx_ctx* c, int G) {
     const uint32_t n = c->n_cells;
     if (n == 0) return;
+    double* out = NT == 1 ? c->ll.p : c->post_ll.p;
 #define CLX_SCORE(GG)                                                                                                  \
-    k_score_rows<GG, NT, WITH_E><<<(unsigned)(((uint64_t)n * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(                 \
-        c->csr.p, c->row_ptr.p, n, c->tab.p, c->n_loci, c->hrow.p,                                                      \
-        NT == 1 ? c->ll.p : c->post_ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag)
+    k_score_rows<GG, NT, WITH_E><<<(unsigned)(((uint64_t)c->n_seg * GG + TPB - 1) / TPB), TPB, 0, c->stream>>>(         \
+        c->csr.p, c->row_ptr.p, n, c->tab.p, c->n_loci, c->hrow.p, c->seg_row.p, c->seg_first.p, c->n_seg, c->seg_part.p, \
+        c->seg_cnt.p, out, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag)
     switch (G) {
         case 4: CLX_SCORE(4); break;
         case 8: CLX_SCORE(8); break;
@@ -59,6 +62,12 @@ void launch_score_rows(clx_ctx* c, int G) {
     }
 #undef CLX_SCORE
     c->launches++;
+    if (c->n_seg > n) {  // some row has more than one segment
+        k_score_rows_combine<NT, WITH_E><<<(n + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->seg_first.p, n, c->n_seg, c->seg_part.p, c->seg_cnt.p,
+                                                                                  c->hrow.p, out, c->ell.p, c->nloci.p, c->norm.p,
+                                                                                  &c->d_stats.p->nan_flag);
+        c->launches++;
+    }
 }
 
 template <bool FUSE>
@@ -223,6 +232,26 @@ int em_alloc(clx_ctx* c) {
         CLX_CUDA(c, cudaStreamSynchronize(c->stream));
     }
     CLX_TRY(p2p_setup(c, L, c->max_local_cells));
+    {   // row segments of the gather scoring kernel
+        DevBuf<uint32_t> cnt;
+        DevBuf<uint8_t> tmp;
+        size_t tb = 0;
+        CLX_CUDA(c, cnt.alloc(N + 1));
+        CLX_CUDA(c, c->seg_first.alloc(N + 1));
+        k_row_seg_count<<<(unsigned)((N + 1 + TPB - 1) / TPB), TPB, 0, c->stream>>>(c->row_ptr.p, (uint32_t)N, cnt.p);
+        CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt.p, c->seg_first.p, (int)(N + 1), c->stream));
+        CLX_CUDA(c, tmp.alloc(tb));
+        CLX_CUDA(c, cub::DeviceScan::ExclusiveSum(tmp.p, tb, cnt.p, c->seg_first.p, (int)(N + 1), c->stream));
+        uint32_t n_seg = 0;
+        CLX_CUDA(c, cudaMemcpyAsync(&n_seg, c->seg_first.p + N, 4, cudaMemcpyDeviceToHost, c->stream));
+        CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->n_seg = n_seg;
+        CLX_CUDA(c, c->seg_row.alloc((size_t)n_seg + 1));
+        CLX_CUDA(c, c->seg_cnt.alloc((size_t)n_seg + 1));
+        CLX_CUDA(c, c->seg_part.alloc(4 * (size_t)n_seg + 1));
+        if (N) k_row_seg_fill<<<(unsigned)((N + TPB - 1) / TPB), TPB, 0, c->stream>>>(c->seg_first.p, (uint32_t)N, c->seg_row.p);
+        c->launches += 4;
+    }
     c->score_G = env_int("CLX_SCORE_G", pick_group(N ? (double)c->nnz / N : 0.0));
     c->col_G = env_int("CLX_COL_G", pick_group(L ? (double)c->nnz / L : 0.0));
     // roofline accounting of the gather scoring kernel: packed entries + row pointers + outputs + table
@@ -280,19 +309,22 @@ int enqueue_iteration(clx_ctx* c) {
     }
     auto heavy = [&]() -> int {
         if (!c->n_heavy) return CLX_OK;
-        k_heavy_em<<<(unsigned)((c->n_heavy + HEAVY_HB - 1) / HEAVY_HB), TPB, 0, hs>>>(
-            c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, 1);
+        if (c->n_deep) {  // HEAVY_CHAIN_TOTAL < total <= HEAVY_GIANT_TOTAL: a warp per entry
+            k_heavy_em<<<(c->n_deep + HEAVY_HB - 1) / HEAVY_HB, TPB, 0, hs>>>(c->deep_idx.p, c->n_deep, c->h_locus.p, c->h_ref.p, c->h_alt.p,
+                                                                              cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+            c->launches++;
+        }
         // entries up to HEAVY_CHAIN_TOTAL: one evaluation per (locus, total) group
         const unsigned gg = (unsigned)std::min<uint64_t>((c->n_heavy + 127) / 128, (uint64_t)c->sm_count * 16);
         k_heavy_groups<<<gg, 128, 0, hs>>>(c->hg_start.p, c->hg_member.p, c->hg_count.p, c->h_locus.p, c->h_ref.p, c->h_alt.p, cnts,
                                            c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
-        c->launches += 2;
+        c->launches++;
         if (c->n_giant) {
             k_heavy_giant<<<c->n_giant, TPB, 0, hs>>>(c->giant_idx.p, c->n_giant, c->h_locus.p, c->h_ref.p, c->h_alt.p, cnts,
                                                       c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
             c->launches++;
         }
-        if (c->n_cells) {
+        if (c->n_cells && !use_tiled(c)) {  // the gather kernel adds per-cell sums; the run-stream finish walks the lists itself
             k_heavy_row_sums<<<(unsigned)(((uint64_t)c->n_cells * 32 + TPB - 1) / TPB), TPB, 0, hs>>>(c->h_row_ptr.p, c->n_cells, c->hv_ll.p,
                                                                                                     c->hv_e.p, nullptr, c->hrow.p);
             c->launches++;
@@ -500,9 +532,12 @@ int em_posteriors(clx_ctx* c, double posterior_threshold, uint32_t min_loci_used
     if (c->n_heavy) {
         k_heavy_post<<<(unsigned)((3 * c->n_heavy + TPB - 1) / TPB), TPB, 0, s>>>(
             c->h_locus.p, c->h_ref.p, c->h_alt.p, (uint32_t)c->n_heavy, c->tab.p, L, c->lnfact.p, c->hv_ll.p);
-        k_heavy_row_sums<<<(unsigned)(((uint64_t)N * 32 + TPB - 1) / TPB), TPB, 0, s>>>(c->h_row_ptr.p, N, c->hv_ll.p, c->hv_ll.p + c->n_heavy,
-                                                                                     c->hv_ll.p + 2 * c->n_heavy, c->hrow.p);
-        c->launches += 2;
+        c->launches++;
+        if (!use_tiled(c)) {
+            k_heavy_row_sums<<<(unsigned)(((uint64_t)N * 32 + TPB - 1) / TPB), TPB, 0, s>>>(c->h_row_ptr.p, N, c->hv_ll.p, c->hv_ll.p + c->n_heavy,
+                                                                                         c->hv_ll.p + 2 * c->n_heavy, c->hrow.p);
+            c->launches++;
+        }
     }
     phase_end(c, CLX_PHASE_HEAVY);
     // get_loci_used_for_posterior_calc pushes true on both branches (main.rs:301-303): every locus is scored

@@ -219,24 +219,23 @@ static __device__ __noinline__ double heavy_ll_k(uint64_t n, uint64_t k, double 
     return ln_binomial_int(n, k, lnfact, lng, lng_n) + num - den;
 }
 
-__global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
-                                                       const uint32_t* __restrict__ h_alt, uint32_t n_heavy, EmCounts cnts,
+__global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restrict__ deep_idx, uint32_t n_deep,
+                                                       const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
+                                                       const uint32_t* __restrict__ h_alt, EmCounts cnts,
                                                        const double* __restrict__ lnfact, int with_expected,
-                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e, int chains_grouped) {
+                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e) {
     const double* __restrict__ lng = cnts.lng;
     const uint32_t lng_n = cnts.lng_n;
-    const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u;
-    bool live = h < n_heavy;
+    const bool live = i < n_deep;
+    const uint32_t h = live ? deep_idx[i] : 0u;
     uint64_t a = 0, n = 0;
     double alpha = 1.0, beta = 1.0, den = 0.0, lgab = 0.0;
     bool on = false;
     if (live) {
         a = h_alt[h];
         n = a + (uint64_t)h_ref[h];
-        if (chains_grouped && n <= HEAVY_CHAIN_MAX) live = false;  // k_heavy_groups evaluates these
-    }
-    if (live) {
         em_alpha_beta(cnts, h_locus[h], &alpha, &beta, &den);
         on = den == den;  // NaN den marks a locus that is switched off: contributes nothing
         if (!on) {
@@ -246,25 +245,15 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
             lgab = ln_gamma_int(((double)a + alpha) + ((double)(n - a) + beta), lng, lng_n);
         }
     }
-    if (live && on && n <= HEAVY_CHAIN_MAX) {
-        const double own = heavy_ll_k(n, a, alpha, beta, lgab, den, lnfact, lng, lng_n);
-        double ex = 0.0;
-        if (with_expected) {
-            ex = 2.0 * heavy_ll_k(n, 0, alpha, beta, lgab, den, lnfact, lng, lng_n);
-            for (uint64_t k = 1; k <= n; ++k) ex = logsumexp2(ex, 2.0 * heavy_ll_k(n, k, alpha, beta, lgab, den, lnfact, lng, lng_n));
-        }
-        hv_ll[h] = own;
-        hv_e[h] = ex;
-    }
     // deep entries of this warp, one at a time over all 32 lanes
-    unsigned int deep = __ballot_sync(0xffffffffu, live && on && n > HEAVY_CHAIN_MAX && n <= HEAVY_GIANT);
+    unsigned int deep = __ballot_sync(0xffffffffu, live && on);
     while (deep) {
         const int src = __ffs(deep) - 1;
         deep &= deep - 1;
         const uint64_t dn = __shfl_sync(0xffffffffu, (unsigned long long)n, src), da = __shfl_sync(0xffffffffu, (unsigned long long)a, src);
         const double dal = __shfl_sync(0xffffffffu, alpha, src), dbe = __shfl_sync(0xffffffffu, beta, src);
         const double dden = __shfl_sync(0xffffffffu, den, src), dlgab = __shfl_sync(0xffffffffu, lgab, src);
-        const uint32_t dh = h - lane + (uint32_t)src;
+        const uint32_t dh = __shfl_sync(0xffffffffu, h, src);
         double ex = 0.0;
         if (with_expected) {
             double m = -INFINITY;
@@ -398,7 +387,13 @@ __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict_
     const uint32_t h = giant_idx[blockIdx.x];
     double alpha, beta, den;
     em_alpha_beta(cnts, h_locus[h], &alpha, &beta, &den);
-    if (!(den == den)) return;  // switched off: k_heavy_em wrote the zeros
+    if (!(den == den)) {  // switched off by the -80 rule: contributes nothing
+        if (threadIdx.x == 0) {
+            hv_ll[h] = 0.0;
+            hv_e[h] = 0.0;
+        }
+        return;
+    }
     const uint64_t a = h_alt[h], r = h_ref[h], n = a + r;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) {
@@ -489,18 +484,45 @@ __global__ void __launch_bounds__(256) k_heavy_row_sums(const uint32_t* __restri
 // G lanes per CSR row, U independent 128-bit loads of two packed entries per lane in flight, one memo-table
 // sector per entry (NaN = locus switched off), xor-shuffle tree, heavy values appended in row order.
 constexpr int SCORE_UNROLL = 4;
+constexpr uint32_t ROW_SEG = 4096;  // entries per row segment: a longer row is split over several lane groups
+// segments of every row (at least one, so that an empty row still gets its outputs): ceil(len / ROW_SEG)
+__global__ void k_row_seg_count(const uint64_t* __restrict__ row_ptr, uint32_t n_cells, uint32_t* __restrict__ n_seg) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n_cells) return;
+    if (i == n_cells) {
+        n_seg[i] = 0;
+        return;
+    }
+    const uint64_t len = row_ptr[i + 1] - row_ptr[i];
+    n_seg[i] = len ? (uint32_t)((len + ROW_SEG - 1) / ROW_SEG) : 1u;
+}
+__global__ void k_row_seg_fill(const uint32_t* __restrict__ seg_first, uint32_t n_cells, uint32_t* __restrict__ seg_row) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_cells) return;
+    for (uint32_t s = seg_first[i]; s < seg_first[i + 1]; ++s) seg_row[s] = i;
+}
+
+// G lanes per row SEGMENT (seg_row / seg_first: a row of a skewed matrix can hold 10^5 entries; one lane group walking
+// it alone was the whole pass at C5).  A row with one segment is finished here; the segments of a longer row leave
+// partial sums in seg_part ([NT + 1][n_seg] doubles + counts) and k_score_rows_combine adds them in segment order.
 template <int G, int NT, bool WITH_E>
 __global__ void __launch_bounds__(256) k_score_rows(const RowEntry* __restrict__ csr, const uint64_t* __restrict__ row_ptr,
                                                     uint32_t n_cells, const double* __restrict__ tab, uint32_t n_loci,
-                                                    const double* __restrict__ hrow, double* __restrict__ ll, double* __restrict__ ell,
+                                                    const double* __restrict__ hrow, const uint32_t* __restrict__ seg_row,
+                                                    const uint32_t* __restrict__ seg_first, uint32_t n_seg,
+                                                    double* __restrict__ seg_part, uint32_t* __restrict__ seg_cnt,
+                                                    double* __restrict__ ll, double* __restrict__ ell,
                                                     uint32_t* __restrict__ nloci, double* __restrict__ norm,
                                                     unsigned int* __restrict__ nan_flag) {
     constexpr int U = SCORE_UNROLL;
     const uint32_t gid = (blockIdx.x * blockDim.x + threadIdx.x) / G;
     const uint32_t g = threadIdx.x % G;
-    const bool live = gid < n_cells;
-    const uint32_t row = live ? gid : 0;
-    const uint64_t begin = live ? row_ptr[row] : 0, end = live ? row_ptr[row + 1] : 0;
+    const bool live = gid < n_seg;
+    const uint32_t row = live ? seg_row[gid] : 0;
+    const uint32_t sf = live ? seg_first[row] : 0, sn = live ? seg_first[row + 1] - sf : 1;
+    const uint64_t rb = live ? row_ptr[row] : 0, re = live ? row_ptr[row + 1] : 0;
+    const uint64_t begin = live ? rb + (uint64_t)(gid - sf) * ROW_SEG : 0;
+    const uint64_t end = live ? (begin + ROW_SEG < re ? begin + ROW_SEG : re) : 0;
     double acc[NT];
 #pragma unroll
     for (int t = 0; t < NT; ++t) acc[t] = 0.0;
@@ -552,7 +574,12 @@ __global__ void __launch_bounds__(256) k_score_rows(const RowEntry* __restrict__
         if (WITH_E) acc_e += __shfl_xor_sync(0xffffffffu, acc_e, off);
         cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
     }
-    if (live && g == 0) {
+    if (live && g == 0 && sn > 1) {  // one segment of a long row: partial sums for k_score_rows_combine
+#pragma unroll
+        for (int t = 0; t < NT; ++t) seg_part[(size_t)t * n_seg + gid] = acc[t];
+        if (WITH_E) seg_part[(size_t)NT * n_seg + gid] = acc_e;
+        seg_cnt[gid] = cnt;
+    } else if (live && g == 0) {
         // the cell's heavy entries, already summed (k_heavy_row_sums): [t][cell], EM: [0] log_pmf, [1] expected
 #pragma unroll
         for (int t = 0; t < NT; ++t) acc[t] += hrow[(size_t)t * n_cells + row];
@@ -566,6 +593,42 @@ __global__ void __launch_bounds__(256) k_score_rows(const RowEntry* __restrict__
             norm[row] = nv;
             if (nv != nv) atomicOr(nan_flag, 1u);
         }
+    }
+}
+
+// rows of more than one segment: partial sums added in segment order, then the tail of k_score_rows
+template <int NT, bool WITH_E>
+__global__ void __launch_bounds__(256) k_score_rows_combine(const uint32_t* __restrict__ seg_first, uint32_t n_cells, uint32_t n_seg,
+                                                            const double* __restrict__ seg_part, const uint32_t* __restrict__ seg_cnt,
+                                                            const double* __restrict__ hrow, double* __restrict__ ll,
+                                                            double* __restrict__ ell, uint32_t* __restrict__ nloci,
+                                                            double* __restrict__ norm, unsigned int* __restrict__ nan_flag) {
+    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n_cells) return;
+    const uint32_t s0 = seg_first[row], s1 = seg_first[row + 1];
+    if (s1 - s0 <= 1) return;
+    double acc[NT], acc_e = 0.0;
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) acc[t] = 0.0;
+    for (uint32_t s = s0; s < s1; ++s) {
+#pragma unroll
+        for (int t = 0; t < NT; ++t) acc[t] += seg_part[(size_t)t * n_seg + s];
+        if (WITH_E) acc_e += seg_part[(size_t)NT * n_seg + s];
+        cnt += seg_cnt[s];
+    }
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+        acc[t] += hrow[(size_t)t * n_cells + row];
+        ll[(size_t)t * n_cells + row] = acc[t];
+    }
+    if (NT == 1) {
+        if (WITH_E) acc_e += hrow[(size_t)n_cells + row];
+        ell[row] = acc_e;
+        nloci[row] = cnt;
+        const double nv = cnt > 0 ? acc[0] / (double)cnt : 0.0;  // main.rs:315-322
+        norm[row] = nv;
+        if (nv != nv) atomicOr(nan_flag, 1u);
     }
 }
 

@@ -67,6 +67,14 @@ struct GiantAt {
     uint64_t limit;
     __device__ bool operator()(uint32_t h) const { return (uint64_t)ref[h] + (uint64_t)alt[h] > limit; }
 };
+struct DeepAt {  // beyond the grouped chains, up to the giants
+    const uint32_t* ref;
+    const uint32_t* alt;
+    __device__ bool operator()(uint32_t h) const {
+        const uint64_t n = (uint64_t)ref[h] + (uint64_t)alt[h];
+        return n > (uint64_t)HEAVY_CHAIN_TOTAL && n <= (uint64_t)HEAVY_GIANT_TOTAL;
+    }
+};
 // (locus, total) key of a heavy entry whose chain is evaluated per group; deeper entries sort behind all of them
 __global__ void k_heavy_group_keys(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                    const uint32_t* __restrict__ h_alt, uint32_t n_heavy, unsigned long long* __restrict__ keys,
@@ -467,7 +475,9 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     }
     // entries too deep for the batched heavy kernel get a CTA each (em_kernels.cuh: k_heavy_giant)
     c->n_giant = 0;
+    c->n_deep = 0;
     CLX_CUDA(c, c->giant_idx.alloc(n_heavy));
+    CLX_CUDA(c, c->deep_idx.alloc(n_heavy));
     if (n_heavy) {
         cub::CountingInputIterator<uint32_t> counting(0);
         GiantAt gp{c->h_ref.p, c->h_alt.p, (uint64_t)HEAVY_GIANT_TOTAL};
@@ -475,10 +485,18 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         CLX_CUDA(c, tmp.alloc(tmp_bytes));
         CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, c->giant_idx.p, n_sel.p, (int)n_heavy, gp, s));
         c->launches += 2;
-        uint32_t ng = 0;
+        uint32_t ng = 0, nd = 0;
         CLX_CUDA(c, cudaMemcpyAsync(&ng, n_sel.p, 4, cudaMemcpyDeviceToHost, s));
+        // deep entries (HEAVY_CHAIN_TOTAL < total <= HEAVY_GIANT_TOTAL): a warp each in k_heavy_em
+        DeepAt dp{c->h_ref.p, c->h_alt.p};
+        CLX_CUDA(c, cub::DeviceSelect::If(nullptr, tmp_bytes, counting, c->deep_idx.p, n_sel.p, (int)n_heavy, dp, s));
+        CLX_CUDA(c, tmp.alloc(tmp_bytes));
+        CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, c->deep_idx.p, n_sel.p, (int)n_heavy, dp, s));
+        c->launches += 2;
+        CLX_CUDA(c, cudaMemcpyAsync(&nd, n_sel.p, 4, cudaMemcpyDeviceToHost, s));
         CLX_CUDA(c, cudaStreamSynchronize(s));
         c->n_giant = ng;
+        c->n_deep = nd;
     }
     k_segment_ptr<<<(n_cells + 1 + TPB - 1) / TPB, TPB, 0, s>>>(hpos.p, n_heavy, c->row_ptr.p, n_cells, c->h_row_ptr.p);
     k_segment_ptr<<<(n_loci + 1 + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, n_heavy, c->col_ptr.p, n_loci, c->hc_col_ptr.p);

@@ -590,8 +590,8 @@ __global__ void __launch_bounds__(W_MAX * 32, 1)
 constexpr int FIN_LANES = 8;
 template <int MODE>
 __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__ part, const uint32_t* __restrict__ cb_item,
-                                                      uint32_t NB, uint32_t n_cells, const double* __restrict__ hs0,
-                                                      const double* __restrict__ hs1,
+                                                      uint32_t NB, uint32_t n_cells, const uint32_t* __restrict__ h_row_ptr,
+                                                      const double* __restrict__ hv0, const double* __restrict__ hv1,
                                                       const uint32_t* __restrict__ n_used, double* __restrict__ out0,
                                                       double* __restrict__ out1, uint32_t* __restrict__ nloci,
                                                       double* __restrict__ norm, unsigned int* __restrict__ nan_flag) {
@@ -611,14 +611,20 @@ __global__ void __launch_bounds__(256) k_score_finish(const double* __restrict__
         s0 += p.x;
         s1 += p.y;
     }
+    if (live) {  // the cell's heavy values, row order, strided over the cell's lanes (a skewed matrix has cells with
+                 // thousands of them: one lane alone walking the list was the whole pass)
+        const uint32_t hb = h_row_ptr[i], he = h_row_ptr[i + 1];
+        for (uint32_t h = hb + sub; h < he; h += FIN_LANES) {
+            s0 += hv0[h];
+            if (MODE != SCORE_POST_C) s1 += hv1[h];
+        }
+    }
 #pragma unroll
     for (int off = 32 / FIN_LANES; off < 32; off <<= 1) {
         s0 += __shfl_xor_sync(0xffffffffu, s0, off);
         if (MODE != SCORE_POST_C) s1 += __shfl_xor_sync(0xffffffffu, s1, off);
     }
     if (!live || sub != 0) return;
-    s0 += hs0[i];  // the cell's heavy entries, summed by k_heavy_row_sums
-    if (MODE != SCORE_POST_C) s1 += hs1[i];
     out0[i] = s0;
     if (MODE != SCORE_POST_C) out1[i] = s1;
     if (MODE == SCORE_EM) {
@@ -649,16 +655,17 @@ int score_tiled(clx_ctx* c, ScoreMode mode) {
         c->launches++;
         CLX_DEBUG_SYNC(c, "k_score_runs");
     }
+    const size_t nh = c->n_heavy;
     const unsigned fgrid = (unsigned)(((uint64_t)N * FIN_LANES + 255) / 256);
     if (mode == SCORE_EM)
-        k_score_finish<SCORE_EM><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->hrow.p, c->hrow.p + N,
+        k_score_finish<SCORE_EM><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p, c->hv_e.p,
                                                       c->n_used.p, c->ll.p, c->ell.p, c->nloci.p, c->norm.p, &c->d_stats.p->nan_flag);
     else if (mode == SCORE_POST_AB)
-        k_score_finish<SCORE_POST_AB><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->hrow.p,
-                                                           c->hrow.p + N, nullptr, c->post_ll.p, c->post_ll.p + N, nullptr, nullptr,
+        k_score_finish<SCORE_POST_AB><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p,
+                                                           c->hv_ll.p + nh, nullptr, c->post_ll.p, c->post_ll.p + N, nullptr, nullptr,
                                                            nullptr);
     else
-        k_score_finish<SCORE_POST_C><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->hrow.p + 2 * (size_t)N,
+        k_score_finish<SCORE_POST_C><<<fgrid, 256, 0, s>>>(c->tl_part.p, c->tl_cb_item.p, c->tl_NB, N, c->h_row_ptr.p, c->hv_ll.p + 2 * nh,
                                                           nullptr, nullptr, c->post_ll.p + 2 * (size_t)N, nullptr, nullptr, nullptr, nullptr);
     c->launches++;
     return CLX_OK;

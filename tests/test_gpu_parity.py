@@ -258,6 +258,16 @@ def test_parity_gather_scoring_forced(libs, monkeypatch):
         run_parity(gpu, orc, synth.generate(CASES["rescue_filter"]))
 
 
+def test_parity_gather_rows_in_segments(libs, monkeypatch):
+    """Rows of ~7000 entries through the gather kernel: two row segments each (ROW_SEG = 4096), partial sums combined
+    by k_score_rows_combine — the path of the deep cells of a skewed matrix."""
+    monkeypatch.setenv("CLX_SCORE_PATH", "gather")
+    gpu, orc = _pair(libs)
+    cfg = synth.SynthConfig(n_cells=160, n_loci=12_000, density=0.6, minority_frac=0.1, seed=23, deep_frac=0.01)
+    with gpu, orc:
+        run_parity(gpu, orc, synth.generate(cfg))
+
+
 def test_parity_very_sparse_takes_gather_scoring(libs, capfd, monkeypatch):
     """Many cell blocks (forced small: 24 blocks of 256 cells) over ~60 locus tiles: ~100 MB of table staging per pass for
     a few hundred entries per (cell block, tile) unit, so the load picks the gather kernel by itself (checked on the load
