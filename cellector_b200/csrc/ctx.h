@@ -121,11 +121,15 @@ struct clx_ctx {
     clx::DevBuf<uint32_t> h_row_ptr;                      // [n_cells + 1]
     clx::DevBuf<uint32_t> hc_perm;                        // [n_heavy] CSC order -> index into the CSR-order lists
     clx::DevBuf<uint32_t> hc_col_ptr;                     // [n_loci + 1]
-    // heavy entries with total <= HEAVY_CHAIN_MAX grouped by (locus, total): the (total + 1) log_pmf values and the
-    // expected-log-likelihood chain are evaluated once per group (em_kernels.cuh: k_heavy_groups)
-    clx::DevBuf<uint32_t> hg_member;                      // [n_heavy] heavy entries ordered by (locus, total); chain entries first
-    clx::DevBuf<uint32_t> hg_start;                       // [n_heavy + 1] first member of every group (only [0, *hg_count] valid)
-    clx::DevBuf<uint32_t> hg_count;                       // [2] device: number of groups, number of chain entries
+    // heavy entries in (locus, total) order ("member" order): equal keys form a group whose chain (total <= HEAVY_CHAIN_TOTAL)
+    // is evaluated once (em_kernels.cuh: k_heavy_groups); a locus's members are one contiguous range for the column pass
+    clx::DevBuf<uint32_t> hg_member;                      // [n_heavy] member -> index into the CSR-order lists
+    clx::DevBuf<uint32_t> hg_start;                       // [n_heavy + 1] first member of every group (only [0, *hg_count) valid)
+    clx::DevBuf<uint32_t> hg_count;                       // [2] device: number of groups
+    clx::DevBuf<uint4> hm_ent;                            // [n_heavy] member order: {cell, ref, alt, CSR-order index}
+    clx::DevBuf<uint32_t> hm_pos;                         // [n_heavy] CSR-order index -> member
+    clx::DevBuf<double> hm_val;                           // [n_heavy] member order: log_pmf of the current EM pass
+    clx::DevBuf<uint32_t> hm_col_ptr;                     // [n_loci + 1] members of every locus
     clx::DevBuf<uint32_t> giant_idx;                      // [n_giant] heavy entries with total > HEAVY_GIANT_TOTAL
     uint32_t n_giant = 0;
     clx::DevBuf<uint32_t> deep_idx;                       // [n_deep] heavy entries with HEAVY_CHAIN_TOTAL < total <= HEAVY_GIANT_TOTAL

@@ -107,8 +107,8 @@ void launch_locus_classes(clx_ctx* c) {
     double* out_ll = c->p2p ? reinterpret_cast<double*>((unsigned char*)c->win + c->win_off_part_ll) : c->loc_ll.p;
     unsigned long long* out_int = c->p2p ? reinterpret_cast<unsigned long long*>((unsigned char*)c->win + c->win_off_part_int) : c->loc_int.p;
     k_locus_finish<FUSE><<<(L + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->cls_all.p, c->cls_min.p, L, c->tab.p, c->loci_used.p, c->excl_bits.p,
-                                                                    c->hc_col_ptr.p, c->hc_perm.p, c->h_cell.p, c->h_ref.p, c->h_alt.p,
-                                                                    c->hv_ll.p, c->csc.p, c->col_ptr.p, out_ll, out_int, c->n_used.p,
+                                                                    c->hm_col_ptr.p, c->hm_ent.p, c->hm_val.p, c->csc.p, c->col_ptr.p,
+                                                                    out_ll, out_int, c->n_used.p,
                                                                     c->d_stats.p);
     c->launches++;
 }
@@ -311,17 +311,17 @@ int enqueue_iteration(clx_ctx* c) {
         if (!c->n_heavy) return CLX_OK;
         if (c->n_deep) {  // HEAVY_CHAIN_TOTAL < total <= HEAVY_GIANT_TOTAL: a warp per entry
             k_heavy_em<<<(c->n_deep + HEAVY_HB - 1) / HEAVY_HB, TPB, 0, hs>>>(c->deep_idx.p, c->n_deep, c->h_locus.p, c->h_ref.p, c->h_alt.p,
-                                                                              cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+                                                                              cnts, c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, c->hm_pos.p, c->hm_val.p);
             c->launches++;
         }
         // entries up to HEAVY_CHAIN_TOTAL: one evaluation per (locus, total) group
         const unsigned gg = (unsigned)std::min<uint64_t>((c->n_heavy + 127) / 128, (uint64_t)c->sm_count * 16);
-        k_heavy_groups<<<gg, 128, 0, hs>>>(c->hg_start.p, c->hg_member.p, c->hg_count.p, c->h_locus.p, c->h_ref.p, c->h_alt.p, cnts,
-                                           c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+        k_heavy_groups<<<gg, 128, 0, hs>>>(c->hg_start.p, c->hm_ent.p, c->hg_count.p, (uint32_t)c->n_heavy, c->h_locus.p, cnts, c->lnfact.p,
+                                           with_e, c->hv_ll.p, c->hv_e.p, c->hm_val.p);
         c->launches++;
         if (c->n_giant) {
             k_heavy_giant<<<c->n_giant, TPB, 0, hs>>>(c->giant_idx.p, c->n_giant, c->h_locus.p, c->h_ref.p, c->h_alt.p, cnts,
-                                                      c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p);
+                                                      c->lnfact.p, with_e, c->hv_ll.p, c->hv_e.p, c->hm_pos.p, c->hm_val.p);
             c->launches++;
         }
         if (c->n_cells && !use_tiled(c)) {  // the gather kernel adds per-cell sums; the run-stream finish walks the lists itself

@@ -223,7 +223,8 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
                                                        const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                                        const uint32_t* __restrict__ h_alt, EmCounts cnts,
                                                        const double* __restrict__ lnfact, int with_expected,
-                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+                                                       double* __restrict__ hv_ll, double* __restrict__ hv_e,
+                                                       const uint32_t* __restrict__ hm_pos, double* __restrict__ hm_val) {
     const double* __restrict__ lng = cnts.lng;
     const uint32_t lng_n = cnts.lng_n;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -241,6 +242,7 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
         if (!on) {
             hv_ll[h] = 0.0;
             hv_e[h] = 0.0;
+            hm_val[hm_pos[h]] = 0.0;
         } else {
             lgab = ln_gamma_int(((double)a + alpha) + ((double)(n - a) + beta), lng, lng_n);
         }
@@ -270,6 +272,7 @@ __global__ void __launch_bounds__(HEAVY_HB) k_heavy_em(const uint32_t* __restric
             const double own = heavy_ll_k(dn, da, dal, dbe, dlgab, dden, lnfact, lng, lng_n);
             hv_ll[dh] = own;
             hv_e[dh] = ex;
+            hm_val[hm_pos[dh]] = own;
         }
     }
 }
@@ -339,25 +342,27 @@ __global__ void __launch_bounds__(256) k_tables_em(EmCounts cnts, uint32_t n_loc
 // depend only on the locus and the total, so they are evaluated once per group and handed to every member (own log_pmf
 // = ll_alt).  Same expressions, same order as the per-entry chain of k_heavy_em: bit-identical values, ~4x fewer of them
 // at 14 heavy entries per locus (C3: 287 -> measured in profiles/).
-__global__ void __launch_bounds__(128) k_heavy_groups(const uint32_t* __restrict__ hg_start, const uint32_t* __restrict__ hg_member,
-                                                      const uint32_t* __restrict__ hg_count, const uint32_t* __restrict__ h_locus,
-                                                      const uint32_t* __restrict__ h_ref, const uint32_t* __restrict__ h_alt,
-                                                      EmCounts cnts, const double* __restrict__ lnfact, int with_expected,
-                                                      double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+__global__ void __launch_bounds__(128) k_heavy_groups(const uint32_t* __restrict__ hg_start, const uint4* __restrict__ hm_ent,
+                                                      const uint32_t* __restrict__ hg_count, uint32_t n_heavy,
+                                                      const uint32_t* __restrict__ h_locus, EmCounts cnts,
+                                                      const double* __restrict__ lnfact, int with_expected,
+                                                      double* __restrict__ hv_ll, double* __restrict__ hv_e, double* __restrict__ hm_val) {
     const double* __restrict__ lng = cnts.lng;
     const uint32_t lng_n = cnts.lng_n;
-    const uint32_t n_groups = hg_count[0], n_chain = hg_count[1];
+    const uint32_t n_groups = hg_count[0];
     for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < n_groups; g += gridDim.x * blockDim.x) {
-        const uint32_t m0 = hg_start[g], m1 = g + 1 < n_groups ? hg_start[g + 1] : n_chain;
-        const uint32_t h0 = hg_member[m0];
-        const uint64_t n = (uint64_t)h_ref[h0] + (uint64_t)h_alt[h0];
+        const uint32_t m0 = hg_start[g], m1 = g + 1 < n_groups ? hg_start[g + 1] : n_heavy;
+        const uint4 e0 = hm_ent[m0];
+        const uint64_t n = (uint64_t)e0.y + (uint64_t)e0.z;
+        if (n > (uint64_t)HEAVY_CHAIN_MAX) continue;  // deep and giant entries: k_heavy_em / k_heavy_giant
         double alpha, beta, den;
-        em_alpha_beta(cnts, h_locus[h0], &alpha, &beta, &den);
+        em_alpha_beta(cnts, h_locus[e0.w], &alpha, &beta, &den);
         if (!(den == den)) {  // switched off by the -80 rule: contributes nothing
             for (uint32_t m = m0; m < m1; ++m) {
-                const uint32_t h = hg_member[m];
+                const uint32_t h = hm_ent[m].w;
                 hv_ll[h] = 0.0;
                 hv_e[h] = 0.0;
+                hm_val[m] = 0.0;
             }
             continue;
         }
@@ -370,9 +375,11 @@ __global__ void __launch_bounds__(128) k_heavy_groups(const uint32_t* __restrict
             if (with_expected) ex = k == 0 ? 2.0 * v : logsumexp2(ex, 2.0 * v);
         }
         for (uint32_t m = m0; m < m1; ++m) {
-            const uint32_t h = hg_member[m];
-            hv_ll[h] = ll[h_alt[h]];
-            hv_e[h] = ex;
+            const uint4 e = hm_ent[m];
+            const double own = ll[e.z];
+            hv_ll[e.w] = own;
+            hv_e[e.w] = ex;
+            hm_val[m] = own;
         }
     }
 }
@@ -382,7 +389,8 @@ __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict_
                                                      const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                                      const uint32_t* __restrict__ h_alt, EmCounts cnts,
                                                      const double* __restrict__ lnfact, int with_expected,
-                                                     double* __restrict__ hv_ll, double* __restrict__ hv_e) {
+                                                     double* __restrict__ hv_ll, double* __restrict__ hv_e,
+                                                     const uint32_t* __restrict__ hm_pos, double* __restrict__ hm_val) {
     __shared__ double s_m[8], s_s[8];
     const uint32_t h = giant_idx[blockIdx.x];
     double alpha, beta, den;
@@ -391,6 +399,7 @@ __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict_
         if (threadIdx.x == 0) {
             hv_ll[h] = 0.0;
             hv_e[h] = 0.0;
+            hm_val[hm_pos[h]] = 0.0;
         }
         return;
     }
@@ -399,6 +408,7 @@ __global__ void __launch_bounds__(256) k_heavy_giant(const uint32_t* __restrict_
     if (tid == 0) {
         const double v = log_beta_binomial_pmf_den((double)a, (double)r, alpha, beta, ln_binomial(n, a, lnfact), den);
         hv_ll[h] = v;
+        hm_val[hm_pos[h]] = v;
     }
     if (!with_expected) {
         if (tid == 0) hv_e[h] = 0.0;
@@ -813,9 +823,8 @@ template <bool FUSE_FILTER>
 __global__ void __launch_bounds__(256) k_locus_finish(const uint32_t* __restrict__ cls_all, const uint32_t* __restrict__ cls_min,
                                                       uint32_t n_loci, const double* __restrict__ tab, uint8_t* __restrict__ used,
                                                       const uint32_t* __restrict__ excl_bits,
-                                                      const uint32_t* __restrict__ hc_col_ptr, const uint32_t* __restrict__ hc_perm,
-                                                      const uint32_t* __restrict__ h_cell, const uint32_t* __restrict__ h_ref,
-                                                      const uint32_t* __restrict__ h_alt, const double* __restrict__ hv_ll,
+                                                      const uint32_t* __restrict__ hm_col_ptr, const uint4* __restrict__ hm_ent,
+                                                      const double* __restrict__ hm_val,
                                                       const ColEntry* __restrict__ csc, const uint64_t* __restrict__ col_ptr,
                                                       double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int,
                                                       uint32_t* __restrict__ n_used, DeviceStats* __restrict__ st) {
@@ -851,14 +860,14 @@ __global__ void __launch_bounds__(256) k_locus_finish(const uint32_t* __restrict
                 A_maj += (unsigned long long)mj * (unsigned)a;
             }
         }
-        const uint32_t hb = hc_col_ptr[l], he = hc_col_ptr[l + 1];
-        for (uint32_t j = hb; j < he; ++j) {
-            const uint32_t h = hc_perm[j];
-            const uint32_t c = h_cell[h];
-            const bool ex = (excl_bits[c >> 5] >> (c & 31)) & 1u;
-            const double v = hv_ll[h];
-            if (ex) { s_min += v; R_min += h_ref[h]; A_min += h_alt[h]; }
-            else    { s_maj += v; R_maj += h_ref[h]; A_maj += h_alt[h]; }
+        // the locus's heavy entries: one contiguous range in member order ({cell, ref, alt, .} + this pass's log_pmf)
+        const uint32_t hb = hm_col_ptr[l], he = hm_col_ptr[l + 1];
+        for (uint32_t m = hb; m < he; ++m) {
+            const uint4 e = __ldg(hm_ent + m);
+            const bool ex = (excl_bits[e.x >> 5] >> (e.x & 31)) & 1u;
+            const double v = hm_val[m];
+            if (ex) { s_min += v; R_min += e.y; A_min += e.z; }
+            else    { s_maj += v; R_maj += e.y; A_maj += e.z; }
         }
         const bool on = used[l] != 0;  // entries were scored only if the locus was in use (main.rs:556)
         const size_t L = n_loci;

@@ -75,23 +75,45 @@ struct DeepAt {  // beyond the grouped chains, up to the giants
         return n > (uint64_t)HEAVY_CHAIN_TOTAL && n <= (uint64_t)HEAVY_GIANT_TOTAL;
     }
 };
-// (locus, total) key of a heavy entry whose chain is evaluated per group; deeper entries sort behind all of them
+// (locus, total) key of a heavy entry: the sort puts the heavy entries of a locus next to each other (the column pass
+// reads them as one contiguous range) and equal totals of a locus into one group (their chain is evaluated once)
 __global__ void k_heavy_group_keys(const uint32_t* __restrict__ h_locus, const uint32_t* __restrict__ h_ref,
                                    const uint32_t* __restrict__ h_alt, uint32_t n_heavy, unsigned long long* __restrict__ keys,
-                                   uint32_t* __restrict__ idx, uint32_t* __restrict__ n_chain) {
+                                   uint32_t* __restrict__ idx) {
     const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
     if (h >= n_heavy) return;
     const uint64_t n = (uint64_t)h_ref[h] + (uint64_t)h_alt[h];
-    const bool chain = n <= (uint64_t)HEAVY_CHAIN_TOTAL;
-    keys[h] = chain ? (((unsigned long long)h_locus[h] << 8) | (unsigned long long)n) : ~0ull;
+    keys[h] = ((unsigned long long)h_locus[h] << 32) | (unsigned long long)(n > 0xFFFFFFFFull ? 0xFFFFFFFFull : n);
     idx[h] = h;
-    if (chain) atomicAdd(n_chain, 1u);
 }
-// group boundaries of the sorted keys: start[g] for every first member, the count through an atomic-free scan
 struct GroupHead {
     const unsigned long long* keys;
-    __device__ bool operator()(uint32_t i) const { return keys[i] != ~0ull && (i == 0 || keys[i] != keys[i - 1]); }
+    __device__ bool operator()(uint32_t i) const { return i == 0 || keys[i] != keys[i - 1]; }
 };
+// member-order copies: {cell, ref, alt, row-order index} per member, the inverse permutation, per-locus ranges
+__global__ void k_heavy_members(const uint32_t* __restrict__ member, const unsigned long long* __restrict__ keys_sorted,
+                                uint32_t n_heavy, const uint32_t* __restrict__ h_cell, const uint32_t* __restrict__ h_ref,
+                                const uint32_t* __restrict__ h_alt, uint4* __restrict__ ent, uint32_t* __restrict__ pos) {
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n_heavy) return;
+    const uint32_t h = member[m];
+    ent[m] = make_uint4(h_cell[h], h_ref[h], h_alt[h], h);
+    pos[h] = m;
+    (void)keys_sorted;
+}
+__global__ void k_heavy_col_ptr(const unsigned long long* __restrict__ keys_sorted, uint32_t n_heavy, uint32_t n_loci,
+                                uint32_t* __restrict__ col_ptr) {
+    const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l > n_loci) return;
+    const unsigned long long want = (unsigned long long)l << 32;
+    uint32_t lo = 0, hi = n_heavy;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (keys_sorted[mid] < want) lo = mid + 1;
+        else hi = mid;
+    }
+    col_ptr[l] = lo;
+}
 struct ToU64 {
     __device__ uint64_t operator()(uint32_t v) const { return (uint64_t)v; }
 };
@@ -450,19 +472,23 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         k_heavy_perm<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(hcpos.p, csc_src.p, hpos.p, n_heavy, c->hc_perm.p);
         c->launches += 4;
     }
-    // chain entries (total <= HEAVY_CHAIN_TOTAL) grouped by (locus, total)
+    // heavy entries in (locus, total) order: groups of equal keys, member-order copies, per-locus ranges
     CLX_CUDA(c, c->hg_member.alloc(n_heavy));
     CLX_CUDA(c, c->hg_start.alloc((size_t)n_heavy + 1));
     CLX_CUDA(c, c->hg_count.alloc(2));
+    CLX_CUDA(c, c->hm_ent.alloc((size_t)n_heavy + 1));
+    CLX_CUDA(c, c->hm_pos.alloc((size_t)n_heavy + 1));
+    CLX_CUDA(c, c->hm_val.alloc((size_t)n_heavy + 1));
+    CLX_CUDA(c, c->hm_col_ptr.alloc((size_t)n_loci + 2));
     CLX_CUDA(c, cudaMemsetAsync(c->hg_count.p, 0, 8, s));
+    CLX_CUDA(c, cudaMemsetAsync(c->hm_col_ptr.p, 0, c->hm_col_ptr.bytes(), s));
     if (n_heavy) {
         DevBuf<unsigned long long> gk, gk_sorted;
         DevBuf<uint32_t> gi;
         CLX_CUDA(c, gk.alloc(n_heavy));
         CLX_CUDA(c, gk_sorted.alloc(n_heavy));
         CLX_CUDA(c, gi.alloc(n_heavy));
-        k_heavy_group_keys<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(c->h_locus.p, c->h_ref.p, c->h_alt.p, n_heavy, gk.p, gi.p,
-                                                                   c->hg_count.p + 1);
+        k_heavy_group_keys<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(c->h_locus.p, c->h_ref.p, c->h_alt.p, n_heavy, gk.p, gi.p);
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, gk.p, gk_sorted.p, gi.p, c->hg_member.p, (int)n_heavy, 0, 64, s));
         CLX_CUDA(c, tmp.alloc(tmp_bytes));
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, gk.p, gk_sorted.p, gi.p, c->hg_member.p, (int)n_heavy, 0, 64, s));
@@ -471,7 +497,10 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         CLX_CUDA(c, cub::DeviceSelect::If(nullptr, tmp_bytes, counting, c->hg_start.p, c->hg_count.p, (int)n_heavy, gh, s));
         CLX_CUDA(c, tmp.alloc(tmp_bytes));
         CLX_CUDA(c, cub::DeviceSelect::If(tmp.p, tmp_bytes, counting, c->hg_start.p, c->hg_count.p, (int)n_heavy, gh, s));
-        c->launches += 7;
+        k_heavy_members<<<(n_heavy + TPB - 1) / TPB, TPB, 0, s>>>(c->hg_member.p, gk_sorted.p, n_heavy, c->h_cell.p, c->h_ref.p, c->h_alt.p,
+                                                                c->hm_ent.p, c->hm_pos.p);
+        k_heavy_col_ptr<<<(n_loci + 1 + TPB - 1) / TPB, TPB, 0, s>>>(gk_sorted.p, n_heavy, n_loci, c->hm_col_ptr.p);
+        c->launches += 9;
     }
     // entries too deep for the batched heavy kernel get a CTA each (em_kernels.cuh: k_heavy_giant)
     c->n_giant = 0;
