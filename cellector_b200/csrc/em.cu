@@ -98,9 +98,9 @@ template <bool FUSE>
 void launch_locus_classes(clx_ctx* c) {
     const uint32_t N = c->n_cells, L = c->n_loci;
     if (N) {
-        const uint32_t words = (N + 31u) / 32u;
-        k_excl_delta<<<(unsigned)(((uint64_t)words * 32 + TPB - 1) / TPB), TPB, 0, c->stream>>>(c->csr.p, c->row_ptr.p, N, c->excl_bits.p,
-                                                                                            c->excl_prev.p, c->cls_min.p);
+        k_excl_delta<<<(unsigned)(((uint64_t)c->n_seg * 32 + TPB - 1) / TPB), TPB, 0, c->stream>>>(c->csr.p, c->row_ptr.p, c->seg_row.p,
+                                                                                             c->seg_first.p, c->n_seg, c->excl_bits.p,
+                                                                                             c->excl_prev.p, c->cls_min.p);
         c->launches++;
     }
     if (L == 0) return;
@@ -109,7 +109,7 @@ void launch_locus_classes(clx_ctx* c) {
     k_locus_finish<FUSE><<<(L + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->cls_all.p, c->cls_min.p, L, c->tab.p, c->loci_used.p, c->excl_bits.p,
                                                                     c->hm_col_ptr.p, c->hm_ent.p, c->hm_val.p, c->csc.p, c->col_ptr.p,
                                                                     out_ll, out_int, c->n_used.p,
-                                                                    c->d_stats.p);
+                                                                    c->d_stats.p, c->excl_prev.p, (N + 31u) / 32u);
     c->launches++;
 }
 

@@ -789,31 +789,27 @@ __global__ void __launch_bounds__(256) k_columns(const ColEntry* __restrict__ cs
 // (integer atomics, so the result does not depend on the order), which after the first iterations is a handful of rows
 // instead of every nonzero of the matrix.
 //
-// One warp per 32-cell bitmap word; the changed cells of the word are taken one after the other, the row spread over
-// the lanes.  The warp owns prev[word] and brings it up to date itself.
+// One warp per row SEGMENT (the segments of the gather scoring kernel: at most ROW_SEG entries, so the deep cells of a
+// skewed matrix are spread over many warps); a warp whose cell did not change leaves at once.  prev is brought up to date
+// by k_locus_finish, which runs after every warp here has read it.
 __global__ void __launch_bounds__(256) k_excl_delta(const RowEntry* __restrict__ csr, const uint64_t* __restrict__ row_ptr,
-                                                    uint32_t n_cells, const uint32_t* __restrict__ bits,
-                                                    uint32_t* __restrict__ prev, uint32_t* __restrict__ cls_min) {
-    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
-    if (w >= (n_cells + 31u) / 32u) return;
-    const uint32_t now = bits[w];
-    uint32_t diff = now ^ prev[w];
-    if (diff == 0) return;
-    __syncwarp();
-    if (lane == 0) prev[w] = now;
-    while (diff) {
-        const uint32_t b = (uint32_t)__ffs((int)diff) - 1u;
-        diff &= diff - 1u;
-        const uint32_t cell = w * 32u + b;
-        if (cell >= n_cells) break;
-        const uint32_t delta = ((now >> b) & 1u) ? 1u : 0xFFFFFFFFu;  // joined the excluded set : left it
-        const uint64_t e = row_ptr[cell + 1];
-        for (uint64_t i = row_ptr[cell] + lane; i < e; i += 32) {
-            const RowEntry x = csr[i];
-            const uint32_t n = (uint32_t)x.ref + (uint32_t)x.alt;
-            const uint32_t cls = (n - 1u) < (uint32_t)K_LIGHT ? (uint32_t)tab_slot((int)x.alt, (int)n) : (uint32_t)CLS_OTHER;
-            atomicAdd(&cls_min[(size_t)x.locus * CLS_STRIDE + cls], delta);
-        }
+                                                    const uint32_t* __restrict__ seg_row, const uint32_t* __restrict__ seg_first,
+                                                    uint32_t n_seg, const uint32_t* __restrict__ bits,
+                                                    const uint32_t* __restrict__ prev, uint32_t* __restrict__ cls_min) {
+    const uint32_t sg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (sg >= n_seg) return;
+    const uint32_t cell = seg_row[sg];
+    const uint32_t now = (bits[cell >> 5] >> (cell & 31u)) & 1u, was = (prev[cell >> 5] >> (cell & 31u)) & 1u;
+    if (now == was) return;
+    const uint32_t delta = now ? 1u : 0xFFFFFFFFu;  // joined the excluded set : left it
+    const uint64_t rb = row_ptr[cell], re = row_ptr[cell + 1];
+    const uint64_t b = rb + (uint64_t)(sg - seg_first[cell]) * ROW_SEG;
+    const uint64_t e = b + ROW_SEG < re ? b + ROW_SEG : re;
+    for (uint64_t i = b + lane; i < e; i += 32) {
+        const RowEntry x = csr[i];
+        const uint32_t n = (uint32_t)x.ref + (uint32_t)x.alt;
+        const uint32_t cls = (n - 1u) < (uint32_t)K_LIGHT ? (uint32_t)tab_slot((int)x.alt, (int)n) : (uint32_t)CLS_OTHER;
+        atomicAdd(&cls_min[(size_t)x.locus * CLS_STRIDE + cls], delta);
     }
 }
 
@@ -827,8 +823,11 @@ __global__ void __launch_bounds__(256) k_locus_finish(const uint32_t* __restrict
                                                       const double* __restrict__ hm_val,
                                                       const ColEntry* __restrict__ csc, const uint64_t* __restrict__ col_ptr,
                                                       double* __restrict__ loc_ll, unsigned long long* __restrict__ loc_int,
-                                                      uint32_t* __restrict__ n_used, DeviceStats* __restrict__ st) {
+                                                      uint32_t* __restrict__ n_used, DeviceStats* __restrict__ st,
+                                                      uint32_t* __restrict__ excl_prev, uint32_t n_words) {
     const uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    // cls_min now matches excl_bits (k_excl_delta has finished): remember the set it matches
+    for (uint32_t i = l; i < n_words; i += gridDim.x * blockDim.x) excl_prev[i] = excl_bits[i];
     bool filtered = false, in_use = false;
     if (l < n_loci) {
         uint32_t ca[CLS_STRIDE], cm[CLS_STRIDE];
