@@ -99,6 +99,7 @@ struct clx_ctx {
            win_off_tot_int = 0;
     std::vector<void*> peer_win;          // [world] every rank's window as mapped here (own window at [rank])
     clx::DevBuf<void*> d_peer_win;        // the same table in device memory
+    bool p2p_failed = false;              // a peer-memory barrier timed out: the ranks are out of step until clx_load_coo maps again
     unsigned long long p2p_epoch = 0;     // one per iteration; barrier flags only grow
 
     // --- matrix (load.cu)

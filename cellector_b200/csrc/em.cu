@@ -436,6 +436,8 @@ int enqueue_iteration(clx_ctx* c) {
 
 int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
     if (!c->loaded) return fail(c, CLX_ERR_STATE, "clx_em_iteration before clx_load_coo");
+    if (c->p2p_failed)
+        return fail(c, CLX_ERR_NCCL, "a peer-memory barrier timed out earlier: the ranks are out of step, load again on every rank");
     NvtxRange nvtx("clx:em_iteration");
     cudaStream_t s = c->stream;
     c->h_params->iqr_multiple = iqr_multiple;
@@ -477,7 +479,10 @@ int em_iteration(clx_ctx* c, double iqr_multiple, clx_iter_stats* out) {
     CLX_CUDA(c, cudaGetLastError());
     phase_resolve(c);
     const DeviceStats& st = *c->h_stats;
-    if (st.pad) return fail(c, CLX_ERR_NCCL, "a peer-memory barrier timed out (a rank is missing or failed)");
+    if (st.pad) {
+        c->p2p_failed = true;
+        return fail(c, CLX_ERR_NCCL, "a peer-memory barrier timed out (a rank is missing or failed)");
+    }
     if (st.nan_flag) return fail(c, CLX_ERR_NAN, "NaN normalized log likelihood (the reference panics in argsort, main.rs:504)");
     c->n_excluded_global = st.n_excluded;
     if (out) {

@@ -35,13 +35,14 @@ __global__ void k_p2p_barrier(unsigned char* const* __restrict__ win, int rank, 
     const int t = threadIdx.x;
     if (t >= world) return;
     const unsigned long long epoch = reinterpret_cast<const unsigned long long*>(win[rank] + off_counters)[8];
+    const long long limit = (long long)reinterpret_cast<const unsigned long long*>(win[rank] + off_counters)[9];
     __threadfence_system();  // everything this rank stored before the barrier is visible before the flag is
     unsigned long long* theirs = reinterpret_cast<unsigned long long*>(win[t]) + (size_t)phase * world + rank;
     st_release_sys(theirs, epoch);
     const unsigned long long* mine = reinterpret_cast<const unsigned long long*>(win[rank]) + (size_t)phase * world + t;
     const long long t0 = clock64();
     while (ld_acquire_sys(mine) < epoch) {
-        if (clock64() - t0 > 4000000000ll) {  // ~2 s at 1.9 GHz: a peer died or never got here
+        if (clock64() - t0 > limit) {  // a peer died or never got here
             atomicOr(err, 1u);
             break;
         }
@@ -119,18 +120,32 @@ int p2p_setup(clx_ctx* c, size_t L, size_t max_local) {
     c->win_off_tot_ll = c->win_off_part_int + up(8 * L * 8 + 8);
     c->win_off_tot_int = c->win_off_tot_ll + up(2 * L * 8 + 8);
     const size_t need = c->win_off_tot_int + up(8 * L * 8 + 8);
+    // barrier time limit in SM cycles, slot 9 of the counters block (slot 8 is the epoch)
+    auto put_limit = [&]() -> int {
+        const char* tenv = getenv("CLX_P2P_TIMEOUT_MS");
+        const double ms = tenv && *tenv ? atof(tenv) : 2000.0;
+        int khz = 1900000;
+        cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, c->device);
+        const unsigned long long cycles = (unsigned long long)(ms * (double)khz);
+        CLX_CUDA(c, cudaMemcpyAsync((unsigned char*)c->win + c->win_off_counters + 9 * 8, &cycles, 8, cudaMemcpyHostToDevice, c->stream));
+        CLX_CUDA(c, cudaStreamSynchronize(c->stream));
+        return CLX_OK;
+    };
     // a window that is already mapped everywhere and large enough is kept (mapping costs milliseconds): the layout
     // depends only on global sizes, flags and epoch simply continue.  Unanimous or not at all.
     DevBuf<unsigned long long> sync;
     CLX_CUDA(c, sync.alloc(2));
     {
-        const unsigned long long keep = (c->p2p && want && c->win && need <= c->win_bytes) ? 1ull : 0ull;
+        const unsigned long long keep = (c->p2p && !c->p2p_failed && want && c->win && need <= c->win_bytes) ? 1ull : 0ull;
         CLX_CUDA(c, cudaMemcpyAsync(sync.p, &keep, 8, cudaMemcpyHostToDevice, c->stream));
         CLX_TRY(comm_allreduce_u64(c, sync.p, 1));
         unsigned long long n_keep = 0;
         CLX_CUDA(c, cudaMemcpyAsync(&n_keep, sync.p, 8, cudaMemcpyDeviceToHost, c->stream));
         CLX_CUDA(c, cudaStreamSynchronize(c->stream));
-        if (n_keep == (unsigned long long)c->world) return CLX_OK;
+        if (n_keep == (unsigned long long)c->world) {
+            c->p2p_failed = false;
+            return put_limit();
+        }
     }
     // peers may still be reading the old window: everyone closes its mappings, then a collective, then the free
     for (size_t r = 0; r < c->peer_win.size(); ++r)
@@ -203,7 +218,8 @@ int p2p_setup(clx_ctx* c, size_t L, size_t max_local) {
     CLX_CUDA(c, cudaStreamSynchronize(c->stream));
     c->p2p_epoch = 0;
     c->p2p = true;
-    return CLX_OK;
+    c->p2p_failed = false;
+    return put_limit();
 }
 
 int p2p_barrier(clx_ctx* c, int phase) {
