@@ -4,7 +4,7 @@ TAG=$1; WL=${2:-C2}
 mkdir -p gpurun_out
 B="python bench.py --workload $WL --no-e2e --no-cpu-baseline --no-large --slice-cells 0 --steps 3 --warmup 3"
 timeout 400 $B > gpurun_out/${TAG}_${WL}_plain.json 2> gpurun_out/${TAG}_${WL}_plain.err || { echo "plain run failed"; exit 1; }
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv -k regex:^k_ --log-file gpurun_out/${TAG}_launches_${WL}.csv $B > gpurun_out/${TAG}_${WL}_ncu.log 2>&1; echo "ncu rc=$?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv -k "regex:^(k_|Device)" --log-file gpurun_out/${TAG}_launches_${WL}.csv $B > gpurun_out/${TAG}_${WL}_ncu.log 2>&1; echo "ncu rc=$?"
 python - <<PY
 import csv, collections
 rows = [r for r in csv.reader(open("gpurun_out/${TAG}_launches_${WL}.csv")) if len(r) > 5]
