@@ -197,6 +197,8 @@ struct clx_ctx {
     bool capturing = false, graph_events_fresh = false;
     std::vector<clx::PendingEvent> graph_events;      // phase events recorded by graph nodes (CLX_FLAG_PROFILE)
     clx::DeviceStats* h_stats = nullptr;              // pinned
+    unsigned char* h_stage = nullptr;                 // pinned staging of the result getters (one sync per call instead of one per array)
+    size_t h_stage_bytes = 0;
     clx::DevBuf<uint8_t> flush_buf;
     uint32_t max_local_cells = 0;
 

@@ -24,13 +24,20 @@ inline unsigned grid_for(uint64_t n, int tpb = TPB, unsigned cap = 148u * 16u) {
     return (unsigned)(g > cap ? cap : g);
 }
 
-__global__ void k_locus_hist(const uint32_t* __restrict__ locus, const uint32_t* __restrict__ cell,
-                             const uint32_t* __restrict__ ref, const uint32_t* __restrict__ alt, uint64_t nnz0,
-                             uint32_t n_loci0, uint32_t n_cells, unsigned int* __restrict__ cnt,
-                             unsigned int* __restrict__ err) {
+// every cell index in range (the cell array arrives on the side stream while the locus filter runs)
+__global__ void k_cell_check(const uint32_t* __restrict__ cell, uint64_t nnz0, uint32_t n_cells, unsigned int* __restrict__ err) {
+    bool bad = false;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < nnz0; i += (uint64_t)gridDim.x * blockDim.x)
+        bad |= cell[i] >= n_cells;
+    if (bad) atomicOr(err, 1u);
+}
+
+__global__ void k_locus_hist(const uint32_t* __restrict__ locus, const uint32_t* __restrict__ ref,
+                             const uint32_t* __restrict__ alt, uint64_t nnz0, uint32_t n_loci0,
+                             unsigned int* __restrict__ cnt, unsigned int* __restrict__ err) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < nnz0; i += (uint64_t)gridDim.x * blockDim.x) {
         const uint32_t l = locus[i];
-        if (l >= n_loci0 || cell[i] >= n_cells) {
+        if (l >= n_loci0) {
             atomicOr(err, 1u);
             continue;
         }
@@ -119,9 +126,10 @@ struct ToU64 {
 };
 
 __global__ void k_cell_keys(const uint32_t* __restrict__ kept_idx, const uint32_t* __restrict__ cell, uint64_t nnz,
-                            uint32_t* __restrict__ keys, uint32_t* __restrict__ row_cnt) {
+                            uint32_t n_cells, uint32_t* __restrict__ keys, uint32_t* __restrict__ row_cnt) {
     for (uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < nnz; k += (uint64_t)gridDim.x * blockDim.x) {
-        const uint32_t c = cell[kept_idx[k]];
+        uint32_t c = cell[kept_idx[k]];
+        if (c >= n_cells) c = n_cells - 1;  // k_cell_check has flagged it; the load fails at its next host sync
         keys[k] = c;
         atomicAdd(&row_cnt[c], 1u);
     }
@@ -247,6 +255,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     // every cub call below takes a 32-bit signed item count
     if (nnz0 >= 0x7FFFFFFFull) return fail(c, CLX_ERR_ARG, "more than 2^31-2 nonzeros per GPU: shard the cells over more ranks");
     if (nnz0 > 0 && (!locus || !cell || !ref)) return fail(c, CLX_ERR_ARG, "null COO array");
+    if (nnz0 > 0 && n_cells == 0) return fail(c, CLX_ERR_ARG, "COO coordinate out of range (locus >= n_loci0 or cell >= n_cells)");
     c->n_cells = n_cells;
     c->n_loci0 = n_loci0;
     c->nnz0 = nnz0;
@@ -276,7 +285,6 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         // cudaMemcpyDefault: the caller's arrays may be pageable or pinned host memory, or device memory (a host that
         // parses or generates on the GPU); the copy engine picks the path from the pointer
         CLX_CUDA(c, cudaMemcpyAsync(d_locus.p, locus, nnz0 * 4, cudaMemcpyDefault, s));
-        CLX_CUDA(c, cudaMemcpyAsync(d_cell.p, cell, nnz0 * 4, cudaMemcpyDefault, s));
         if (alt) {
             CLX_CUDA(c, cudaMemcpyAsync(d_ref.p, ref, nnz0 * 4, cudaMemcpyDefault, s));
             CLX_CUDA(c, cudaMemcpyAsync(d_alt.p, alt, nnz0 * 4, cudaMemcpyDefault, s));
@@ -287,6 +295,12 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
             k_unpack_counts<<<grid_for(nnz0), TPB, 0, s>>>(d_packed.p, nnz0, d_ref.p, d_alt.p);
             c->launches++;
         }
+        // the cell indices travel on the side stream, after the arrays the locus filter needs have landed: the filter,
+        // the scan and the compaction of the kept entries run while they are still on the wire
+        CLX_CUDA(c, cudaEventRecord(c->ev_fork, s));
+        CLX_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+        CLX_CUDA(c, cudaMemcpyAsync(d_cell.p, cell, nnz0 * 4, cudaMemcpyDefault, c->stream2));
+        CLX_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
     }
 
     clk.mark("COO to device");
@@ -301,7 +315,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     CLX_CUDA(c, cudaMemsetAsync(err.p, 0, 4, s));
     CLX_CUDA(c, cudaMemsetAsync(flag.p, 0, flag.bytes(), s));
     if (nnz0) {
-        k_locus_hist<<<grid_for(nnz0), TPB, 0, s>>>(d_locus.p, d_cell.p, d_ref.p, d_alt.p, nnz0, n_loci0, n_cells, cnt.p, err.p);
+        k_locus_hist<<<grid_for(nnz0), TPB, 0, s>>>(d_locus.p, d_ref.p, d_alt.p, nnz0, n_loci0, cnt.p, err.p);
         c->launches++;
     }
     CLX_TRY(comm_allreduce_u32(c, cnt.p, 2 * (size_t)n_loci0));
@@ -348,7 +362,12 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     c->nnz = nnz;
 
     clk.mark("compaction");
-    // ---- CSR: stable sort by cell
+    // ---- CSR: stable sort by cell (the cell indices have arrived by now, or we wait for them here)
+    if (nnz0) {
+        CLX_CUDA(c, cudaStreamWaitEvent(s, c->ev_join, 0));
+        k_cell_check<<<grid_for(nnz0), TPB, 0, s>>>(d_cell.p, nnz0, n_cells, err.p);
+        c->launches++;
+    }
     DevBuf<uint32_t> keys, keys_sorted, csr_src, row_cnt;
     CLX_CUDA(c, keys.alloc(nnz));
     CLX_CUDA(c, keys_sorted.alloc(nnz));
@@ -357,7 +376,7 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
     CLX_CUDA(c, cudaMemsetAsync(row_cnt.p, 0, row_cnt.bytes(), s));
     CLX_CUDA(c, c->row_ptr.alloc((size_t)n_cells + 1));
     if (nnz) {
-        k_cell_keys<<<grid_for(nnz), TPB, 0, s>>>(kept_idx.p, d_cell.p, nnz, keys.p, row_cnt.p);
+        k_cell_keys<<<grid_for(nnz), TPB, 0, s>>>(kept_idx.p, d_cell.p, nnz, n_cells, keys.p, row_cnt.p);
         c->launches++;
         const int eb = bits_for(n_cells);
         CLX_CUDA(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys_sorted.p, kept_idx.p, csr_src.p, (int)nnz, 0, eb, s));
@@ -427,7 +446,9 @@ int load_coo(clx_ctx* c, uint64_t nnz0, uint32_t n_loci0, uint32_t n_cells, cons
         }
         unsigned long long h_max = 0;
         CLX_CUDA(c, cudaMemcpyAsync(&h_max, d_max.p, 8, cudaMemcpyDeviceToHost, s));
+        CLX_CUDA(c, cudaMemcpyAsync(&h_err, err.p, 4, cudaMemcpyDeviceToHost, s));
         CLX_CUDA(c, cudaStreamSynchronize(s));
+        if (h_err) return fail(c, CLX_ERR_ARG, "COO coordinate out of range (locus >= n_loci0 or cell >= n_cells)");
         const unsigned long long want = 2 * h_max + 16, cap = 1ull << 22;  // at most 32 MB
         c->lng_n = (uint32_t)(want < cap ? want : cap);
         CLX_CUDA(c, c->lng.alloc(c->lng_n));

@@ -124,6 +124,13 @@ def test_out_of_range_coordinate_is_an_error(libs):
     with gpu:
         with pytest.raises(RuntimeError, match="out of range"):
             gpu.load_cell_data([0, 9], [0, 0], [1, 1], [1, 1], n_loci0=5, n_cells=3)
+        with pytest.raises(RuntimeError, match="out of range"):  # a cell index, at a locus the filter drops anyway
+            gpu.load_cell_data([0, 1], [0, 3], [1, 1], [1, 1], n_loci0=5, n_cells=3)
+        with pytest.raises(RuntimeError, match="out of range"):  # a cell index among the kept entries
+            gpu.load_cell_data([0] * 9, [0, 1, 2, 0, 1, 2, 0, 1, 7], [2] * 9, [2] * 9, n_loci0=2, n_cells=3)
+        with pytest.raises(RuntimeError, match="out of range"):
+            gpu.load_cell_data([0], [0], [1], [1], n_loci0=5, n_cells=0)
+        gpu.load_cell_data([0, 1], [0, 0], [5, 5], [5, 5], n_loci0=5, n_cells=3)  # the context is still usable
 
 
 def test_final_locus_counts_and_reset(libs):
