@@ -443,6 +443,7 @@ def run_large(args, dd, lib, name, rank, world, local_rank, balanced=True, slice
     d = sd.generate(cfg, int(cut[rank]), int(cut[rank + 1]), device=f"cuda:{local_rank}")
     torch.cuda.synchronize()
     gen_s = time.perf_counter() - t0
+    torch.cuda.empty_cache()  # the generator's temporaries go back to the driver: the library allocates from its own pool
     ctx = Cellector(local_rank, args.flags, lib)
     collective = world > 1
     if collective:
