@@ -15,21 +15,25 @@
 //     index inside the staged tile (locus_local * 9 + slot(alt, total));
 //   * a cell belongs to ONE warp of the CTA for the whole pass (cell_local % W): its shared-memory accumulator is
 //     updated with plain read-modify-writes, no atomics, and there is no CTA barrier between tiles;
-//   * the runs of one (cell block, warp, tile) SUB-UNIT are ordered by length and taken 32 at a time: a GROUP.  Lane l
-//     sums run l of the group in registers; the group runs for its longest run (shorter runs are padded with the
-//     all-zero slot) and ends with ONE warp-wide accumulator update.  With W = 16 and 4096-cell blocks a sub-unit
-//     pools 256 runs, so the runs of a group have almost equal lengths (~17 % padded lookups at 5 entries per run);
-//   * inside a group the runs are dealt to lanes so that the 8 lanes of a quarter warp own accumulator slots in
-//     distinct 16-byte bank groups (the update is two conflict-free 128-bit shared-memory instructions);
-//   * the words of a lane are consecutive in its own 16-byte pieces: chunk c of a warp is 32 x 16 bytes, read with
-//     one coalesced LDG.128 per lane, three chunks ahead of the one being summed (registers, no staging ring);
-//     control is in-band and warp-uniform: a HEADER word opens a group (accumulator index of the lane's cell, "this
-//     sub-unit starts the next tile", "nothing follows"), the last entry word of a group carries a flag;
+//   * the runs of one (cell block, warp, tile) SUB-UNIT are dealt into GROUPS of 32, one run per lane: lane 8j + v
+//     always gets a run whose cell has accumulator class v = (cell_local / W) & 7, the runs of a class are sorted by
+//     length and taken 4 at a time, so the runs of a group have almost equal lengths and the 8 lanes of a quarter warp
+//     own accumulator slots in distinct 16-byte bank groups (the update at the end of a group is conflict-free);
+//   * a group runs for its longest run, in PIECES of 4 steps; word 0 of a piece carries its number of valid steps,
+//     word 1 the "group ends here" flag (both warp-uniform), so the decoder is straight-line code per piece.  A lane
+//     with nothing to do in a step reads one of 8 all-zero slots behind the tile, the one in a bank group no other
+//     lane of its quarter warp uses in that step; the ORDER in which a lane takes its run's entries is chosen at load
+//     time (k_sub_fill) so that the lookups of a quarter warp spread over the bank groups;
+//   * chunk c of a warp is 32 x 16 bytes (8 words per lane), read with one coalesced LDG.128 per lane, STREAM_PF chunks
+//     ahead of the one being summed (registers, reloaded in place).  A CELL chunk carries the accumulator indices of the
+//     lane's next 8 runs (and "this sub-unit starts the next tile"); ENTRY chunks are two pieces;
 //   * sub-units are numbered warp-major ((cell block, warp), then tile) and start on chunk boundaries, so the words a
 //     warp consumes over the consecutive tiles of a work item are ONE range of chunks;
-//   * a work ITEM = one cell block x a range of consecutive tiles; the CTA keeps the block's accumulators in shared
-//     memory across the range and writes one partial per cell at the end; k_score_finish adds the partials of a
-//     cell block in item order (fixed order: deterministic), appends the heavy values and normalises.
+//   * a work ITEM = one cell block x a range of (tile, warp) sub-units; the sequence of all sub-units is cut into one
+//     contiguous piece of equal cost per SM (build_tiled), static, no queue.  The CTA keeps the block's accumulators in
+//     shared memory across the range and writes one partial per cell at the end; k_score_finish adds the partials of
+//     a cell block in item order (fixed order: deterministic), adds the heavy values and normalises;
+//   * matrices with less than one entry per cell and tile do not get a stream at all: the gather kernel scores them.
 #include <cub/cub.cuh>
 #include <stdio.h>
 #include <string.h>
