@@ -76,6 +76,8 @@ ABI = {
     "score_bytes": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "flush_l2": (C.c_int, [C.c_void_p]),
+    "locus_filter_static": (C.c_int, [C.c_int, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
+                                      C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "alloc_pinned": (C.c_void_p, [C.c_size_t]),
     "free_pinned": (None, [C.c_void_p]),
 }

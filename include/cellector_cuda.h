@@ -150,6 +150,24 @@ int clx_final_locus_counts(clx_ctx* ctx, uint64_t* minority_ref_alt, uint64_t* m
 void* clx_alloc_pinned(size_t bytes);
 void clx_free_pinned(void* p);
 
+/* The locus filter alone (the rule of get_loci_used), allocating nothing.  This entry point has NO counterpart in the
+ * reference: it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Its scratch (two u32 counters per locus) is a
+ * file-scope static __device__ array inside the library, sized for CLX_STATIC_MAX_LOCI loci: 16 MiB + 256 B that every
+ * GPU the library is used on holds until the process exits.  n_loci0 > CLX_STATIC_MAX_LOCI is rejected with
+ * CLX_ERR_ARG.  It needs no context; errors are read with clx_last_error(NULL).
+ *   d_locus, d_ref, d_alt   DEVICE arrays of nnz0 entries on `device` (same meaning as in clx_load_coo)
+ *   d_used                  DEVICE array of n_loci0 bytes: 1 where the locus passes min_ref / min_alt, else 0
+ *   d_n_used                DEVICE word: number of loci kept (may be NULL)
+ *   stream                  cudaStream_t of `device` to enqueue on (NULL = the default stream); synchronised on return
+ * The call makes `device` current, and calls no cudaMalloc, cudaFree or allocating library routine.  All calls on a GPU
+ * share the one array (it is cleared at the start of each call): calls that overlap on the same GPU race and must be
+ * serialised by the caller. */
+#define CLX_STATIC_MAX_LOCI (1u << 21)
+int clx_locus_filter_static(int device, uint64_t nnz0, uint32_t n_loci0, const uint32_t* d_locus,
+                            const uint32_t* d_ref, const uint32_t* d_alt, uint32_t min_ref, uint32_t min_alt,
+                            uint8_t* d_used, uint32_t* d_n_used, void* stream);
+
 /* Profiling helpers (not part of the reference surface). */
 int clx_get_phase_ms(clx_ctx* ctx, int phase, double* total_ms, uint64_t* launches);
 /* Switch CLX_FLAG_PROFILE on or off after clx_create (the phase events are extra nodes of the iteration graph and
