@@ -76,6 +76,8 @@ ABI = {
     "score_bytes": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "flush_l2": (C.c_int, [C.c_void_p]),
+    "soup_em": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double),
+                          C.POINTER(C.c_uint32)]),
     "locus_filter_static": (C.c_int, [C.c_int, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
                                       C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "alloc_pinned": (C.c_void_p, [C.c_size_t]),
@@ -216,6 +218,17 @@ class CtxApi:
         mj = np.empty((self.n_loci0, 2), np.uint64)
         self._check(self._f("final_locus_counts")(self._h, _ptr(mn), _ptr(mj)), "final_locus_counts")
         return mn, mj
+
+    # souporcell's EM (souporcell/souporcell/src/main.rs:109-186) from the caller's initial centers [k][n_loci_used]
+    def soup_em(self, centers_init):
+        cen = np.ascontiguousarray(centers_init, dtype=np.float32)
+        k = cen.shape[0]
+        assert cen.shape == (k, self.n_loci_used)
+        lp = np.empty((self.n_cells, k), np.float64)
+        out = np.empty((k, self.n_loci_used), np.float64)
+        loss, it = C.c_double(0), C.c_uint32(0)
+        self._check(self._f("soup_em")(self._h, k, _ptr(cen), _ptr(lp), _ptr(out), C.byref(loss), C.byref(it)), "soup_em")
+        return dict(log_probs=lp, centers=out, loss=loss.value, iterations=int(it.value))
 
     # cellector() driver loop (main.rs:36-46)
     def run_em(self, iqr_multiple=5.0, max_iterations=1000):

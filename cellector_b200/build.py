@@ -16,7 +16,7 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcellector_cuda.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
-CU_SOURCES = ["abi.cu", "load.cu", "em.cu", "comm.cu", "tiled.cu", "p2p.cu", "noalloc.cu"]
+CU_SOURCES = ["abi.cu", "load.cu", "em.cu", "comm.cu", "tiled.cu", "p2p.cu", "noalloc.cu", "soup.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
     "-fmad=false",                      # Rust never contracts a*b+c; parity needs the same (numerics.cuh)

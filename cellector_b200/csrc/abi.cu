@@ -271,6 +271,7 @@ void clx_destroy(clx_ctx* c) {
     if (c->ev_iter_b) cudaEventDestroy(c->ev_iter_b);
     if (c->h_stats) cudaFreeHost(c->h_stats);
     if (c->h_stage) cudaFreeHost(c->h_stage);
+    if (c->h_soup) cudaFreeHost(c->h_soup);
     if (c->stream2) {
         cudaStreamSynchronize(c->stream2);
         cudaStreamDestroy(c->stream2);

@@ -199,6 +199,7 @@ struct clx_ctx {
     clx::DeviceStats* h_stats = nullptr;              // pinned
     unsigned char* h_stage = nullptr;                 // pinned staging of the result getters (one sync per call instead of one per array)
     size_t h_stage_bytes = 0;
+    double* h_soup = nullptr;                         // pinned, 64 bytes: loss / refusal flags of clx_soup_em (soup.cu)
     clx::DevBuf<uint8_t> flush_buf;
     uint32_t max_local_cells = 0;
 

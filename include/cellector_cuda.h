@@ -145,6 +145,23 @@ int clx_posteriors(clx_ctx* ctx, double posterior_threshold, uint32_t min_loci_u
  * [n_loci0][2] = (ref, alt).  Replaces the third text pass of load_mtx_final. */
 int clx_final_locus_counts(clx_ctx* ctx, uint64_t* minority_ref_alt, uint64_t* majority_ref_alt);
 
+/* souporcell's k-cluster EM (the tool cellector_pipeline.py:233-240 runs right after cellector; replaces
+ * EM(), souporcell/souporcell/src/main.rs:109-186, with binomial_loss :199-213, normalize_in_log_with_temp :230-242,
+ * update_centers_average :273-280, update_final :244-251) on the matrix loaded with clx_load_coo (same locus filter as
+ * souporcell's load_cell_data :436-440 with its default min_*_umis = 0).  One run from the caller's initial centers
+ * (the draws of init_cluster_centers_uniform, main.rs:354-364, stay on the host side with the host's generator):
+ *   k                 clusters, 1..8
+ *   centers_init      HOST array [k][n_loci_used], f32 in (0, 1)
+ *   log_probs         HOST array [n_cells][k]: the log_binoms of the last iteration (main.rs:164); may be NULL
+ *   centers_out       HOST array [k][n_loci_used]: centers after the last update; may be NULL
+ *   total_log_loss    loss of the last iteration (main.rs:167), what souporcell_main compares between restarts (:73)
+ *   iterations        EM iterations run (all temperature steps)
+ * Sums are f64 in a fixed order (the reference: f32, serial).  Refused with CLX_ERR_ARG: a (locus, cell) coordinate
+ * stored more than once (the reference keeps its last line, main.rs:421) and counts above 65534.  With cells sharded
+ * over ranks (clx_comm_init) every rank calls it with the same centers; sums and loss are all-reduced. */
+int clx_soup_em(clx_ctx* ctx, uint32_t k, const float* centers_init, double* log_probs, double* centers_out,
+                double* total_log_loss, uint32_t* iterations);
+
 /* Page-locked host memory for the COO arrays handed to clx_load_coo (what a host parser fills; replaces the
  * row-list Vec growth of load_data.rs:165-173).  Works without a context; returns NULL on failure. */
 void* clx_alloc_pinned(size_t bytes);

@@ -1,0 +1,95 @@
+"""souporcell's k-cluster EM on the GPU (clx_soup_em, through the C ABI) against the CPU oracle
+(oracle/souporcell_oracle.cc) on the same seeded inputs and the same initial centers.
+
+Tolerances: the CUDA path states the reference's formulas in f64 with fixed-order sums; against the oracle's f64
+statement everything must agree to 1e-9 relative (iteration count and loss trace included); against the oracle's f32
+statement (the reference's own arithmetic: f32 variables, serial sums) the results must agree within f32 rounding and
+every clearly assigned cell must get the same cluster."""
+import numpy as np
+import pytest
+
+from cellector_b200 import soup, synth
+from tests.soup_oracle import SoupOracle
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "k2": (synth.SynthConfig(n_cells=1200, n_loci=4000, density=0.04, minority_frac=0.3, seed=51), 2),
+    "k3_deep": (synth.SynthConfig(n_cells=900, n_loci=3000, density=0.05, minority_frac=0.4, seed=52, deep_frac=0.05,
+                                  deep_mean=40.0, doublet_frac=0.05), 3),
+    "k5_skewed": (synth.SynthConfig(n_cells=1500, n_loci=5000, density=0.02, minority_frac=0.2, seed=53, row_sigma=1.5), 5),
+    "k8": (synth.SynthConfig(n_cells=500, n_loci=2000, density=0.05, minority_frac=0.5, seed=54), 8),
+    "k1": (synth.SynthConfig(n_cells=300, n_loci=1000, density=0.05, minority_frac=0.1, seed=55), 1),
+}
+
+
+def _both(d, k, seed=4):
+    from cellector_b200 import Cellector
+    with Cellector(0) as gpu, SoupOracle() as orc:
+        n_used, _ = gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+        assert orc.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)[0] == n_used
+        np.testing.assert_array_equal(gpu.locus_ids(), orc.locus_ids())
+        init = soup.init_cluster_centers_uniform(n_used, k, seed)
+        g = gpu.soup_em(init)
+        g2 = gpu.soup_em(init)  # a second run on the same context: same bits (fixed-order sums, no atomics)
+        o64 = orc.soup_em(init, precise=True)
+        o32 = orc.soup_em(init, precise=False)
+    assert g2["iterations"] == g["iterations"] and g2["loss"] == g["loss"]
+    np.testing.assert_array_equal(g2["log_probs"], g["log_probs"])
+    return g, o64, o32
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_soup_em_matches_oracle(name):
+    cfg, k = CASES[name]
+    g, o64, o32 = _both(synth.generate(cfg), k)
+    assert g["iterations"] == o64["iterations"] and 9 <= g["iterations"] < 1000
+    np.testing.assert_allclose(g["loss"], o64["loss"], rtol=1e-10)
+    np.testing.assert_allclose(g["log_probs"], o64["log_probs"], rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(g["centers"], o64["centers"], rtol=1e-9)
+    # the reference's f32 arithmetic
+    assert abs(g["iterations"] - o32["iterations"]) <= 2
+    np.testing.assert_allclose(g["loss"], o32["loss"], rtol=1e-4)
+    # five clusters on two individuals split arbitrarily: the EM is ill-conditioned there and f32 rounding moves
+    # single cells' log-probabilities by a few tenths (oracle f32 against oracle f64: 0.27), not their loss or assignment
+    np.testing.assert_allclose(g["log_probs"], o32["log_probs"], rtol=2e-3, atol=0.5 if name == "k5_skewed" else 1e-2)
+    if k > 1:
+        s = np.sort(g["log_probs"], axis=1)
+        clear = (s[:, -1] - s[:, -2]) > 0.1
+        assert (np.argmax(g["log_probs"], axis=1) == np.argmax(o32["log_probs"], axis=1))[clear].all()
+
+
+def test_soup_restarts_recover_the_two_individuals():
+    """souporcell_main (main.rs:62-106): best of a few restarts separates the two simulated individuals"""
+    from cellector_b200 import Cellector
+    cfg = synth.SynthConfig(n_cells=2000, n_loci=6000, density=0.04, minority_frac=0.25, seed=56)
+    d = synth.generate(cfg)
+    with Cellector(0) as gpu:
+        gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+        best = soup.souporcell_main(gpu, k=2, restarts=4, seed=4)
+    truth = np.asarray(d.is_minority, dtype=np.int64)
+    agree = (best["assignment"] == truth).mean()
+    assert max(agree, 1.0 - agree) > 0.98   # cluster ids are arbitrary
+
+
+def test_soup_refuses_duplicated_coordinates_and_clipped_counts():
+    from cellector_b200 import Cellector
+    d = synth.generate(synth.SynthConfig(n_cells=200, n_loci=600, density=0.08, minority_frac=0.3, seed=57))
+    with Cellector(0) as gpu:
+        # one line of a locus that passes the filter, stored a second time at the end of the file
+        kept = (np.bincount(d.locus[d.ref > 0], minlength=d.n_loci) >= 1) & (np.bincount(d.locus[d.alt > 0], minlength=d.n_loci) >= 1)
+        i = int(np.flatnonzero(kept[d.locus])[5])
+        locus = np.concatenate([d.locus, d.locus[i:i + 1]])
+        cell = np.concatenate([d.cell, d.cell[i:i + 1]])
+        ref = np.concatenate([d.ref, d.ref[i:i + 1]])
+        alt = np.concatenate([d.alt, d.alt[i:i + 1]])
+        n_used, _ = gpu.load_cell_data(locus, cell, ref, alt, d.n_loci, d.n_cells, 1, 1)
+        with pytest.raises(RuntimeError, match="stored more than once"):
+            gpu.soup_em(soup.init_cluster_centers_uniform(n_used, 2, 4))
+        ref2 = d.ref.copy()
+        ref2[i] = 70000
+        n_used, _ = gpu.load_cell_data(d.locus, d.cell, ref2, d.alt, d.n_loci, d.n_cells, 1, 1)
+        with pytest.raises(RuntimeError, match="65534"):
+            gpu.soup_em(soup.init_cluster_centers_uniform(n_used, 2, 4))
+        with pytest.raises(RuntimeError, match=r"\[1, 8\]"):
+            gpu.soup_em(soup.init_cluster_centers_uniform(n_used, 9, 4))
