@@ -78,6 +78,8 @@ ABI = {
     "flush_l2": (C.c_int, [C.c_void_p]),
     "soup_em": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double),
                           C.POINTER(C.c_uint32)]),
+    "soup_restarts": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                C.c_void_p, C.POINTER(C.c_uint32)]),
     "locus_filter_static": (C.c_int, [C.c_int, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
                                       C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "alloc_pinned": (C.c_void_p, [C.c_size_t]),
@@ -229,6 +231,19 @@ class CtxApi:
         loss, it = C.c_double(0), C.c_uint32(0)
         self._check(self._f("soup_em")(self._h, k, _ptr(cen), _ptr(lp), _ptr(out), C.byref(loss), C.byref(it)), "soup_em")
         return dict(log_probs=lp, centers=out, loss=loss.value, iterations=int(it.value))
+
+    # best of several restarts (souporcell_main, main.rs:69-88); centers_init [n_restarts][k][n_loci_used]
+    def soup_restarts(self, centers_init):
+        cen = np.ascontiguousarray(centers_init, dtype=np.float32)
+        n, k = cen.shape[0], cen.shape[1]
+        assert cen.shape == (n, k, self.n_loci_used)
+        lp = np.empty((self.n_cells, k), np.float64)
+        out = np.empty((k, self.n_loci_used), np.float64)
+        losses, its, best = np.empty(n, np.float64), np.empty(n, np.uint32), C.c_uint32(0)
+        self._check(self._f("soup_restarts")(self._h, k, n, _ptr(cen), _ptr(lp), _ptr(out), _ptr(losses), _ptr(its),
+                                             C.byref(best)), "soup_restarts")
+        return dict(log_probs=lp, centers=out, losses=losses, iterations=its, best=int(best.value),
+                    loss=float(losses[best.value]))
 
     # cellector() driver loop (main.rs:36-46)
     def run_em(self, iqr_multiple=5.0, max_iterations=1000):

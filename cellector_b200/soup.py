@@ -17,13 +17,9 @@ def init_cluster_centers_uniform(n_loci: int, k: int, seed: int, restart: int = 
 
 def souporcell_main(ctx, k: int, restarts: int = 100, seed: int = 4):
     """Best of `restarts` EM runs and the argmax assignment (main.rs:69-106).  `ctx` is a loaded context with a
-    `soup_em` method (cellector_b200.Cellector)."""
-    best = None
-    for r in range(restarts):
-        res = ctx.soup_em(init_cluster_centers_uniform(ctx.n_loci_used, k, seed, r))
-        res["restart"] = r
-        if best is None or res["loss"] > best["loss"]:  # main.rs:73
-            best = res
+    `soup_restarts` method (cellector_b200.Cellector): the restarts share the passes over the matrix on the GPU."""
+    init = np.stack([init_cluster_centers_uniform(ctx.n_loci_used, k, seed, r) for r in range(restarts)])
+    best = ctx.soup_restarts(init)
     # first maximum wins, like the strict > of main.rs:96-99
     best["assignment"] = np.argmax(best["log_probs"], axis=1).astype(np.uint32)
     return best

@@ -162,6 +162,16 @@ int clx_final_locus_counts(clx_ctx* ctx, uint64_t* minority_ref_alt, uint64_t* m
 int clx_soup_em(clx_ctx* ctx, uint32_t k, const float* centers_init, double* log_probs, double* centers_out,
                 double* total_log_loss, uint32_t* iterations);
 
+/* Best of n_restarts such runs (replaces the restart loop of souporcell_main, main.rs:69-88, which gives one restart
+ * at a time to each rayon thread): restarts are run R at a time over the same pass of the matrix (R = 8 for k <= 2,
+ * else 16 / k), each with its own loop state, results identical to n_restarts calls of clx_soup_em.
+ *   centers_init      HOST array [n_restarts][k][n_loci_used]
+ *   log_probs, centers_out   of the best restart (strictly largest total_log_loss, the first one on ties: main.rs:73, 84)
+ *   losses, iterations       HOST arrays [n_restarts]; may be NULL
+ *   best              index of the best restart; may be NULL */
+int clx_soup_restarts(clx_ctx* ctx, uint32_t k, uint32_t n_restarts, const float* centers_init, double* log_probs,
+                      double* centers_out, double* losses, uint32_t* iterations, uint32_t* best);
+
 /* Page-locked host memory for the COO arrays handed to clx_load_coo (what a host parser fills; replaces the
  * row-list Vec growth of load_data.rs:165-173).  Works without a context; returns NULL on failure. */
 void* clx_alloc_pinned(size_t bytes);

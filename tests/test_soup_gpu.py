@@ -72,6 +72,30 @@ def test_soup_restarts_recover_the_two_individuals():
     assert max(agree, 1.0 - agree) > 0.98   # cluster ids are arbitrary
 
 
+@pytest.mark.parametrize("k,n_restarts", [(2, 11), (3, 7), (8, 3)])
+def test_soup_restarts_equal_single_runs(k, n_restarts):
+    """restarts run R at a time (R = 8, 5, 2 here; the last batch is partly empty): every restart's loss and iteration
+    count equal the oracle's f64 run from the same centers, and the best one is the reference's choice"""
+    from cellector_b200 import Cellector
+    d = synth.generate(synth.SynthConfig(n_cells=700, n_loci=2500, density=0.04, minority_frac=0.35, seed=58, deep_frac=0.02))
+    with Cellector(0) as gpu, SoupOracle() as orc:
+        n_used, _ = gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+        orc.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+        init = np.stack([soup.init_cluster_centers_uniform(n_used, k, 4, r) for r in range(n_restarts)])
+        g = gpu.soup_restarts(init)
+        single = gpu.soup_em(init[g["best"]])
+        runs = [orc.soup_em(init[r], precise=True) for r in range(n_restarts)]
+    assert [int(x) for x in g["iterations"]] == [r["iterations"] for r in runs]
+    np.testing.assert_allclose(g["losses"], [r["loss"] for r in runs], rtol=1e-10)
+    want_best = int(np.argmax([r["loss"] for r in runs]))  # first maximum, like the strict > of main.rs:73
+    assert g["best"] == want_best
+    np.testing.assert_allclose(g["log_probs"], runs[want_best]["log_probs"], rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(g["centers"], runs[want_best]["centers"], rtol=1e-9)
+    # a restart's result does not depend on the slot or the batch it ran in
+    np.testing.assert_array_equal(single["log_probs"], g["log_probs"])
+    assert single["loss"] == g["loss"]
+
+
 def test_soup_refuses_duplicated_coordinates_and_clipped_counts():
     from cellector_b200 import Cellector
     d = synth.generate(synth.SynthConfig(n_cells=200, n_loci=600, density=0.08, minority_frac=0.3, seed=57))

@@ -34,6 +34,17 @@ with Cellector(0) as gpu:
     sec = sum(r["seconds"] for r in runs)
     out["gpu_us_per_iteration"] = 1e6 * sec / it
     out["gpu_entries_per_s"] = nnz * it / sec
+    # restarts batched over the same passes of the matrix (clx_soup_restarts)
+    n_batch = int(os.environ.get("SOUP_BENCH_RESTARTS", "16"))
+    init = np.stack([soup.init_cluster_centers_uniform(n_used, k, 4, r) for r in range(n_batch)])
+    gpu.soup_restarts(init[:2])
+    t = time.perf_counter()
+    rb = gpu.soup_restarts(init)
+    dt = time.perf_counter() - t
+    itb = int(rb["iterations"].sum())
+    out["gpu_batched"] = dict(restarts=n_batch, seconds=dt, restart_iterations=itb, us_per_restart_iteration=1e6 * dt / itb,
+                              entries_per_s=nnz * itb / dt, best=rb["best"], best_loss=rb["loss"],
+                              iterations=[int(x) for x in rb["iterations"]])
     g0 = gpu.soup_em(soup.init_cluster_centers_uniform(n_used, k, 4, 0))
 with SoupOracle() as orc:
     orc.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
@@ -49,4 +60,5 @@ out["parity"] = dict(iterations_gpu=g0["iterations"], iterations_f64=o64["iterat
                      loss_rel_vs_f32=abs(g0["loss"] - o32["loss"]) / abs(o32["loss"]),
                      same_assignment_as_f32=float((np.argmax(g0["log_probs"], 1) == np.argmax(o32["log_probs"], 1)).mean()))
 out["speedup_per_iteration"] = out["cpu_f32"]["us_per_iteration"] / out["gpu_us_per_iteration"]
+out["speedup_per_restart_iteration_batched"] = out["cpu_f32"]["us_per_iteration"] / out["gpu_batched"]["us_per_restart_iteration"]
 print(json.dumps(out))
