@@ -8,14 +8,23 @@
 //             [--interquartile_range_multiple 5] [--min_alleles_posterior 5] [--expected_percent_minority P]
 //             [--min_loci_for_assignment 30]
 //   additive flags (not in the reference): --device N, --threads N, --max_iterations N, --timing_json FILE,
-//             --no_iteration_files (skip the per-iteration diagnostics), --parse_only (parser self-check)
+//             --no_iteration_files (skip the per-iteration diagnostics), --parse_only (parser self-check),
+//             --gpus N: cells sharded over N GPUs (devices --device .. --device + N - 1).  The process parses the
+//             matrix once, then forks N - 1 workers BEFORE any CUDA call; every process owns one GPU and one context
+//             (the library's model: one process per GPU, clx_comm_init between them), takes a contiguous range of
+//             cells with an equal share of the nonzeros, and rank 0 writes every file from per-cell arrays the ranks
+//             fill in shared memory.
 //
 // There is no CPU fallback: without a CUDA device the run fails in clx_create.
+#include <sys/mman.h>
+#include <sys/prctl.h>
 #include <sys/stat.h>
 #include <sys/wait.h>
+#include <signal.h>
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -50,14 +59,30 @@ struct Params {  // main.rs:613-627
     uint64_t min_loci_used = 30;
     // additive
     int device = 0;
+    int gpus = 1;
     unsigned threads = 0;
     uint64_t max_iterations = 0;  // 0 = no cap, like the reference (main.rs:42-46)
     std::string timing_json;
     bool no_iteration_files = false, parse_only = false;
 };
 
+// --gpus N: what the ranks share (one anonymous MAP_SHARED mapping made before the fork)
+struct TeamShared {
+    std::atomic<uint32_t> arrived, generation;  // barrier
+    std::atomic<uint32_t> id_ready;             // rank 0 has written nccl_id
+    std::atomic<uint32_t> failed;               // a rank died: everybody leaves
+    unsigned char nccl_id[128];
+};
+TeamShared* g_team = nullptr;
+int g_rank = 0, g_world = 1;
+std::vector<pid_t> g_children;
+
 [[noreturn]] void die(const std::string& msg, int code = 101) {  // 101 = exit status of a Rust panic
-    fprintf(stderr, "cellector: %s\n", msg.c_str());
+    if (g_world > 1) fprintf(stderr, "cellector (rank %d): %s\n", g_rank, msg.c_str());
+    else fprintf(stderr, "cellector: %s\n", msg.c_str());
+    if (g_team) g_team->failed.store(1);
+    if (g_rank != 0) _exit(code);  // a worker must not flush stdio buffers inherited from the parent
+    for (const pid_t pid : g_children) kill(pid, SIGKILL);
     exit(code);
 }
 
@@ -96,7 +121,7 @@ void usage() {
         "        --min_alleles_posterior <n>          (default 5)\n"
         "        --expected_percent_minority <p>\n"
         "        --min_loci_for_assignment <n>        (default 30)\n"
-        "        --device <n> --threads <n> --max_iterations <n> --timing_json <file> --no_iteration_files --parse_only\n",
+        "        --device <n> --gpus <n> --threads <n> --max_iterations <n> --timing_json <file> --no_iteration_files --parse_only\n",
         stderr);
 }
 
@@ -139,7 +164,7 @@ Params load_params(int argc, char** argv) {
     }
     static const char* known[] = {"output_directory", "ref", "alt", "barcodes", "min_alt", "min_ref", "ground_truth", "vcf",
                                   "posterior_threshold", "interquartile_range_multiple", "min_alleles_posterior",
-                                  "expected_percent_minority", "min_loci_for_assignment", "device", "threads", "max_iterations",
+                                  "expected_percent_minority", "min_loci_for_assignment", "device", "gpus", "threads", "max_iterations",
                                   "timing_json", "no_iteration_files", "parse_only"};
     for (const auto& e : kv) {
         bool ok = false;
@@ -173,6 +198,8 @@ Params load_params(int argc, char** argv) {
     }
     if (kv.count("min_loci_for_assignment")) p.min_loci_used = parse_u64_arg("min_loci_for_assignment", kv["min_loci_for_assignment"]);
     if (kv.count("device")) p.device = (int)parse_u64_arg("device", kv["device"]);
+    if (kv.count("gpus")) p.gpus = (int)parse_u64_arg("gpus", kv["gpus"]);
+    if (p.gpus < 1 || p.gpus > 64) die("--gpus must be between 1 and 64", 1);
     if (kv.count("threads")) p.threads = (unsigned)parse_u64_arg("threads", kv["threads"]);
     if (kv.count("max_iterations")) p.max_iterations = parse_u64_arg("max_iterations", kv["max_iterations"]);
     if (kv.count("timing_json")) p.timing_json = kv["timing_json"];
@@ -305,6 +332,32 @@ double binomial_pmf(double p, uint64_t n, uint64_t k) {
     return exp(lb + (double)k * log(p) + (double)(n - k) * log(1.0 - p));
 }
 
+// all ranks arrive, or the run ends: a rank that died has set `failed`; rank 0 also notices a worker that crashed
+void team_barrier() {
+    if (g_world == 1) return;
+    const uint32_t gen = g_team->generation.load();
+    if (g_team->arrived.fetch_add(1) + 1 == (uint32_t)g_world) {
+        g_team->arrived.store(0);
+        g_team->generation.fetch_add(1);
+        return;
+    }
+    for (uint64_t spins = 0; g_team->generation.load() == gen; ++spins) {
+        if (g_team->failed.load()) die("another rank failed");
+        if (g_rank == 0 && (spins & 255) == 255) {
+            int st = 0;
+            const pid_t pid = waitpid(-1, &st, WNOHANG);
+            if (pid > 0 && !(WIFEXITED(st) && WEXITSTATUS(st) == 0)) die("a worker process ended abnormally");
+        }
+        usleep(20);
+    }
+}
+
+void* shared_alloc(size_t bytes) {
+    void* p = mmap(nullptr, bytes ? bytes : 1, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+    if (p == MAP_FAILED) die("mmap of the shared result arrays failed");
+    return p;
+}
+
 }  // namespace
 
 int run(const Params& params);
@@ -417,7 +470,7 @@ int run(const Params& params) {
     int create_rc = CLX_OK;
     std::string create_err;
     std::thread cuda_init;
-    if (!params.parse_only)
+    if (!params.parse_only && params.gpus == 1)
         cuda_init = std::thread([&] {
             create_rc = clx_create(&ctx, params.device, params.has_vcf ? CLX_FLAG_KEEP_COO : 0u);
             if (create_rc != CLX_OK) create_err = clx_last_error(nullptr);
@@ -442,17 +495,103 @@ int run(const Params& params) {
     std::vector<VcfLocus> vcf_data;
     if (params.has_vcf) vcf_data = load_vcf_data(params);
 
+    // ---- per-cell result arrays: plain memory on one GPU, a shared mapping the ranks fill side by side on several
+    const size_t N = n_cells;
+    const size_t cell_bytes = N * (7 * sizeof(double) + sizeof(uint32_t) + 3) + 64;
+    unsigned char* cell_mem = params.gpus > 1 ? (unsigned char*)shared_alloc(cell_bytes) : (unsigned char*)calloc(cell_bytes, 1);
+    if (!cell_mem) die("out of host memory");
+    double* const ll = (double*)cell_mem;
+    double *const ell = ll + N, *const norm = ell + N, *const post = norm + N, *const dpost = post + N, *const ll_maj = dpost + N,
+                  *const ll_min = ll_maj + N;
+    uint32_t* const nloci = (uint32_t*)(ll_min + N);
+    uint8_t *const label = (uint8_t*)(nloci + N), *const anomaly = label + N, *const qual = anomaly + N;
+
+    // ---- --gpus N: contiguous cell ranges with equal shares of the nonzeros, one process per GPU
+    uint32_t c0 = 0, c1 = n_cells;  // this rank's cells
+    if (params.gpus > 1) {
+        if (n_cells < (uint32_t)params.gpus) die("--gpus: fewer cells than GPUs");
+        std::vector<uint64_t> start(n_cells + 1, 0);
+        for (uint64_t i = 0; i < nnz0; ++i) {
+            if (sink.cell[i] >= n_cells) die("cell index out of range in the matrix");
+            start[sink.cell[i] + 1]++;
+        }
+        for (uint32_t c = 0; c < n_cells; ++c) start[c + 1] += start[c];
+        std::vector<uint32_t> bound(params.gpus + 1, n_cells);
+        bound[0] = 0;
+        for (int r = 1; r < params.gpus; ++r) {
+            const uint64_t want = nnz0 / params.gpus * r;
+            uint32_t b = (uint32_t)(std::lower_bound(start.begin(), start.end(), want) - start.begin());
+            b = std::max(b, bound[r - 1] + 1);                                  // every rank gets a cell
+            bound[r] = std::min(b, n_cells - (uint32_t)(params.gpus - r));
+        }
+        g_team = (TeamShared*)shared_alloc(sizeof(TeamShared));
+        new (g_team) TeamShared();
+        g_world = params.gpus;
+        fflush(stdout);
+        fflush(stderr);
+        for (int r = 1; r < params.gpus; ++r) {
+            const pid_t pid = fork();  // no CUDA call has been made yet: every process initialises its own GPU
+            if (pid < 0) die("fork failed");
+            if (pid == 0) {
+                g_rank = r;
+                g_children.clear();
+                prctl(PR_SET_PDEATHSIG, SIGKILL);
+                break;
+            }
+            g_children.push_back(pid);
+        }
+        c0 = bound[g_rank];
+        c1 = bound[g_rank + 1];
+    }
+    const bool root = g_rank == 0;
+    const uint32_t n_local = c1 - c0;
+
     // ---- device: load_cell_data
     const double t_join0 = now_s();
-    cuda_init.join();
+    if (cuda_init.joinable()) cuda_init.join();
+    else if (!params.parse_only) {
+        create_rc = clx_create(&ctx, params.device + g_rank, params.has_vcf ? CLX_FLAG_KEEP_COO : 0u);
+        if (create_rc != CLX_OK) create_err = clx_last_error(nullptr);
+    }
     const double t_cuda_wait = now_s() - t_join0;
     if (create_rc != CLX_OK) die("clx_create failed: " + create_err);
+    uint32_t* lcoo = nullptr;  // this rank's entries, file order kept, cell ids rank-local
+    uint64_t nnz0_local = nnz0;
+    if (g_world > 1) {
+        if (root) {
+            CLX(clx_nccl_unique_id(g_team->nccl_id));
+            g_team->id_ready.store(1);
+        }
+        for (uint64_t spins = 0; !g_team->id_ready.load(); ++spins) {
+            if (g_team->failed.load() || spins > 3000000) die("no NCCL id from rank 0");
+            usleep(100);
+        }
+        CLX(clx_comm_init(ctx, g_rank, g_world, g_team->nccl_id));
+        nnz0_local = 0;
+        for (uint64_t i = 0; i < nnz0; ++i) nnz0_local += sink.cell[i] >= c0 && sink.cell[i] < c1;
+        lcoo = (uint32_t*)malloc((size_t)std::max<uint64_t>(nnz0_local, 1) * 4 * sizeof(uint32_t));
+        if (!lcoo) die("out of host memory");
+        uint64_t k = 0;
+        for (uint64_t i = 0; i < nnz0; ++i)
+            if (sink.cell[i] >= c0 && sink.cell[i] < c1) {
+                lcoo[k] = sink.locus[i];
+                lcoo[nnz0_local + k] = sink.cell[i] - c0;
+                lcoo[2 * nnz0_local + k] = sink.ref[i];
+                lcoo[3 * nnz0_local + k] = sink.alt[i];
+                ++k;
+            }
+    }
     const double t_load0 = now_s();
     uint32_t n_loci = 0;
     uint64_t nnz = 0;
     if (params.min_ref > 0xFFFFFFFFull || params.min_alt > 0xFFFFFFFFull) die("min_ref / min_alt out of range");
-    CLX(clx_load_coo(ctx, nnz0, n_loci0, n_cells, sink.locus, sink.cell, sink.ref, sink.alt, (uint32_t)params.min_ref,
-                     (uint32_t)params.min_alt, &n_loci, &nnz));
+    if (g_world > 1)
+        CLX(clx_load_coo(ctx, nnz0_local, n_loci0, n_local, lcoo, lcoo + nnz0_local, lcoo + 2 * nnz0_local, lcoo + 3 * nnz0_local,
+                         (uint32_t)params.min_ref, (uint32_t)params.min_alt, &n_loci, &nnz));
+    else
+        CLX(clx_load_coo(ctx, nnz0, n_loci0, n_cells, sink.locus, sink.cell, sink.ref, sink.alt, (uint32_t)params.min_ref,
+                         (uint32_t)params.min_alt, &n_loci, &nnz));
+    free(lcoo);
     std::vector<uint32_t> locus_ids(n_loci);
     CLX(clx_get_locus_ids(ctx, locus_ids.data()));
     free(coo);
@@ -460,8 +599,6 @@ int run(const Params& params) {
     const double t_load1 = now_s();
 
     // ---- cellector(): the EM loop (main.rs:36-46)
-    std::vector<double> ll(n_cells), ell(n_cells), norm(n_cells);
-    std::vector<uint32_t> nloci(n_cells);
     std::vector<double> l_min(n_loci), l_maj(n_loci);
     std::vector<uint32_t> c_min(n_loci), c_maj(n_loci);
     std::vector<uint64_t> r_min(n_loci), a_min(n_loci), r_maj(n_loci), a_maj(n_loci);
@@ -478,12 +615,18 @@ int run(const Params& params) {
         const double t1 = now_s();
         t_em += t1 - t0;
         // main.rs:338-339
-        printf("detected %llu new anomylous cells and rescued %llu cells to the majority in iteration %llu\n",
-               (unsigned long long)st.n_new_excluded, (unsigned long long)st.n_rescued, (unsigned long long)(iteration + 1));
-        printf("median normalized log likelihood %s with interquartile range %s, threshold %s\n", f64_str(st.median).c_str(),
-               f64_str(st.iqr).c_str(), f64_str(st.threshold).c_str());
+        if (root) {
+            printf("detected %llu new anomylous cells and rescued %llu cells to the majority in iteration %llu\n",
+                   (unsigned long long)st.n_new_excluded, (unsigned long long)st.n_rescued, (unsigned long long)(iteration + 1));
+            printf("median normalized log likelihood %s with interquartile range %s, threshold %s\n", f64_str(st.median).c_str(),
+                   f64_str(st.iqr).c_str(), f64_str(st.threshold).c_str());
+        }
         const bool files = !params.no_iteration_files;
-        if (files || st.n_loci_filtered > 0) {
+        if (files) {  // every rank puts its cells' vectors side by side; rank 0 writes them below
+            CLX(clx_get_cell_vectors(ctx, ll + c0, ell + c0, nloci + c0, norm + c0, nullptr));
+            team_barrier();
+        }
+        if (root && (files || st.n_loci_filtered > 0)) {  // the per-locus vectors are the same on every rank
             clx_locus_arrays la;
             memset(&la, 0, sizeof(la));
             la.ll_minority = l_min.data();
@@ -553,8 +696,7 @@ int run(const Params& params) {
                 }
             }
         }
-        if (files) {  // output_iteration_tsv (main.rs:349-366)
-            CLX(clx_get_cell_vectors(ctx, ll.data(), ell.data(), nloci.data(), norm.data(), nullptr));
+        if (files && root) {  // output_iteration_tsv (main.rs:349-366)
             FileWriter w(params.output_directory + "/iteration_" + std::to_string(iteration) + ".tsv");
             w.buf += "cell_id\tbarcode\tassignment\tlog_likelihood\texpected_log_likelihood\tnum_loci_used\n";
             for (uint32_t c = 0; c < n_cells; ++c) {
@@ -575,21 +717,29 @@ int run(const Params& params) {
         if (!st.any_change) break;
         if (params.max_iterations && iteration >= params.max_iterations) break;
     }
-    if (params.no_iteration_files) CLX(clx_get_cell_vectors(ctx, nullptr, nullptr, nloci.data(), norm.data(), nullptr));
+    if (params.no_iteration_files) CLX(clx_get_cell_vectors(ctx, nullptr, nullptr, nloci + c0, norm + c0, nullptr));
 
     // ---- calculate_posteriors (main.rs:228-280) + assignment rule
     const double t_post0 = now_s();
-    std::vector<double> post(n_cells), dpost(n_cells), ll_maj(n_cells), ll_min(n_cells);
-    std::vector<uint8_t> label(n_cells), anomaly(n_cells), qual(n_cells);
     if (params.min_loci_used > 0xFFFFFFFFull) die("min_loci_for_assignment out of range");
-    CLX(clx_posteriors(ctx, params.posterior_threshold, (uint32_t)params.min_loci_used, post.data(), dpost.data(), ll_maj.data(),
-                       ll_min.data(), label.data(), anomaly.data(), qual.data()));
+    CLX(clx_posteriors(ctx, params.posterior_threshold, (uint32_t)params.min_loci_used, post + c0, dpost + c0, ll_maj + c0,
+                       ll_min + c0, label + c0, anomaly + c0, qual + c0));
     const double t_post1 = now_s();
 
     // ---- output_final_vcf (main.rs:52-131)
-    if (params.has_vcf) {
-        std::vector<uint64_t> mn(2 * (size_t)n_loci0 + 2), mj(2 * (size_t)n_loci0 + 2);
+    std::vector<uint64_t> mn, mj;
+    if (params.has_vcf) {  // the counts are summed over the ranks inside the call: every rank makes it
+        mn.resize(2 * (size_t)n_loci0 + 2);
+        mj.resize(2 * (size_t)n_loci0 + 2);
         CLX(clx_final_locus_counts(ctx, mn.data(), mj.data()));
+    }
+    team_barrier();  // every rank's posterior arrays are in place
+    if (!root) {     // workers are done: rank 0 writes the remaining files
+        clx_destroy(ctx);
+        fflush(nullptr);
+        _exit(0);
+    }
+    if (params.has_vcf) {
         FileWriter w(params.output_directory + "/cellector.vcf");
         size_t record = 0;
         const double ambient = 0.03, gt_threshold = 0.99;
@@ -675,11 +825,17 @@ int run(const Params& params) {
         b += "{\"parse_s\": " + f64_str(t_parse1 - t_parse0) + ", \"cuda_init_wait_s\": " + f64_str(t_cuda_wait) + ", \"load_s\": " + f64_str(t_load1 - t_load0) + ", \"em_s\": " + f64_str(t_em) +
              ", \"posterior_s\": " + f64_str(t_post1 - t_post0) + ", \"write_s\": " + f64_str(t_write) + ", \"total_s\": " + f64_str(t_end - t_start) +
              ", \"iterations\": " + std::to_string(iteration) + ", \"nnz0\": " + std::to_string(nnz0) + ", \"nnz_used\": " + std::to_string(nnz) +
-             ", \"n_loci_used\": " + std::to_string(n_loci) + ", \"n_cells\": " + std::to_string(n_cells) + ", \"threads\": " +
+             ", \"n_loci_used\": " + std::to_string(n_loci) + ", \"n_cells\": " + std::to_string(n_cells) + ", \"gpus\": " +
+             std::to_string(g_world) + ", \"threads\": " +
              std::to_string(params.threads) + ", \"gpu_launches\": " + std::to_string(launches) + ", \"em_device_ms\": [";
         for (size_t i = 0; i < em_device_ms.size(); ++i) b += (i ? ", " : "") + f64_str(em_device_ms[i]);
         b += "]}\n";
     }
     clx_destroy(ctx);
+    for (const pid_t pid : g_children) {
+        int st = 0;
+        waitpid(pid, &st, 0);
+        if (!(WIFEXITED(st) && WEXITSTATUS(st) == 0)) die("a worker process ended abnormally");
+    }
     return 0;
 }

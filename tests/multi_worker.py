@@ -57,6 +57,7 @@ def main():
         alt = np.concatenate([s[5] for s in shards])
         order = np.lexsort((cell, locus))  # file order: sorted by (locus, cell)
         n_total = sum(s[1] for s in shards)
+        whole = (locus[order].astype(np.uint32), cell[order].astype(np.uint32), ref[order], alt[order], d.n_loci, n_total)
         orc = Oracle()
         o = orc.load_cell_data(locus[order].astype(np.uint32), cell[order].astype(np.uint32), ref[order], alt[order],
                                d.n_loci, n_total)
@@ -96,6 +97,28 @@ def main():
         for k in ("ll_major", "ll_minor"):
             parity.assert_close(gp[k], op[k], f"posterior {k}")
         print(f"MULTI_OK case={case} world={world} iterations={n_it} cells={len(gp['label'])} CLX_P2P={os.environ.get('CLX_P2P')}", flush=True)
+    # souporcell's EM on the same shards (soup.cu: partial sums and the loss are all-reduced), single run and batched
+    from cellector_b200 import soup
+    inits = np.stack([soup.init_cluster_centers_uniform(gpu.n_loci_used, 2, 4, r) for r in range(3)])
+    s1 = gpu.soup_em(inits[0])
+    s3 = gpu.soup_restarts(inits)
+    alls = [None] * world
+    dist.all_gather_object(alls, (s1["log_probs"], s3["log_probs"]))
+    if rank == 0:
+        from tests.soup_oracle import SoupOracle
+        with SoupOracle() as so:
+            so.load_cell_data(*whole)
+            runs = [so.soup_em(inits[r], precise=True) for r in range(3)]
+        assert s1["iterations"] == runs[0]["iterations"], (s1["iterations"], runs[0]["iterations"])
+        np.testing.assert_allclose(s1["loss"], runs[0]["loss"], rtol=1e-10)
+        np.testing.assert_allclose(np.concatenate([a[0] for a in alls]), runs[0]["log_probs"], rtol=1e-9, atol=1e-9)
+        np.testing.assert_allclose(s1["centers"], runs[0]["centers"], rtol=1e-9)
+        assert [int(x) for x in s3["iterations"]] == [r["iterations"] for r in runs]
+        np.testing.assert_allclose(s3["losses"], [r["loss"] for r in runs], rtol=1e-10)
+        b = int(np.argmax([r["loss"] for r in runs]))
+        assert s3["best"] == b
+        np.testing.assert_allclose(np.concatenate([a[1] for a in alls]), runs[b]["log_probs"], rtol=1e-9, atol=1e-9)
+        print(f"MULTI_SOUP_OK case={case} world={world} iterations={s1['iterations']}", flush=True)
     gpu.close()
     dist.destroy_process_group()
 

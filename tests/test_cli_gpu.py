@@ -26,9 +26,15 @@ def col(rows, i, typ=str):
     return np.array([typ(r[i]) for r in rows]) if typ is not str else [r[i] for r in rows]
 
 
-@pytest.mark.parametrize("with_vcf", [False, True], ids=["plain", "vcf_gz"])
-def test_cli_outputs_match_oracle(tmp_path, oracle_lib, with_vcf):
+@pytest.mark.parametrize("with_vcf,gpus", [(False, 1), (True, 1), (False, 2), (True, 2)],
+                         ids=["plain", "vcf_gz", "plain_gpus2", "vcf_gz_gpus2"])
+def test_cli_outputs_match_oracle(tmp_path, oracle_lib, with_vcf, gpus):
+    """gpus = 2: `--gpus 2` (one forked worker per GPU, cells sharded, rank 0 writes) must produce the same files."""
     from tests.oracle import Oracle
+    if gpus > 1:
+        import torch
+        if torch.cuda.device_count() < gpus:
+            pytest.skip(f"needs {gpus} GPUs")
     cfg = synth.SynthConfig(n_cells=1800, n_loci=5000, density=0.03, minority_frac=0.07, seed=23, deep_frac=0.01, deep_mean=50.0)
     d = synth.generate(cfg)
     paths = synth.write_mtx_pair(d, str(tmp_path / "in"))
@@ -44,6 +50,8 @@ def test_cli_outputs_match_oracle(tmp_path, oracle_lib, with_vcf):
         subprocess.check_call(["gzip", "-k", paths["alt.mtx"]])
         cmd[2] = paths["alt.mtx"] + ".gz"
         cmd += ["-v", str(vcf), "--min_alt", "5", "--min_ref=6", "--interquartile_range_multiple", "4"]
+    if gpus > 1:
+        cmd += ["--gpus", str(gpus)]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     min_ref, min_alt, iqr = (6, 5, 4.0) if with_vcf else (4, 4, 5.0)
@@ -161,4 +169,4 @@ def test_cli_outputs_match_oracle(tmp_path, oracle_lib, with_vcf):
             assert not os.path.exists(out / "cellector.vcf")
     import json
     t = json.load(open(tmp_path / "timing.json"))
-    assert t["iterations"] == it and t["nnz0"] == d.nnz and t["gpu_launches"] > 0
+    assert t["iterations"] == it and t["nnz0"] == d.nnz and t["gpu_launches"] > 0 and t["gpus"] == gpus

@@ -25,4 +25,4 @@ def test_sharded_matches_oracle(case, p2p):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
            "--master-port", "29533", os.path.join(ROOT, "tests", "multi_worker.py"), case]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env={**os.environ, "CLX_P2P": p2p})
-    assert r.returncode == 0 and "MULTI_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.returncode == 0 and "MULTI_OK" in r.stdout and "MULTI_SOUP_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
