@@ -55,6 +55,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-cells", type=int, default=5000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cli-e2e", action="store_true", help="skip the `cellector` CLI run on the workload written as .mtx text")
     ap.add_argument("--flags", type=int, default=0, help="extra clx_create flags (e.g. 4 = v0 scoring kernel)")
     return ap.parse_args()
 
@@ -591,6 +592,77 @@ def e2e_job(args, dd, ctx, data, host, nnz_total):
                     "nonzeros x EM iterations / job seconds (median job, max over ranks)"}
 
 
+def cli_e2e(args, data, cpu_em_s_per_iteration):
+    """The drop-in surface itself: the workload written as a real alt.mtx / ref.mtx pair, the `cellector` binary run on
+    it (process start -> last file closed; second of two runs, the first warms the page cache), next to the CPU oracle
+    doing the same stages single-threaded like the reference (text parse with orc_read_mtx_pair, load, EM to convergence
+    at the per-iteration time measured above, posteriors; it writes no files, so its number is a lower bound)."""
+    import ctypes as C
+    import shutil
+    import subprocess
+    import tempfile
+    from tests.oracle import Oracle, load_oracle
+    cli = os.path.join(ROOT, "cellector_b200", "bin", "cellector")
+    if not os.path.exists(cli):
+        return {"unavailable": "cellector_b200/bin/cellector is not built"}
+    work = tempfile.mkdtemp(prefix="clx_cli_e2e_")
+    try:
+        import pandas as pd
+        header = "%%MatrixMarket matrix coordinate real general\n% written by sprs\n" + f"{data.n_loci}\t{data.n_cells}\t{data.nnz}\n"
+        l1, c1 = data.locus.astype(np.int64) + 1, data.cell.astype(np.int64) + 1
+        for name, vals in (("alt.mtx", data.alt), ("ref.mtx", data.ref)):
+            path = os.path.join(work, name)
+            with open(path, "w") as f:
+                f.write(header)
+            pd.DataFrame({"l": l1, "c": c1, "v": vals}).to_csv(path, sep="\t", header=False, index=False, mode="a")
+        with open(os.path.join(work, "barcodes.tsv"), "w") as f:
+            f.write("\n".join(f"CELL{i:09d}-1" for i in range(data.n_cells)) + "\n")
+        mtx_bytes = sum(os.path.getsize(os.path.join(work, n)) for n in ("alt.mtx", "ref.mtx"))
+        runs = []
+        for rep in range(2):
+            out = os.path.join(work, f"out{rep}")
+            t0 = time.perf_counter()
+            r = subprocess.run([cli, "-a", os.path.join(work, "alt.mtx"), "-r", os.path.join(work, "ref.mtx"), "-b",
+                                os.path.join(work, "barcodes.tsv"), "--output_directory", out, "--timing_json", out + ".json"],
+                               capture_output=True, text=True, timeout=600)
+            wall = time.perf_counter() - t0
+            if r.returncode != 0:
+                return {"unavailable": "the CLI failed: " + r.stderr[-300:]}
+            t = json.load(open(out + ".json"))
+            t["process_wall_s"] = wall
+            t.pop("em_device_ms", None)
+            runs.append(t)
+        lib = load_oracle()
+        nl, nc, nnz = C.c_uint32(0), C.c_uint32(0), C.c_uint64(0)
+        coo = [np.empty(data.nnz, np.uint32) for _ in range(4)]
+        t0 = time.perf_counter()
+        rc = lib.orc_read_mtx_pair(os.path.join(work, "alt.mtx").encode(), os.path.join(work, "ref.mtx").encode(), C.byref(nl),
+                                   C.byref(nc), C.byref(nnz), *[a.ctypes.data for a in coo], data.nnz)
+        parse_s = time.perf_counter() - t0
+        cpu = {"unavailable": "orc_read_mtx_pair failed"}
+        if rc == 0 and nnz.value == data.nnz:
+            with Oracle(lib) as orc:
+                t0 = time.perf_counter()
+                orc.load_cell_data(coo[0], coo[1], coo[2], coo[3], nl.value, nc.value)
+                load_s = time.perf_counter() - t0
+            em_s = cpu_em_s_per_iteration * runs[-1]["iterations"] if cpu_em_s_per_iteration else None
+            cpu = {"parse_s": parse_s, "load_s": load_s, "em_s": em_s, "cores": 1, "kind": "port",
+                   "total_s_lower_bound": (parse_s + load_s + em_s) if em_s is not None else None,
+                   "what": "oracle port, single-threaded like the reference: text parse + row lists + EM iterations (per-iteration "
+                           "time of cpu_baseline x the CLI's iteration count); posteriors and every output file left out"}
+        res = {"seconds": runs[-1]["process_wall_s"], "workload": args.workload, "mtx_bytes": mtx_bytes, "stages": runs[-1],
+               "first_run_seconds": runs[0]["process_wall_s"], "cpu": cpu,
+               "what": "cellector_b200/bin/cellector on the workload as alt.mtx/ref.mtx text: process start -> exit, every output "
+                       "file of the reference written (iteration_*.tsv, locus contributions, assignments); second of two runs"}
+        if cpu.get("total_s_lower_bound"):
+            res["speedup_vs_cpu_lower_bound"] = cpu["total_s_lower_bound"] / res["seconds"]
+        return res
+    except Exception as e:  # the bench line must not die on the optional leg
+        return {"unavailable": f"{type(e).__name__}: {e}"}
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
 def strip(m):
     return {k: v for k, v in m.items() if k not in ("cfg", "balanced", "clocks")}
 
@@ -624,6 +696,12 @@ def main():
         e2e = None if args.no_e2e else e2e_job(args, dd, ctx, data, host, float(nnz_used))
         cpu, par = (None, None) if args.no_cpu_baseline else cpu_baseline_and_parity(args, ctx, data)
         ctx.close()
+        cli = None
+        if not args.no_cli_e2e and not args.no_e2e and name in ("C1", "C2"):
+            em_s = None
+            if cpu is not None:
+                em_s = float(nnz_used) / cpu["value"]
+            cli = cli_e2e(args, data, em_s)
         large = None
         if not args.no_large and name == "C2":
             lg = run_large(args, dd, lib, args.large, 0, 1, local_rank)
@@ -636,6 +714,8 @@ def main():
                 "wall_ms_per_step_incl_l2_flush": m["wall_ms"], "clocks": m["clocks"], "e2e": e2e, "gpu_launches": m["launches"],
                 "roofline": m["roofline"], "cpu_baseline": cpu, "parity": par, "phase_us_per_step": m["phase_us_per_step"],
                 "ms_per_step_with_phase_events": m["ms_per_step_with_phase_events"], "timing": timing}
+        if cli is not None:
+            line["cli_e2e"] = cli
         if large is not None:
             line["large"] = large
             line["roofline_large"] = large["roofline"]
