@@ -176,6 +176,7 @@ struct clx_ctx {
     clx::DevBuf<double> post_ll;                      // [3 * n_cells] posterior pass: minority | majority | doublet log likelihoods
     clx::DevBuf<uint32_t> nloci;                      // [n_cells]
     clx::DevBuf<double> norm_all;                     // [world * max_local] gathered normalized values (world > 1)
+    int select_cluster_ok = 0;                        // 1: this load's select runs as one thread-block cluster (asked in em_alloc)
     clx::DevBuf<uint64_t> sel_keys;                   // select scratch
     clx::DevBuf<unsigned int> sel_hist;               // select scratch
     clx::DevBuf<unsigned long long> sel_state;        // select scratch

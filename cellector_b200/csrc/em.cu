@@ -144,6 +144,50 @@ SelectPlan make_plan(uint64_t n) {
     return p;
 }
 
+// the select as one thread-block cluster: one GPU, at most 16 CTAs of 1024 threads with 1 or 4 keys per thread
+typedef void (*SelectClusterFn)(const double*, uint64_t, SelectPlan, const IterParams*, DeviceStats*, unsigned int*,
+                                unsigned long long*, const double*, uint32_t, uint32_t*, unsigned char* const*, int, int, size_t);
+SelectClusterFn select_cluster_fn(int R) {
+    return R == 1 ? k_select_coop<1, SELECT_SMALL_THREADS, true> : k_select_coop<4, SELECT_SMALL_THREADS, true>;
+}
+bool select_cluster_shape(const clx_ctx* c, uint64_t n_vals, int* R_out, unsigned* grid_out) {
+    if (c->world != 1 || n_vals > 16ull * 4 * SELECT_SMALL_THREADS) return false;
+    const int R = n_vals <= 16ull * SELECT_SMALL_THREADS ? 1 : 4;
+    const uint64_t per_cta = (uint64_t)SELECT_SMALL_THREADS * R;
+    if (R_out) *R_out = R;
+    if (grid_out) *grid_out = (unsigned)std::max<uint64_t>(1, (n_vals + per_cta - 1) / per_cta);
+    return true;
+}
+// asked once per load, outside any stream capture: can this device co-schedule the cluster?
+void select_cluster_probe(clx_ctx* c, uint64_t n_vals) {
+    c->select_cluster_ok = 0;
+    int R = 1;
+    unsigned grid = 1;
+    if (!select_cluster_shape(c, n_vals, &R, &grid)) return;
+    const void* fn = (const void*)select_cluster_fn(R);
+    if (cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+        cudaGetLastError();
+        return;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(SELECT_SMALL_THREADS);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = grid;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n_clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&n_clusters, fn, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        return;
+    }
+    c->select_cluster_ok = n_clusters >= 1 ? 1 : 0;
+}
+
 // exact order statistics of `vals[0, n_vals)` (pads = +inf beyond the n real values) -> d_stats, then the new
 // excluded set of this rank's cells (main.rs:330-335), in place in excl_bits
 int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t n_real) {
@@ -154,6 +198,32 @@ int run_select_exclude(clx_ctx* c, const double* vals, uint64_t n_vals, uint64_t
     // cooperative grid, keys in registers, one launch: as few keys per thread as one CTA per SM allows (1, 4 or 16);
     // 256-thread CTAs for small inputs measured slightly slower (29.8 vs 27.9 us at 10 k keys)
     const uint64_t cap1 = (uint64_t)SELECT_SMALL_THREADS * (uint64_t)c->sm_count;
+    // up to 16 CTAs' worth of keys on one GPU: the same kernel as ONE thread-block cluster (hardware cluster barrier
+    // instead of the cooperative grid barrier; em_alloc asked the device whether it can place it);
+    // CLX_SELECT_MODE=1 keeps the cooperative launch for A/B runs
+    if (mode == 0 && c->select_cluster_ok == 1 && select_cluster_shape(c, n_vals, nullptr, nullptr)) {
+        int R = 1;
+        unsigned grid = 1;
+        select_cluster_shape(c, n_vals, &R, &grid);
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(SELECT_SMALL_THREADS);
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = grid;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        const double* norm_local = c->norm.p;
+        CLX_CUDA(c, cudaLaunchKernelEx(&cfg, select_cluster_fn(R), vals, n_vals, plan, (const IterParams*)c->d_params.p, c->d_stats.p,
+                                       c->sel_hist.p, (unsigned long long*)c->sel_keys.p, norm_local, N, c->excl_bits.p,
+                                       (unsigned char* const*)nullptr, 0, 1, (size_t)0));
+        c->launches++;
+        return CLX_OK;
+    }
     if (mode != 2 && n_vals <= 16 * cap1) {
         const int R = n_vals <= cap1 ? 1 : (n_vals <= 4 * cap1 ? 4 : 16);
         const int threads = SELECT_SMALL_THREADS;
@@ -225,6 +295,7 @@ int em_alloc(clx_ctx* c) {
     CLX_CUDA(c, c->sel_keys.alloc(n_sel + 256));  // key array of the multi-launch path / survivor list
     CLX_CUDA(c, c->sel_hist.alloc(SELECT_COOP_SCRATCH + 8 * SELECT_TARGETS * 256 + 8));
     CLX_CUDA(c, c->sel_state.alloc(sizeof(SelectState) / 8 + 1));
+    select_cluster_probe(c, n_sel);
     // pads of the gather buffer: +inf sorts after every real value
     {
         std::vector<double> inf(norm_n, INFINITY);

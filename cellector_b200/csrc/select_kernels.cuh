@@ -119,13 +119,19 @@ static_assert(SELECT_RANK_CAP <= SELECT_LIST_PAD, "survivor list fits the sort n
 // (main.rs:330-335) for this rank's cells runs in the same launch.
 constexpr int SELECT_COOP_HIST = 8 * SELECT_TARGETS * 256;  // u32 words
 constexpr int SELECT_COOP_SCRATCH = SELECT_COOP_HIST + 8;   // + {or, nor} (2 x u64) + n_list + pad
-template <int R, int T>
+// CL = true: the CTAs form ONE thread-block cluster (at most 16 CTAs, i.e. 16 k / 64 k keys at R = 1 / 4) and meet at
+// the hardware cluster barrier (barrier.cluster arrive.release / wait.acquire) instead of the cooperative grid's
+// barrier in global memory: the 10-k-cell select of C2 is four to five barriers and little else.
+template <int R, int T, bool CL = false>
 __global__ void __launch_bounds__(T) k_select_coop(
     const double* __restrict__ vals, uint64_t n, SelectPlan plan, const IterParams* __restrict__ prm,
     DeviceStats* __restrict__ st, unsigned int* __restrict__ scratch, unsigned long long* __restrict__ glist,
     const double* __restrict__ norm_local, uint32_t n_cells_local, uint32_t* __restrict__ bits,
     unsigned char* const* __restrict__ win, int rank, int world, size_t off_counters) {
-    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    auto sync_all = [] {
+        if constexpr (CL) cooperative_groups::this_cluster().sync();
+        else cooperative_groups::this_grid().sync();
+    };
     // sharded over peer memory: barrier 0 — every rank has stored its normalized values into this rank's window
     if (win != nullptr) p2p_sync_head(win, rank, world, 0, off_counters, &st->pad);
     __shared__ unsigned int sh[SELECT_TARGETS][256];
@@ -167,7 +173,7 @@ __global__ void __launch_bounds__(T) k_select_coop(
         atomicOr(&g_or[0], k_or);
         atomicOr(&g_or[1], k_nor);
     }
-    grid.sync();
+    sync_all();
     k_or = __ldcg(&g_or[0]);
     k_nor = __ldcg(&g_or[1]);
     const unsigned long long diff = k_or & k_nor;  // bits that are 1 in some key and 0 in another
@@ -230,7 +236,7 @@ __global__ void __launch_bounds__(T) k_select_coop(
             const unsigned int v = (&sh[0][0])[i];
             if (v) atomicAdd(&gh[i], v);
         }
-        grid.sync();
+        sync_all();
         for (int i = tid; i < SELECT_TARGETS * 256; i += T) (&sh[0][0])[i] = __ldcg(&gh[i]);
         __syncthreads();
         if (warp < SELECT_TARGETS) {
@@ -303,7 +309,7 @@ __global__ void __launch_bounds__(T) k_select_coop(
                     if (slot < SELECT_RANK_CAP) glist[slot] = key[j];
                 }
         }
-        grid.sync();
+        sync_all();
         const unsigned int nl = min(__ldcg(g_nlist), SELECT_RANK_CAP);
         for (unsigned int i = tid; i < nl; i += T) s_list[i] = __ldcg(&glist[i]);
         __syncthreads();
