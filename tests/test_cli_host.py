@@ -111,3 +111,24 @@ def test_cli_flag_errors(tmp_path):
     assert r.returncode == 1 and "required arguments" in r.stderr
     r = subprocess.run([CLI, "--bogus", "1"], capture_output=True, text=True)
     assert r.returncode == 1 and "wasn't expected" in r.stderr
+
+
+SOUP_CLI = os.path.join(ROOT, "cellector_b200", "bin", "souporcell")
+
+
+def test_souporcell_rng_selftest():
+    """ChaCha20 block function of the souporcell host's StdRng against the RFC 7539 section 2.3.2 vector, its first
+    draws against the plain-Python statement in tests/soup_rng.py, and the f32 Display formatting"""
+    from tests.soup_rng import StdRng07
+    r = subprocess.run([SOUP_CLI, "--rng_selftest"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.strip().split("\n")
+    assert lines[0] == ("e4e7f110 15593bd1 1fdd0f50 c47120a3 c7f4d1c7 0368c033 9aaa2204 4e6cd4c3 "
+                        "466482d2 09aa9f07 05d7c214 a2028bd9 d19c12b5 b94e16de e883d0cb 4e3c50a2")
+    rng = StdRng07(bytes([4]) * 32)
+    u8 = [rng.gen_u8() for _ in range(3)]
+    f32 = [rng.gen_f32() for _ in range(3)]
+    t = lines[1].split()
+    assert t[0] == "u8" and [int(x) for x in t[1:4]] == u8
+    assert t[4] == "f32" and [np.float32(x) for x in t[5:8]] == f32
+    assert lines[2].split() == ["f32", "0.1", "-2181.0225", "5", "0.0000001", "340282350000000000000000000000000000000", "-0"]

@@ -117,3 +117,43 @@ def test_soup_refuses_duplicated_coordinates_and_clipped_counts():
             gpu.soup_em(soup.init_cluster_centers_uniform(n_used, 2, 4))
         with pytest.raises(RuntimeError, match=r"\[1, 8\]"):
             gpu.soup_em(soup.init_cluster_centers_uniform(n_used, 9, 4))
+
+
+def test_souporcell_cli_matches_oracle(tmp_path):
+    """the `souporcell` binary end to end (reference flags in, `barcode<TAB>cluster<TAB>log probabilities` out,
+    main.rs:91-105) against the oracle run from the same initial centers (tests/soup_rng.py states the draws separately)"""
+    import os
+    import subprocess
+    from tests.soup_rng import souporcell_initial_centers
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cli = os.path.join(root, "cellector_b200", "bin", "souporcell")
+    d = synth.generate(synth.SynthConfig(n_cells=400, n_loci=1200, density=0.06, minority_frac=0.3, seed=59))
+    paths = synth.write_mtx_pair(d, str(tmp_path / "in"))
+    k, restarts, threads, seed = 2, 5, 2, 7
+    r = subprocess.run([cli, "-a", paths["alt.mtx"], "-r", paths["ref.mtx"], "--barcodes", paths["barcodes.tsv"], "-k", str(k),
+                        "--restarts", str(restarts), "-t", str(threads), "--seed", str(seed)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    with SoupOracle() as orc:
+        n_used, _ = orc.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+        assert f"total loci used {n_used}" in r.stderr
+        init = souporcell_initial_centers(seed, threads, restarts, k, n_used)
+        assert init.shape[0] == 6  # ceil(5 / 2) runs on each of the 2 threads
+        runs = [orc.soup_em(c, precise=True) for c in init]
+    best = int(np.argmax([x["loss"] for x in runs]))
+    want = runs[best]["log_probs"]
+    m = [l for l in r.stderr.split("\n") if l.startswith("best total log probability = ")]
+    assert len(m) == 1 and float(m[0].split("= ")[1]) == pytest.approx(runs[best]["loss"], rel=1e-6)
+    rows = [l.split("\t") for l in r.stdout.strip().split("\n")]
+    barcodes = open(paths["barcodes.tsv"]).read().split()
+    assert [x[0] for x in rows] == barcodes and all(len(x) == 2 + k for x in rows)
+    got = np.array([[float(v) for v in x[2:]] for x in rows])
+    np.testing.assert_allclose(got, want, rtol=2e-7, atol=1e-30)  # printed as f32
+    assert [int(x[1]) for x in rows] == np.argmax(got.astype(np.float32), axis=1).tolist()
+    truth = np.asarray(d.is_minority, dtype=np.int64)
+    agree = (np.array([int(x[1]) for x in rows]) == truth).mean()
+    assert max(agree, 1 - agree) > 0.95
+    # what the reference asserts on or this build leaves out is refused, not ignored
+    for extra in (["--initialization_strategy", "kmeans++"], ["--known_genotypes", "x.vcf"], ["--min_alt_umis", "3"]):
+        bad = subprocess.run([cli, "-a", paths["alt.mtx"], "-r", paths["ref.mtx"], "-b", paths["barcodes.tsv"], "-k", "2", *extra],
+                             capture_output=True, text=True, timeout=60)
+        assert bad.returncode != 0 and "not" in bad.stderr
