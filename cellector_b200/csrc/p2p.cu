@@ -63,6 +63,8 @@ __global__ void k_p2p_put_norm(unsigned char* const* __restrict__ win, int rank,
     }
 }
 
+constexpr int P2P_BATCH = 8;  // peer loads of one element in flight together
+
 // reduce-scatter + all-gather in one kernel: rank r owns loci [L r / world, L (r+1) / world) of each of the ten arrays
 __global__ void k_p2p_reduce(unsigned char* const* __restrict__ win, int rank, int world, size_t off_part_ll, size_t off_part_int,
                              size_t off_tot_ll, size_t off_tot_int, size_t off_counters, uint32_t L,
@@ -76,14 +78,30 @@ __global__ void k_p2p_reduce(unsigned char* const* __restrict__ win, int rank, i
     // ten arrays of L: a = 0, 1 are the f64 arrays, 2..9 the u64 arrays
     for (uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < 10ull * n; k += (uint64_t)gridDim.x * blockDim.x) {
         const uint32_t a = (uint32_t)(k / n), l = l0 + (uint32_t)(k % n);
+        // a peer load takes ~1 us: all of an element's loads are issued before the first one is used (up to P2P_BATCH
+        // ranks at a time), then added in rank order — the order every rank uses, so the doubles agree everywhere
         if (a < 2) {
             double sum = 0.0;
-            for (int r = 0; r < world; ++r) sum += reinterpret_cast<const double*>(win[r] + off_part_ll)[(size_t)a * L + l];
+            for (int r0 = 0; r0 < world; r0 += P2P_BATCH) {
+                double v[P2P_BATCH];
+#pragma unroll
+                for (int j = 0; j < P2P_BATCH; ++j)
+                    v[j] = r0 + j < world ? reinterpret_cast<const double*>(win[r0 + j] + off_part_ll)[(size_t)a * L + l] : 0.0;
+#pragma unroll
+                for (int j = 0; j < P2P_BATCH; ++j)
+                    if (r0 + j < world) sum += v[j];
+            }
             for (int r = 0; r < world; ++r) reinterpret_cast<double*>(win[r] + off_tot_ll)[(size_t)a * L + l] = sum;
         } else {
             unsigned long long sum = 0;
-            for (int r = 0; r < world; ++r)
-                sum += reinterpret_cast<const unsigned long long*>(win[r] + off_part_int)[(size_t)(a - 2) * L + l];
+            for (int r0 = 0; r0 < world; r0 += P2P_BATCH) {
+                unsigned long long v[P2P_BATCH];
+#pragma unroll
+                for (int j = 0; j < P2P_BATCH; ++j)
+                    v[j] = r0 + j < world ? reinterpret_cast<const unsigned long long*>(win[r0 + j] + off_part_int)[(size_t)(a - 2) * L + l] : 0ull;
+#pragma unroll
+                for (int j = 0; j < P2P_BATCH; ++j) sum += v[j];
+            }
             for (int r = 0; r < world; ++r) reinterpret_cast<unsigned long long*>(win[r] + off_tot_int)[(size_t)(a - 2) * L + l] = sum;
         }
     }
@@ -239,7 +257,8 @@ int p2p_put_norm(clx_ctx* c) {
 int p2p_reduce(clx_ctx* c) {
     const uint32_t L = c->n_loci;
     const uint64_t work = 10ull * (L / c->world + 1);
-    k_p2p_reduce<<<(unsigned)std::min<uint64_t>((work + 255) / 256, (uint64_t)c->sm_count * 2), 256, 0, c->stream>>>(
+    // latency-bound on NVLink round trips: as many threads in flight as the SMs hold (8 CTAs of 256 each)
+    k_p2p_reduce<<<(unsigned)std::min<uint64_t>((work + 255) / 256, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
         (unsigned char* const*)c->d_peer_win.p, c->rank, c->world, c->win_off_part_ll, c->win_off_part_int, c->win_off_tot_ll,
         c->win_off_tot_int, c->win_off_counters, L, &c->d_stats.p->n_new, &c->d_stats.p->pad);
     c->launches++;
