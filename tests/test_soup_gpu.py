@@ -59,6 +59,22 @@ def test_soup_em_matches_oracle(name):
         assert (np.argmax(g["log_probs"], axis=1) == np.argmax(o32["log_probs"], axis=1))[clear].all()
 
 
+@pytest.mark.parametrize("name", ["soup_small_k3.json", "soup_c1_k2.json"])
+def test_soup_em_against_committed_golden(name):
+    """the frozen oracle outputs (tests/golden/make_soup_golden.py), C1 at full size included: 1e-9 on the GPU"""
+    from cellector_b200 import Cellector
+    from tests.test_soup_oracle import check_against_golden, load_golden
+    g, d, init = load_golden(name)
+    with Cellector(0) as gpu:
+        n_used, _ = gpu.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+        assert n_used == g["loaded"][0]
+        res = gpu.soup_em(init)
+    check_against_golden(g, res, 1e-9)
+    # and the reference's f32 arithmetic gives the same clustering
+    assert np.bincount(np.argmax(res["log_probs"], axis=1), minlength=g["k"]).tolist() == g["f32"]["assignment_counts"]
+    assert abs(res["loss"] - g["f32"]["loss"]) <= 1e-5 * abs(g["f32"]["loss"])
+
+
 def test_soup_restarts_recover_the_two_individuals():
     """souporcell_main (main.rs:62-106): best of a few restarts separates the two simulated individuals"""
     from cellector_b200 import Cellector

@@ -108,3 +108,43 @@ def test_reference_arithmetic_is_within_f32_rounding_of_the_f64_statement(name):
     clear = np.abs(np.sort(f64["log_probs"], axis=1)[:, -1] - np.sort(f64["log_probs"], axis=1)[:, -2]) > 0.1
     assert clear.mean() > 0.9
     assert (np.argmax(f32["log_probs"], axis=1) == np.argmax(f64["log_probs"], axis=1))[clear].all()
+
+
+GOLDEN = ["soup_small_k3.json", "soup_c1_k2.json"]
+
+
+def load_golden(name):
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name)))
+    d = synth.generate(synth.SynthConfig(**g["config"]))
+    from tests.soup_rng import souporcell_initial_centers
+    init = souporcell_initial_centers(g["seed"], 1, 1, g["k"], g["loaded"][0])[0]
+    assert float(init.astype(np.float64).sum()) == g["init_sum"]
+    return g, d, init
+
+
+def check_against_golden(g, res, rtol):
+    """res = a run in the f64 statement (the oracle: rtol 0 = bit for bit; the CUDA path: 1e-9)"""
+    w = g["f64"]
+    assert res["iterations"] == w["iterations"]
+    close = (lambda a, b: np.testing.assert_array_equal(np.asarray(a), np.asarray(b))) if rtol == 0 else \
+        (lambda a, b: np.testing.assert_allclose(np.asarray(a), np.asarray(b), rtol=rtol, atol=1e-12))
+    close(res["loss"], w["loss"])
+    close(res["log_probs"].sum(axis=0), w["log_probs_sum"])
+    close(res["log_probs"][w["cell_idx"]], w["cell_log_probs"])
+    close(res["centers"][:, w["locus_idx"]], w["locus_centers"])
+    assert np.bincount(np.argmax(res["log_probs"], axis=1), minlength=g["k"]).tolist() == w["assignment_counts"]
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_oracle_reproduces_the_frozen_outputs(name):
+    g, d, init = load_golden(name)
+    with SoupOracle() as o:
+        assert list(o.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)) == g["loaded"]
+        res = o.soup_em(init, precise=True)
+        np.testing.assert_array_equal(res["loss_trace"], np.asarray(g["f64"]["loss_trace"]))
+        check_against_golden(g, res, 0)
+        f32 = o.soup_em(init, precise=False)
+    assert f32["iterations"] == g["f32"]["iterations"] and f32["loss"] == g["f32"]["loss"]
+    assert np.bincount(np.argmax(f32["log_probs"], axis=1), minlength=g["k"]).tolist() == g["f32"]["assignment_counts"]
