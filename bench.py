@@ -55,6 +55,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-cells", type=int, default=5000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-soup", action="store_true", help="skip the souporcell EM leg on the headline matrix")
     ap.add_argument("--no-cli-e2e", action="store_true", help="skip the `cellector` CLI run on the workload written as .mtx text")
     ap.add_argument("--flags", type=int, default=0, help="extra clx_create flags (e.g. 4 = v0 scoring kernel)")
     return ap.parse_args()
@@ -594,7 +595,7 @@ def e2e_job(args, dd, ctx, data, host, nnz_total):
 
 def cli_e2e(args, data, cpu_em_s_per_iteration):
     """The drop-in surface itself: the workload written as a real alt.mtx / ref.mtx pair, the `cellector` binary run on
-    it (process start -> last file closed; second of two runs, the first warms the page cache), next to the CPU oracle
+    it (process start -> last file closed; median of three runs), next to the CPU oracle
     doing the same stages single-threaded like the reference (text parse with orc_read_mtx_pair, load, EM to convergence
     at the per-iteration time measured above, posteriors; it writes no files, so its number is a lower bound)."""
     import ctypes as C
@@ -619,7 +620,7 @@ def cli_e2e(args, data, cpu_em_s_per_iteration):
             f.write("\n".join(f"CELL{i:09d}-1" for i in range(data.n_cells)) + "\n")
         mtx_bytes = sum(os.path.getsize(os.path.join(work, n)) for n in ("alt.mtx", "ref.mtx"))
         runs = []
-        for rep in range(2):
+        for rep in range(3):
             out = os.path.join(work, f"out{rep}")
             t0 = time.perf_counter()
             r = subprocess.run([cli, "-a", os.path.join(work, "alt.mtx"), "-r", os.path.join(work, "ref.mtx"), "-b",
@@ -645,15 +646,19 @@ def cli_e2e(args, data, cpu_em_s_per_iteration):
                 t0 = time.perf_counter()
                 orc.load_cell_data(coo[0], coo[1], coo[2], coo[3], nl.value, nc.value)
                 load_s = time.perf_counter() - t0
-            em_s = cpu_em_s_per_iteration * runs[-1]["iterations"] if cpu_em_s_per_iteration else None
+            em_s = cpu_em_s_per_iteration * runs[-1]["iterations"] if cpu_em_s_per_iteration else None  # same count in every run
             cpu = {"parse_s": parse_s, "load_s": load_s, "em_s": em_s, "cores": 1, "kind": "port",
                    "total_s_lower_bound": (parse_s + load_s + em_s) if em_s is not None else None,
                    "what": "oracle port, single-threaded like the reference: text parse + row lists + EM iterations (per-iteration "
                            "time of cpu_baseline x the CLI's iteration count); posteriors and every output file left out"}
-        res = {"seconds": runs[-1]["process_wall_s"], "workload": args.workload, "mtx_bytes": mtx_bytes, "stages": runs[-1],
-               "first_run_seconds": runs[0]["process_wall_s"], "cpu": cpu,
+        # CUDA start-up inside the child (0.2-0.9 s on a box whose GPU the bench process also holds) decides the wall time:
+        # the median of three runs is reported, all three are listed
+        order = sorted(range(len(runs)), key=lambda i: runs[i]["process_wall_s"])
+        mid = runs[order[len(runs) // 2]]
+        res = {"seconds": mid["process_wall_s"], "workload": args.workload, "mtx_bytes": mtx_bytes, "stages": mid,
+               "all_runs_seconds": [r["process_wall_s"] for r in runs], "cpu": cpu,
                "what": "cellector_b200/bin/cellector on the workload as alt.mtx/ref.mtx text: process start -> exit, every output "
-                       "file of the reference written (iteration_*.tsv, locus contributions, assignments); second of two runs"}
+                       "file of the reference written (iteration_*.tsv, locus contributions, assignments); median of three runs"}
         if cpu.get("total_s_lower_bound"):
             res["speedup_vs_cpu_lower_bound"] = cpu["total_s_lower_bound"] / res["seconds"]
         return res
@@ -661,6 +666,49 @@ def cli_e2e(args, data, cpu_em_s_per_iteration):
         return {"unavailable": f"{type(e).__name__}: {e}"}
     finally:
         shutil.rmtree(work, ignore_errors=True)
+
+
+def soup_leg(ctx, data, k=2, restarts=16):
+    """souporcell's k-cluster EM on the matrix the context holds: time per EM iteration for a single
+    run and per restart-iteration with the restarts batched, next to the oracle in the reference's f32 arithmetic on one
+    core, with the parity of the same run (GPU vs the oracle's f64 statement; assignments vs its f32 one)."""
+    try:
+        from cellector_b200 import soup
+        from tests.soup_oracle import SoupOracle
+        n_used = ctx.n_loci_used
+        if ctx.n_cells != data.n_cells:
+            return {"unavailable": "the context holds a cell slice of the workload"}
+        init = np.stack([soup.init_cluster_centers_uniform(n_used, k, 4, r) for r in range(restarts)])
+        ctx.soup_em(init[0])  # warm-up
+        t0 = time.perf_counter()
+        one = ctx.soup_em(init[0])
+        t_one = time.perf_counter() - t0
+        ctx.soup_restarts(init[:2])
+        t0 = time.perf_counter()
+        many = ctx.soup_restarts(init)
+        t_many = time.perf_counter() - t0
+        with SoupOracle() as orc:
+            orc.load_cell_data(data.locus, data.cell, data.ref, data.alt, data.n_loci, data.n_cells)
+            t0 = time.perf_counter()
+            o32 = orc.soup_em(init[0], precise=False)
+            t_cpu = time.perf_counter() - t0
+            o64 = orc.soup_em(init[0], precise=True)
+            entries = orc.n_entries
+        it_many = int(many["iterations"].sum())
+        rel = float(np.max(np.abs(one["log_probs"] - o64["log_probs"]) / np.abs(o64["log_probs"])))
+        return {"k": k, "entries": int(entries), "iterations": one["iterations"],
+                "gpu_us_per_iteration": 1e6 * t_one / one["iterations"], "gpu_entries_per_s": entries * one["iterations"] / t_one,
+                "batched": {"restarts": restarts, "restart_iterations": it_many, "us_per_restart_iteration": 1e6 * t_many / it_many,
+                            "entries_per_s": entries * it_many / t_many, "best": many["best"]},
+                "cpu_f32": {"iterations": o32["iterations"], "us_per_iteration": 1e6 * t_cpu / o32["iterations"],
+                            "entries_per_s": entries * o32["iterations"] / t_cpu, "cores": 1, "kind": "port"},
+                "parity": {"iterations_gpu_f64_f32": [one["iterations"], o64["iterations"], o32["iterations"]],
+                           "max_rel_log_prob_vs_f64": rel, "loss_rel_vs_f32": abs(one["loss"] - o32["loss"]) / abs(o32["loss"]),
+                           "assignments_identical_to_f32": bool(np.array_equal(np.argmax(one["log_probs"], 1), np.argmax(o32["log_probs"], 1))),
+                           "ok": bool(rel <= 1e-9 and one["iterations"] == o64["iterations"])},
+                "what": "clx_soup_em / clx_soup_restarts wall time (set-up, iterations, results to the host) on the headline matrix"}
+    except Exception as e:  # optional leg
+        return {"unavailable": f"{type(e).__name__}: {e}"}
 
 
 def strip(m):
@@ -695,6 +743,7 @@ def main():
         apply_traffic(m["roofline"], name)
         e2e = None if args.no_e2e else e2e_job(args, dd, ctx, data, host, float(nnz_used))
         cpu, par = (None, None) if args.no_cpu_baseline else cpu_baseline_and_parity(args, ctx, data)
+        soup_res = None if (args.no_soup or name not in ("C1", "C2")) else soup_leg(ctx, data)
         ctx.close()
         cli = None
         if not args.no_cli_e2e and not args.no_e2e and name in ("C1", "C2"):
@@ -716,6 +765,8 @@ def main():
                 "ms_per_step_with_phase_events": m["ms_per_step_with_phase_events"], "timing": timing}
         if cli is not None:
             line["cli_e2e"] = cli
+        if soup_res is not None:
+            line["souporcell_em"] = soup_res
         if large is not None:
             line["large"] = large
             line["roofline_large"] = large["roofline"]
