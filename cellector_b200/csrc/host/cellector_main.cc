@@ -9,6 +9,7 @@
 //             [--min_loci_for_assignment 30]
 //   additive flags (not in the reference): --device N, --threads N, --max_iterations N, --timing_json FILE,
 //             --no_iteration_files (skip the per-iteration diagnostics), --parse_only (parser self-check),
+//             --partition_only (prints the --gpus N cell ranges, no CUDA),
 //             --gpus N: cells sharded over N GPUs (devices --device .. --device + N - 1).  The process parses the
 //             matrix once, then forks N - 1 workers BEFORE any CUDA call; every process owns one GPU and one context
 //             (the library's model: one process per GPU, clx_comm_init between them), takes a contiguous range of
@@ -63,7 +64,7 @@ struct Params {  // main.rs:613-627
     unsigned threads = 0;
     uint64_t max_iterations = 0;  // 0 = no cap, like the reference (main.rs:42-46)
     std::string timing_json;
-    bool no_iteration_files = false, parse_only = false;
+    bool no_iteration_files = false, parse_only = false, partition_only = false;
 };
 
 // --gpus N: what the ranks share (one anonymous MAP_SHARED mapping made before the fork)
@@ -152,7 +153,7 @@ Params load_params(int argc, char** argv) {
             usage();
             die("error: Found argument '" + a + "' which wasn't expected, or isn't valid in this context", 1);
         }
-        if (name == "no_iteration_files" || name == "parse_only") {
+        if (name == "no_iteration_files" || name == "parse_only" || name == "partition_only") {
             kv[name] = "1";
             continue;
         }
@@ -165,7 +166,7 @@ Params load_params(int argc, char** argv) {
     static const char* known[] = {"output_directory", "ref", "alt", "barcodes", "min_alt", "min_ref", "ground_truth", "vcf",
                                   "posterior_threshold", "interquartile_range_multiple", "min_alleles_posterior",
                                   "expected_percent_minority", "min_loci_for_assignment", "device", "gpus", "threads", "max_iterations",
-                                  "timing_json", "no_iteration_files", "parse_only"};
+                                  "timing_json", "no_iteration_files", "parse_only", "partition_only"};
     for (const auto& e : kv) {
         bool ok = false;
         for (const char* k : known) ok = ok || e.first == k;
@@ -205,6 +206,7 @@ Params load_params(int argc, char** argv) {
     if (kv.count("timing_json")) p.timing_json = kv["timing_json"];
     p.no_iteration_files = kv.count("no_iteration_files") > 0;
     p.parse_only = kv.count("parse_only") > 0;
+    p.partition_only = kv.count("partition_only") > 0;
     if (p.threads == 0) p.threads = std::max(1u, std::thread::hardware_concurrency());
     return p;
 }
@@ -470,7 +472,7 @@ int run(const Params& params) {
     int create_rc = CLX_OK;
     std::string create_err;
     std::thread cuda_init;
-    if (!params.parse_only && params.gpus == 1)
+    if (!params.parse_only && !params.partition_only && params.gpus == 1)
         cuda_init = std::thread([&] {
             create_rc = clx_create(&ctx, params.device, params.has_vcf ? CLX_FLAG_KEEP_COO : 0u);
             if (create_rc != CLX_OK) create_err = clx_last_error(nullptr);
@@ -524,6 +526,13 @@ int run(const Params& params) {
             b = std::max(b, bound[r - 1] + 1);                                  // every rank gets a cell
             bound[r] = std::min(b, n_cells - (uint32_t)(params.gpus - r));
         }
+        if (params.partition_only) {  // host self-check of the --gpus split (no CUDA): cell range and entries of every rank
+            for (int r = 0; r < params.gpus; ++r)
+                printf("partition rank %d cells %u %u entries %llu\n", r, bound[r], bound[r + 1],
+                       (unsigned long long)(start[bound[r + 1]] - start[bound[r]]));
+            free(coo);
+            return 0;
+        }
         g_team = (TeamShared*)shared_alloc(sizeof(TeamShared));
         new (g_team) TeamShared();
         g_world = params.gpus;
@@ -542,6 +551,11 @@ int run(const Params& params) {
         }
         c0 = bound[g_rank];
         c1 = bound[g_rank + 1];
+    }
+    if (params.partition_only) {  // --gpus 1: one range
+        printf("partition rank 0 cells 0 %u entries %llu\n", n_cells, (unsigned long long)nnz0);
+        free(coo);
+        return 0;
     }
     const bool root = g_rank == 0;
     const uint32_t n_local = c1 - c0;

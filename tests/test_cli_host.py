@@ -132,3 +132,23 @@ def test_souporcell_rng_selftest():
     assert t[0] == "u8" and [int(x) for x in t[1:4]] == u8
     assert t[4] == "f32" and [np.float32(x) for x in t[5:8]] == f32
     assert lines[2].split() == ["f32", "0.1", "-2181.0225", "5", "0.0000001", "340282350000000000000000000000000000000", "-0"]
+
+
+@pytest.mark.parametrize("gpus", [1, 2, 3, 8])
+def test_cli_gpus_partition(tmp_path, gpus):
+    """the cell ranges `cellector --gpus N` gives its ranks (host logic, no CUDA): contiguous, covering, every rank at
+    least one cell, entry shares balanced although the rows are heavily skewed"""
+    d = synth.generate(synth.SynthConfig(n_cells=1500, n_loci=2500, density=0.02, minority_frac=0.05, seed=61, row_sigma=2.0))
+    paths = synth.write_mtx_pair(d, str(tmp_path / "in"))
+    r = subprocess.run([CLI, "-a", paths["alt.mtx"], "-r", paths["ref.mtx"], "-b", paths["barcodes.tsv"], "--output_directory",
+                        str(tmp_path / "out"), "--gpus", str(gpus), "--partition_only"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    rows = [l.split() for l in r.stdout.strip().split("\n") if l.startswith("partition rank")]
+    assert [int(x[2]) for x in rows] == list(range(gpus))
+    lo, hi, ent = [int(x[4]) for x in rows], [int(x[5]) for x in rows], [int(x[7]) for x in rows]
+    assert lo[0] == 0 and hi[-1] == d.n_cells and lo[1:] == hi[:-1] and all(h > l for l, h in zip(lo, hi))
+    per_cell = np.bincount(d.cell, minlength=d.n_cells)
+    assert ent == [int(per_cell[l:h].sum()) for l, h in zip(lo, hi)] and sum(ent) == d.nnz
+    if gpus > 1:
+        # a contiguous split cannot beat the deepest single cell; beyond that the shares stay near the mean
+        assert max(ent) <= d.nnz / gpus + per_cell.max() + 1
