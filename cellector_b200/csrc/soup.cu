@@ -42,6 +42,7 @@ namespace {
 constexpr int SOUP_TPB = 256;
 constexpr int SOUP_MAX_K = 8;
 constexpr int SOUP_TEMP_STEPS = 9;  // main.rs:137
+constexpr size_t SOUP_BATCH_TABLE_MAX = 48u << 20;  // restarts share passes only while their table is well inside the 126 MB L2
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -490,10 +491,14 @@ int soup_dispatch(clx_ctx* c, uint32_t k, uint32_t n, const float* init, double*
     if constexpr (K > SOUP_MAX_K) {
         return fail(c, CLX_ERR_ARG, "clx_soup_em: k must be in [1, 8]");
     } else {
-        // a single run gets one-slot kernels (16 K bytes of table per locus instead of 16 R K)
-        if (k == (uint32_t)K)
-            return n == 1 ? soup_run<K, 1>(c, n, init, lp, cen, losses, its, best)
-                          : soup_run<K, soup_slots(K)>(c, n, init, lp, cen, losses, its, best);
+        // A single run gets one-slot kernels (16 K bytes of table per locus instead of 16 R K).  So do the restarts of a
+        // matrix whose R-slot table would not stay in L2 (C3: 128 MB for R = 8, and 7.9 ms per restart and iteration
+        // against 5.6 ms one at a time): sharing the passes only pays while the gathered records are L2 hits.
+        if (k == (uint32_t)K) {
+            const size_t table_bytes = (size_t)c->n_loci * soup_slots(K) * K * sizeof(double2);
+            return (n == 1 || table_bytes > SOUP_BATCH_TABLE_MAX) ? soup_run<K, 1>(c, n, init, lp, cen, losses, its, best)
+                                                                  : soup_run<K, soup_slots(K)>(c, n, init, lp, cen, losses, its, best);
+        }
         return soup_dispatch<K + 1>(c, k, n, init, lp, cen, losses, its, best);
     }
 }
