@@ -148,3 +148,24 @@ def test_oracle_reproduces_the_frozen_outputs(name):
         f32 = o.soup_em(init, precise=False)
     assert f32["iterations"] == g["f32"]["iterations"] and f32["loss"] == g["f32"]["loss"]
     assert np.bincount(np.argmax(f32["log_probs"], axis=1), minlength=g["k"]).tolist() == g["f32"]["assignment_counts"]
+
+
+def test_python_chacha20_block_against_rfc7539():
+    """tests/soup_rng.py states the generator of the initial centers a second time (plain Python): its block function
+    against the RFC 7539 section 2.3.2 vector, and the thread-major seeding order of souporcell_main (main.rs:62-67)"""
+    from tests.soup_rng import StdRng07, chacha20_block, souporcell_initial_centers
+    key = bytes(range(32))
+    state = [0x61707865, 0x3320646E, 0x79622D32, 0x6B206574] + [int.from_bytes(key[4 * i:4 * i + 4], "little") for i in range(8)] + \
+            [1, 0x09000000, 0x4A000000, 0]
+    out = chacha20_block(state)
+    assert [f"{w:08x}" for w in out[:4]] == ["e4e7f110", "15593bd1", "1fdd0f50", "c47120a3"]
+    assert [f"{w:08x}" for w in out[12:]] == ["d19c12b5", "b94e16de", "e883d0cb", "4e3c50a2"]
+    # two threads, three restarts -> ceil(3 / 2) = 2 runs per thread; thread 1's generator is seeded from the SECOND
+    # 32 u8 draws of the main generator
+    c = souporcell_initial_centers(seed=4, threads=2, restarts=3, k=2, n_loci=5)
+    assert c.shape == (4, 2, 5) and c.dtype == np.float32 and (c >= np.float32(0.0001)).all() and (c <= np.float32(0.9999)).all()
+    main = StdRng07(bytes([4]) * 32)
+    main.new_seed()
+    t1 = StdRng07(main.new_seed())
+    first = min(max(t1.gen_f32(), np.float32(0.0001)), np.float32(0.9999))
+    assert c[2, 0, 0] == first
