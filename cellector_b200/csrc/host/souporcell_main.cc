@@ -6,10 +6,11 @@
 //
 //   souporcell -a alt.mtx -r ref.mtx -b barcodes.tsv -k K [--min_alt 4] [--min_ref 4] [--restarts 100] [-t 1] [--seed 4]
 //              [--initialization_strategy random_uniform]
+//              [-g known_genotypes.vcf(.gz) --known_genotypes_sample_names S0 S1 ...]
 //   additive flags: --device N, --parse_threads N, --rng_selftest
-//   refused (not built): --known_genotypes, --known_cell_assignments, --min_alt_umis / --min_ref_umis other than 0,
-//   initialization strategies other than random_uniform (the reference itself asserts on kmeans++, middle_variance
-//   and known_cell_assignments: main.rs:341-349, 389-392).
+//   refused (not built): --known_cell_assignments, --min_alt_umis / --min_ref_umis other than 0, initialization
+//   strategies other than random_uniform (the reference itself asserts on kmeans++, middle_variance and
+//   known_cell_assignments: main.rs:341-349, 389-392; random_cell_assignment needs rand's gen_range).
 //
 // Differences a user can see: the per-iteration `binomial ...` and per-restart `thread ... done` lines on stderr are
 // not printed (the loop state lives on the device); the numbers come from f64 sums and are printed as f32 like the
@@ -83,6 +84,9 @@ struct Params {  // main.rs:494-510
     std::string ref_mtx, alt_mtx, barcodes;
     uint64_t num_clusters = 0, min_alt = 4, min_ref = 4, min_alt_umis = 0, min_ref_umis = 0, restarts = 100, threads = 1;
     uint8_t seed = 4;
+    bool has_known_genotypes = false;
+    std::string known_genotypes;
+    std::vector<std::string> known_genotypes_sample_names;
     int device = 0;
     unsigned parse_threads = 0;
 };
@@ -98,6 +102,7 @@ Params load_params(int argc, char** argv) {
     static const std::map<std::string, std::string> shorts = {{"-r", "ref_matrix"}, {"-a", "alt_matrix"}, {"-b", "barcodes"},
                                                              {"-k", "num_clusters"}, {"-g", "known_genotypes"}, {"-t", "threads"}};
     std::map<std::string, std::string> kv;
+    std::vector<std::string> sample_names;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i], name, val;
         bool have_val = false;
@@ -120,6 +125,10 @@ Params load_params(int argc, char** argv) {
         if (!have_val) {
             if (i + 1 >= argc) die("error: The argument '--" + name + "' requires a value but none was supplied", 1);
             val = argv[++i];
+        }
+        if (name == "known_genotypes_sample_names") {  // `multiple: true` (params.yml:53-57): every value up to the next flag
+            sample_names.push_back(val);
+            while (i + 1 < argc && argv[i + 1][0] != '-') sample_names.push_back(argv[++i]);
         }
         kv[name] = val;
     }
@@ -153,8 +162,11 @@ Params load_params(int argc, char** argv) {
     if (kv.count("device")) p.device = (int)parse_u64("device", kv["device"]);
     if (kv.count("parse_threads")) p.parse_threads = (unsigned)parse_u64("parse_threads", kv["parse_threads"]);
     if (p.parse_threads == 0) p.parse_threads = std::max(1u, std::thread::hardware_concurrency());
-    if (kv.count("known_genotypes") || kv.count("known_genotypes_sample_names"))
-        die("--known_genotypes is not built here (initial centers from a VCF, main.rs:309-338)");
+    if (kv.count("known_genotypes")) {
+        p.has_known_genotypes = true;
+        p.known_genotypes = kv["known_genotypes"];
+    }
+    p.known_genotypes_sample_names = sample_names;
     if (kv.count("known_cell_assignments")) die("known cell assignments not yet implemented");  // the reference's assert, main.rs:342
     if (kv.count("initialization_strategy") && kv["initialization_strategy"] != "random_uniform") {
         const std::string& s = kv["initialization_strategy"];
@@ -170,11 +182,120 @@ Params load_params(int argc, char** argv) {
     return p;
 }
 
+// init_cluster_centers_known_genotypes (main.rs:309-338): 0.5 everywhere, then for every VCF record whose 0-based record
+// number is a used locus, cluster s takes (hap0 + hap1) / 2 of sample s (alleles capped at 1, clamped to [0.01, 0.99]);
+// a GT starting with '.' leaves 0.5.  Characters 0 and 2 of the GT string, like the reference.
+std::vector<float> known_genotype_centers(const Params& p, uint32_t k, uint32_t n_loci, const std::vector<uint32_t>& locus_ids) {
+    if (p.known_genotypes_sample_names.empty()) die("currently requiring known_genotypes_sample_names if known_genotypes set");
+    if (p.known_genotypes_sample_names.size() > k)
+        die("index out of bounds: the len is " + std::to_string(k) + " but the index is " + std::to_string(k) +
+            " (more sample names than clusters, main.rs:331)");
+    std::vector<float> centers((size_t)k * n_loci, 0.5f);
+    std::vector<int64_t> index_of;  // record number -> used-locus index
+    for (uint32_t i = 0; i < n_loci; ++i) {
+        if (locus_ids[i] >= index_of.size()) index_of.resize((size_t)locus_ids[i] + 1, -1);
+        index_of[locus_ids[i]] = i;
+    }
+    FileBytes f(p.known_genotypes);
+    std::vector<int> sample_col;  // column of every requested sample
+    size_t record = 0;
+    for_each_line(f.data(), f.size(), [&](const char* s, size_t n) {
+        if (n >= 2 && s[0] == '#' && s[1] == '#') return;
+        std::vector<std::pair<const char*, size_t>> col;
+        for (size_t b = 0; b <= n;) {
+            size_t e = b;
+            while (e < n && s[e] != '\t') ++e;
+            col.emplace_back(s + b, e - b);
+            b = e + 1;
+        }
+        if (n >= 1 && s[0] == '#') {  // #CHROM line: sample names from column 9 on
+            for (const std::string& name : p.known_genotypes_sample_names) {
+                int at = -1;
+                for (size_t c = 9; c < col.size(); ++c)
+                    if (std::string(col[c].first, col[c].second) == name) at = (int)c;
+                if (at < 0) die("sample " + name + " is not in the known_genotypes vcf");
+                sample_col.push_back(at);
+            }
+            return;
+        }
+        if (n == 0) return;
+        const size_t this_record = record++;
+        if (this_record >= index_of.size() || index_of[this_record] < 0) return;
+        if (sample_col.empty()) die("the known_genotypes vcf has no #CHROM header line");
+        if (col.size() < 10) die("vcf record without sample columns");
+        int gt_field = -1, fi = 0;  // position of GT in the FORMAT column
+        for (size_t b = 0; b <= col[8].second; ++fi) {
+            size_t e = b;
+            while (e < col[8].second && col[8].first[e] != ':') ++e;
+            if (e - b == 2 && col[8].first[b] == 'G' && col[8].first[b + 1] == 'T') gt_field = fi;
+            b = e + 1;
+        }
+        if (gt_field < 0) die("vcf record without a GT field");
+        for (size_t si = 0; si < sample_col.size(); ++si) {
+            if ((size_t)sample_col[si] >= col.size()) die("vcf record with too few sample columns");
+            const char* v = col[sample_col[si]].first;
+            const size_t vn = col[sample_col[si]].second;
+            size_t b = 0;
+            for (int skip = 0; skip < gt_field; ++skip) {
+                while (b < vn && v[b] != ':') ++b;
+                ++b;
+            }
+            size_t e = b;
+            while (e < vn && v[e] != ':') ++e;
+            if (b >= vn || e == b) die("empty GT");
+            if (v[b] == '.') continue;  // main.rs:324
+            if (e - b < 3) die("called `Option::unwrap()` on a `None` value (GT shorter than three characters, main.rs:326)");
+            if (v[b] < '0' || v[b] > '9' || v[b + 2] < '0' || v[b + 2] > '9') die("called `Result::unwrap()` on an `Err` value: ParseIntError (GT)");
+            const unsigned hap0 = std::min(1u, (unsigned)(v[b] - '0')), hap1 = std::min(1u, (unsigned)(v[b + 2] - '0'));
+            centers[si * (size_t)n_loci + (size_t)index_of[this_record]] = std::fmax(std::fmin((float)(hap0 + hap1) / 2.0f, 0.99f), 0.01f);
+        }
+    });
+    return centers;
+}
+
 #define CLX(call)                                                                                  \
     do {                                                                                           \
         const int rc__ = (call);                                                                   \
         if (rc__ != CLX_OK) die(std::string(#call) + " failed: " + clx_last_error(ctx));           \
     } while (0)
+
+// main.rs:89-105: the best loss on stderr; zip(barcodes, log probabilities): barcode, first best cluster, every log probability
+void print_results(const std::vector<std::string>& barcodes, const std::vector<double>& log_probs, uint32_t n_cells, uint32_t k,
+                   double best_loss) {
+    {
+        std::string s = "best total log probability = ";
+        append_f32(s, (float)best_loss);  // main.rs:89
+        fprintf(stderr, "%s\n", s.c_str());
+    }
+    // main.rs:91-105: zip(barcodes, log probabilities): barcode, first best cluster, every log probability
+    std::string out;
+    out.reserve(1 << 20);
+    const size_t n_out = std::min<size_t>(barcodes.size(), n_cells);
+    for (size_t c = 0; c < n_out; ++c) {
+        const double* lp = &log_probs[c * k];
+        uint32_t bi = 0;
+        float blp = -INFINITY;
+        for (uint32_t q = 0; q < k; ++q)
+            if ((float)lp[q] > blp) {
+                bi = q;
+                blp = (float)lp[q];
+            }
+        out += barcodes[c];
+        out += '\t';
+        append_u64(out, bi);
+        out += '\t';
+        for (uint32_t q = 0; q < k; ++q) {
+            append_f32(out, (float)lp[q]);
+            if (q + 1 < k) out += '\t';
+        }
+        out += '\n';
+        if (out.size() > (1 << 20) - 4096) {
+            fwrite(out.data(), 1, out.size(), stdout);
+            out.clear();
+        }
+    }
+    fwrite(out.data(), 1, out.size(), stdout);
+}
 
 }  // namespace
 
@@ -246,6 +367,20 @@ int main(int argc, char** argv) {
     // souporcell_main (main.rs:62-88): one generator per thread seeded from the main one, solves_per_thread runs each;
     // a thread keeps its first best run, the threads are compared in order: the first maximum in thread-major order
     const uint32_t k = (uint32_t)params.num_clusters;
+    if (params.has_known_genotypes) {
+        // every restart of the reference starts from the same VCF-derived centers and ends in the same place (main.rs:303-305:
+        // no draw is made); the first one is kept by the strict > of main.rs:73 — one run here
+        std::vector<uint32_t> locus_ids(n_loci);
+        CLX(clx_get_locus_ids(ctx, locus_ids.data()));
+        const std::vector<float> centers = known_genotype_centers(params, k, n_loci, locus_ids);
+        std::vector<double> log_probs((size_t)n_cells * k);
+        double loss = 0.0;
+        uint32_t iterations = 0;
+        CLX(clx_soup_em(ctx, k, centers.data(), log_probs.data(), nullptr, &loss, &iterations));
+        print_results(barcodes, log_probs, n_cells, k, loss);
+        clx_destroy(ctx);
+        return 0;
+    }
     const uint64_t solves_per_thread = (params.restarts + params.threads - 1) / params.threads;  // (restarts / threads).ceil()
     const uint64_t runs = solves_per_thread * params.threads;
     if (runs == 0) die("no restarts");
@@ -267,39 +402,7 @@ int main(int argc, char** argv) {
     std::vector<uint32_t> iterations(runs);
     uint32_t best = 0;
     CLX(clx_soup_restarts(ctx, k, (uint32_t)runs, centers.data(), log_probs.data(), nullptr, losses.data(), iterations.data(), &best));
-    {
-        std::string s = "best total log probability = ";
-        append_f32(s, (float)losses[best]);  // main.rs:89
-        fprintf(stderr, "%s\n", s.c_str());
-    }
-    // main.rs:91-105: zip(barcodes, log probabilities): barcode, first best cluster, every log probability
-    std::string out;
-    out.reserve(1 << 20);
-    const size_t n_out = std::min<size_t>(barcodes.size(), n_cells);
-    for (size_t c = 0; c < n_out; ++c) {
-        const double* lp = &log_probs[c * k];
-        uint32_t bi = 0;
-        float blp = -INFINITY;
-        for (uint32_t q = 0; q < k; ++q)
-            if ((float)lp[q] > blp) {
-                bi = q;
-                blp = (float)lp[q];
-            }
-        out += barcodes[c];
-        out += '\t';
-        append_u64(out, bi);
-        out += '\t';
-        for (uint32_t q = 0; q < k; ++q) {
-            append_f32(out, (float)lp[q]);
-            if (q + 1 < k) out += '\t';
-        }
-        out += '\n';
-        if (out.size() > (1 << 20) - 4096) {
-            fwrite(out.data(), 1, out.size(), stdout);
-            out.clear();
-        }
-    }
-    fwrite(out.data(), 1, out.size(), stdout);
+    print_results(barcodes, log_probs, n_cells, k, losses[best]);
     clx_destroy(ctx);
     return 0;
 }

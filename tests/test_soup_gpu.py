@@ -169,7 +169,64 @@ def test_souporcell_cli_matches_oracle(tmp_path):
     agree = (np.array([int(x[1]) for x in rows]) == truth).mean()
     assert max(agree, 1 - agree) > 0.95
     # what the reference asserts on or this build leaves out is refused, not ignored
-    for extra in (["--initialization_strategy", "kmeans++"], ["--known_genotypes", "x.vcf"], ["--min_alt_umis", "3"]):
+    for extra in (["--initialization_strategy", "kmeans++"], ["--known_cell_assignments", "x.tsv"], ["--min_alt_umis", "3"]):
         bad = subprocess.run([cli, "-a", paths["alt.mtx"], "-r", paths["ref.mtx"], "-b", paths["barcodes.tsv"], "-k", "2", *extra],
                              capture_output=True, text=True, timeout=60)
         assert bad.returncode != 0 and "not" in bad.stderr
+
+
+def test_souporcell_cli_known_genotypes(tmp_path):
+    """`souporcell -g genotypes.vcf.gz --known_genotypes_sample_names ...` (init_cluster_centers_known_genotypes,
+    main.rs:309-338): centers from the samples' GT fields, one deterministic EM run; against the oracle from the same
+    centers built here.  Cluster s is sample s, so the clusters are not arbitrary: 1 = the minority individual."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cli = os.path.join(root, "cellector_b200", "bin", "souporcell")
+    cfg = synth.SynthConfig(n_cells=500, n_loci=1500, density=0.05, minority_frac=0.3, seed=60)
+    d = synth.generate(cfg)
+    paths = synth.write_mtx_pair(d, str(tmp_path / "in"))
+    p_major, p_minor = synth.locus_model(cfg)
+    gt_of = {0.01: "0/0", 0.5: "0|1", 0.99: "1/1"}
+    rng = np.random.Generator(np.random.Philox(7))
+    gts = []
+    vcf = tmp_path / "in" / "known.vcf"
+    with open(vcf, "w") as f:
+        f.write("##fileformat=VCFv4.2\n##source=synthetic\n#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\tother\tmin\tmaj\n")
+        for i in range(d.n_loci):
+            g_maj, g_min = gt_of[float(p_major[i])], gt_of[float(p_minor[i])]
+            u = rng.random()
+            if u < 0.05:
+                g_maj = "./."            # missing: the centre keeps 0.5
+            elif u < 0.08:
+                g_min = "2/1"            # alleles are capped at 1 (main.rs:325-326)
+            gts.append((g_maj, g_min))
+            f.write(f"chr1\t{100 + i}\t.\tA\tG\t.\t.\t.\tDP:GT:GQ\t9:0/1:3\t12:{g_min}:40\t7:{g_maj}:30\n")
+    subprocess.check_call(["gzip", str(vcf)])
+    r = subprocess.run([cli, "-a", paths["alt.mtx"], "-r", paths["ref.mtx"], "-b", paths["barcodes.tsv"], "-k", "2",
+                        "-g", str(vcf) + ".gz", "--known_genotypes_sample_names", "maj", "min", "--restarts", "3"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+
+    def centre(gt):
+        if gt[0] == ".":
+            return np.float32(0.5)
+        v = np.float32(min(int(gt[0]), 1) + min(int(gt[2]), 1)) / np.float32(2.0)
+        return min(max(v, np.float32(0.01)), np.float32(0.99))
+
+    with SoupOracle() as orc:
+        n_used, _ = orc.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells)
+        ids = orc.locus_ids()
+        init = np.array([[centre(gts[l][s]) for l in ids] for s in (0, 1)], np.float32)
+        want = orc.soup_em(init, precise=True)
+    rows = [l.split("\t") for l in r.stdout.strip().split("\n")]
+    got = np.array([[float(v) for v in x[2:]] for x in rows])
+    np.testing.assert_allclose(got, want["log_probs"], rtol=2e-7, atol=1e-30)
+    m = [l for l in r.stderr.split("\n") if l.startswith("best total log probability = ")]
+    assert float(m[0].split("= ")[1]) == pytest.approx(want["loss"], rel=1e-6)
+    assign = np.array([int(x[1]) for x in rows])
+    assert (assign == np.asarray(d.is_minority, dtype=np.int64)).mean() > 0.97
+    # more sample names than clusters is the reference's index panic
+    bad = subprocess.run([cli, "-a", paths["alt.mtx"], "-r", paths["ref.mtx"], "-b", paths["barcodes.tsv"], "-k", "2", "-g",
+                          str(vcf) + ".gz", "--known_genotypes_sample_names", "maj", "min", "other"], capture_output=True, text=True, timeout=60)
+    assert bad.returncode != 0 and "index out of bounds" in bad.stderr
