@@ -1,6 +1,7 @@
 // soup_rng.h — the random draws of souporcell's initialisation (souporcell/souporcell/src/main.rs:62-67, 354-364, 623-629).
-// The reference uses rand 0.7's `StdRng` (souporcell/Cargo.toml: rand = "0.7.0"), a third-party crate that is NOT in
-// /root/reference.  Its published definition is restated here:
+// The reference uses rand's `StdRng` — rand 0.7.2 with rand_chacha 0.2.1 and rand_core 0.5.1, pinned at
+// souporcell/souporcell/Cargo.lock:319-364 (Cargo.toml: rand = "0.7.0") — third-party crates that are NOT in
+// /root/reference.  Their published definition is restated here:
 //   StdRng (rand 0.7)            = ChaCha with 20 rounds (rand_chacha 0.2 ChaCha20Rng), seeded with 32 key bytes,
 //                                  64-bit block counter from 0 (state words 12-13), stream id 0 (words 14-15);
 //                                  the output is the sequence of 32-bit little-endian words of consecutive blocks;

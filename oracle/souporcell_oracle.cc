@@ -11,8 +11,10 @@
 //   update_centers_average      main.rs:273-280
 //   update_final / reset_sums_denoms   main.rs:244-262
 //   souporcell_main's best-of-restarts and argmax assignment   main.rs:62-106
-// The reference draws its initial centers from rand 0.7's StdRng (main.rs:354-364); that generator is a third-party
-// crate absent from /root/reference, so the centers are an INPUT here (the caller's own generator).
+// The reference draws its initial centers from rand 0.7.2's StdRng (main.rs:354-364; Cargo.lock:319-321); that generator is
+// a third-party crate absent from /root/reference, so the centers are an INPUT here (the caller's own generator).
+// ln_binomial is statrs 0.11.0's here (souporcell/souporcell/Cargo.lock:514-515), not cellector's 0.16.0: the same published
+// algorithm (ln of the cached f64 factorials up to 170, Lanczos ln_gamma beyond), restated in statrs_compat.h.
 //
 // Two arithmetic modes of the same statements:
 //   faithful (float)   every variable f32 like the reference, sums in the reference's serial order
