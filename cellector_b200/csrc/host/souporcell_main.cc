@@ -8,7 +8,7 @@
 //              [--initialization_strategy random_uniform]
 //              [-g known_genotypes.vcf(.gz) --known_genotypes_sample_names S0 S1 ...]
 //   additive flags: --device N, --parse_threads N, --rng_selftest
-//   refused (not built): --known_cell_assignments, --min_alt_umis / --min_ref_umis other than 0, initialization
+//   refused (not built): --known_cell_assignments, initialization
 //   strategies other than random_uniform (the reference itself asserts on kmeans++, middle_variance and
 //   known_cell_assignments: main.rs:341-349, 389-392; random_cell_assignment needs rand's gen_range).
 //
@@ -175,8 +175,9 @@ Params load_params(int argc, char** argv) {
         if (s == "random_cell_assignment") die("initialization_strategy random_cell_assignment is not built here (main.rs:366-387)");
         die("initialization strategy must be one of kmeans++, random_uniform, random_cell_assignment, middle_variance");
     }
-    if (p.min_alt_umis != 0 || p.min_ref_umis != 0)
-        die("--min_alt_umis / --min_ref_umis other than 0 are not built here (the locus filter is clx_load_coo's)");
+    if ((p.min_alt_umis != 0 || p.min_ref_umis != 0) && p.min_alt == 0 && p.min_ref == 0)
+        die("--min_alt_umis / --min_ref_umis need --min_alt or --min_ref of at least 1 in this build (a locus that fails the UMI "
+            "minima is dropped on the host before clx_load_coo, whose own filter then has to reject the emptied locus)");
     if (p.num_clusters < 1 || p.num_clusters > 8) die("--num_clusters must be between 1 and 8 in this build");
     if (p.threads < 1) die("attempt to divide by zero (threads = 0)");
     return p;
@@ -355,11 +356,35 @@ int main(int argc, char** argv) {
     if (!coo) die("out of host memory");
     CooSink sink{coo, coo + nnz0, coo + 2 * nnz0, coo + 3 * nnz0};
     parse_mtx_pair(alt, ref, plan, sink, params.parse_threads);
+    // the UMI minima of souporcell's locus filter (main.rs:440: summed ref / alt counts of the locus over all its lines):
+    // clx_load_coo filters on cell counts only, so the lines of a locus that fails them are dropped here; the emptied
+    // locus then fails min_ref / min_alt there, and the dense renumbering of the others is the same
+    uint64_t nnz_load = nnz0;
+    if (params.min_ref_umis != 0 || params.min_alt_umis != 0) {
+        std::vector<uint64_t> umis(2 * (size_t)n_loci0, 0);
+        for (uint64_t i = 0; i < nnz0; ++i) {
+            if (sink.locus[i] >= n_loci0) die("assertion failed: locus < total_loci");  // main.rs:414
+            umis[2 * (size_t)sink.locus[i]] += sink.ref[i];
+            umis[2 * (size_t)sink.locus[i] + 1] += sink.alt[i];
+        }
+        uint64_t w = 0;
+        for (uint64_t i = 0; i < nnz0; ++i) {
+            const size_t l = sink.locus[i];
+            if (umis[2 * l] >= params.min_ref_umis && umis[2 * l + 1] >= params.min_alt_umis) {
+                sink.locus[w] = sink.locus[i];
+                sink.cell[w] = sink.cell[i];
+                sink.ref[w] = sink.ref[i];
+                sink.alt[w] = sink.alt[i];
+                ++w;
+            }
+        }
+        nnz_load = w;
+    }
     cuda_init.join();
     if (create_rc != CLX_OK) die("clx_create failed: " + create_err);
     uint32_t n_loci = 0;
     uint64_t nnz = 0;
-    CLX(clx_load_coo(ctx, nnz0, n_loci0, n_cells, sink.locus, sink.cell, sink.ref, sink.alt, (uint32_t)params.min_ref,
+    CLX(clx_load_coo(ctx, nnz_load, n_loci0, n_cells, sink.locus, sink.cell, sink.ref, sink.alt, (uint32_t)params.min_ref,
                      (uint32_t)params.min_alt, &n_loci, &nnz));
     free(coo);
     fprintf(stderr, "total loci used %u\n", n_loci);  // main.rs:465

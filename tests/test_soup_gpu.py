@@ -169,10 +169,21 @@ def test_souporcell_cli_matches_oracle(tmp_path):
     agree = (np.array([int(x[1]) for x in rows]) == truth).mean()
     assert max(agree, 1 - agree) > 0.95
     # what the reference asserts on or this build leaves out is refused, not ignored
-    for extra in (["--initialization_strategy", "kmeans++"], ["--known_cell_assignments", "x.tsv"], ["--min_alt_umis", "3"]):
+    # the UMI minima of souporcell's locus filter (main.rs:440), applied by the host before the load
+    r2 = subprocess.run([cli, "-a", paths["alt.mtx"], "-r", paths["ref.mtx"], "-b", paths["barcodes.tsv"], "-k", "2", "--restarts", "1",
+                         "--min_ref_umis", "12", "--min_alt_umis", "8", "--seed", str(seed)], capture_output=True, text=True, timeout=300)
+    assert r2.returncode == 0, r2.stderr[-2000:]
+    with SoupOracle() as orc:
+        n_umi, _ = orc.load_cell_data(d.locus, d.cell, d.ref, d.alt, d.n_loci, d.n_cells, 4, 4, 12, 8)
+        assert 0 < n_umi < n_used and f"total loci used {n_umi}" in r2.stderr
+        want2 = orc.soup_em(souporcell_initial_centers(seed, 1, 1, k, n_umi)[0], precise=True)
+    got2 = np.array([[float(v) for v in l.split("\t")[2:]] for l in r2.stdout.strip().split("\n")])
+    np.testing.assert_allclose(got2, want2["log_probs"], rtol=2e-7, atol=1e-30)
+    for extra in (["--initialization_strategy", "kmeans++"], ["--known_cell_assignments", "x.tsv"],
+                  ["--min_alt_umis", "3", "--min_alt", "0", "--min_ref", "0"]):
         bad = subprocess.run([cli, "-a", paths["alt.mtx"], "-r", paths["ref.mtx"], "-b", paths["barcodes.tsv"], "-k", "2", *extra],
                              capture_output=True, text=True, timeout=60)
-        assert bad.returncode != 0 and "not" in bad.stderr
+        assert bad.returncode != 0 and ("not" in bad.stderr or "need" in bad.stderr), bad.stderr
 
 
 def test_souporcell_cli_known_genotypes(tmp_path):
