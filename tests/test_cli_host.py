@@ -152,3 +152,20 @@ def test_cli_gpus_partition(tmp_path, gpus):
     if gpus > 1:
         # a contiguous split cannot beat the deepest single cell; beyond that the shares stay near the mean
         assert max(ent) <= d.nnz / gpus + per_cell.max() + 1
+
+
+@pytest.mark.parametrize("args,needle", [
+    (["-a", "a", "-r", "r", "-b", "b"], "--num_clusters"),                                      # required argument missing
+    (["-a", "a", "-r", "r", "-b", "b", "-k", "2", "--bogus", "1"], "wasn't expected"),
+    (["-a", "a", "-r", "r", "-b", "b", "-k", "2", "--seed", "256"], "seed is a u8"),
+    (["-a", "a", "-r", "r", "-b", "b", "-k", "2", "--initialization_strategy", "kmeans++"], "kmeans++ not yet implemented"),
+    (["-a", "a", "-r", "r", "-b", "b", "-k", "2", "--initialization_strategy", "random_cell_assignment"], "not built"),
+    (["-a", "a", "-r", "r", "-b", "b", "-k", "2", "--known_cell_assignments", "x"], "known cell assignments not yet implemented"),
+    (["-a", "a", "-r", "r", "-b", "b", "-k", "9"], "between 1 and 8"),
+    (["-a", "a", "-r", "r", "-b", "b", "-k", "2", "-t", "0"], "divide by zero"),
+])
+def test_souporcell_cli_argument_errors(args, needle):
+    """the souporcell host refuses what the reference refuses (its asserts and unwraps) and what this build leaves out,
+    before it touches a file or the GPU"""
+    r = subprocess.run([SOUP_CLI, *args], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and needle in r.stderr, r.stderr
